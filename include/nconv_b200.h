@@ -1,0 +1,152 @@
+/* nconv_b200 — C ABI of the B200 (sm_100a) normalized-convolution hot path.
+ *
+ * The reference (lllllcf/Realtime-Depth-Estimation-Nconv) is pure Python/PyTorch and has no
+ * FFI of its own; its "operator API" for this path is nn.Module.forward.  Each entry point
+ * below cites the reference lines whose ATen call sequence it replaces.  A maintainer binds
+ * them with ctypes; `realtime-depth-estimation-nconv_b200/nconv_b200/`
+ * is that binding, registered with torch.library.
+ *
+ * Conventions
+ *   - all tensors: contiguous fp32 NCHW device memory owned by the caller
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued, never synchronised
+ *   - no allocation inside; scratch is passed in (`workspace`, size from *_workspace_bytes)
+ *   - return value: 0, or a cudaError_t, or an NCONV_B200_ERR_* code; never throws
+ *   - thread-safe for concurrent callers on different devices (nn.DataParallel style)
+ */
+#ifndef NCONV_B200_H_
+#define NCONV_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NCONV_B200_ERR_BAD_ARG 100001
+#define NCONV_B200_ERR_UNSUPPORTED 100002
+#define NCONV_B200_ERR_WORKSPACE 100003
+
+/* flags of nconv_b200_fwd_desc */
+#define NCONV_B200_F_THRESH 1 /* conf = (xa > thr), xa used raw  (step1.py:53-54)            */
+#define NCONV_B200_F_POOL 2   /* also emit 2x2/2 max-pools of y and cout (step1.py:62-74)     */
+#define NCONV_B200_F_TAIL 4   /* nconv6(valid 3x3) -> nconv7(1x1,pad 2) -> crop (step1.py:90-94) */
+
+int nconv_b200_abi_version(void);
+const char* nconv_b200_error_string(int code);
+/* number of kernels this library has enqueued in the calling process (all devices) */
+unsigned long long nconv_b200_launch_count(void);
+
+/* ---- (a3) NConv2d.forward — /root/reference/models/step1.py:116-149 -------------------
+ * D = conv(c,W); N = conv(x*c,W); y = N/(D+eps)+b; cout = D/sum(W[o]).  stride 1, dil 1,
+ * groups 1, zero padding (ph,pw).  One fused kernel. */
+int nconv_b200_nconv2d_fwd(const float* x, const float* c, const float* w, const float* bias,
+                           float* y, float* cout, int B, int Ci, int Co, int H, int W, int kh,
+                           int kw, int ph, int pw, float eps, void* stream);
+
+/* ---- fused stages of DNET.forward — step1.py:51-94 -------------------------------------
+ * One NConv layer whose input is [source A | nearest-upsampled source B] channel-concatenated
+ * (a_first: A's channels come first in the weight's input-channel axis — step1.py:80,85 —
+ * else B first — step1.py:90), optionally thresholding A into a confidence (step1.py:53),
+ * optionally also emitting the two independent 2x2 max-pools (step1.py:62-74), optionally
+ * finishing with the nconv7 1x1 + crop tail (step1.py:92-94). */
+typedef struct {
+  const float* xa;  /* [B,CA,H,W] data of source A                                   */
+  const float* ca;  /* [B,CA,H,W] confidence of A (ignored with F_THRESH)            */
+  const float* xb;  /* [B,CB,HB,WB] data of source B (NULL when CB==0)               */
+  const float* cb;  /* [B,CB,HB,WB]                                                  */
+  const float* w;   /* [CO,CA+CB,K,K]                                                */
+  const float* bias;/* [CO]                                                          */
+  float* y;         /* [B,CO,HO,WO], HO=H+2*pad-K+1; may be NULL with F_TAIL         */
+  float* cout;      /* [B,CO,HO,WO]                                                  */
+  float* y_pool;    /* [B,CO,HO/2,WO/2] with F_POOL                                  */
+  float* c_pool;
+  const float* w_tail; /* [1,CO,1,1] nconv7 weight, with F_TAIL                      */
+  const float* b_tail; /* [1]                                                        */
+  float* out_tail;     /* [B,1,H,W]                                                  */
+  int B, CA, CB, CO, H, W, HB, WB, K, pad;
+  int a_first;
+  int flags;
+  float eps, thr;
+} nconv_b200_fwd_desc;
+int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* stream);
+
+/* ---- (a3, backward) analytic gradient of NConv2d.forward ----------------
+ * Consumes the saved forward outputs (y, cout) instead of recomputing D and N:
+ * D = cout*s, N/(D+eps) = y-b.  gx/gc: [B,Ci,H,W]; gw: [Co,Ci,kh,kw]; gb: [Co].
+ * gx or gc may be NULL (input needs no grad).  workspace: nconv_b200_nconv2d_bwd_workspace_bytes. */
+size_t nconv_b200_nconv2d_bwd_workspace_bytes(int B, int Ci, int Co, int H, int W, int kh, int kw,
+                                              int ph, int pw);
+int nconv_b200_nconv2d_bwd(const float* gy, const float* gcout, const float* x, const float* c,
+                           const float* w, const float* bias, const float* y, const float* cout,
+                           float* gx, float* gc, float* gw, float* gb, int B, int Ci, int Co, int H,
+                           int W, int kh, int kw, int ph, int pw, float eps, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
+/* ---- (a2) EnforcePos — step1.py:190-212: w <- pos_fn(w) in place (training only) --------
+ * mode 0 softplus(beta=10), 1 exp, 2 sigmoid, 3 softmax over each [kh*kw] group (group=kh*kw). */
+int nconv_b200_enforce_pos(float* w, long long n, int mode, int group, void* stream);
+
+/* ---- (a4) threshold — step1.py:53: c0 = (S > thr) as fp32 ------------------------------ */
+int nconv_b200_confidence_mask(const float* s, float* c, long long n, float thr, void* stream);
+
+/* ---- (a5) 2x2/2 max-pool — step1.py:62-74 (F.max_pool2d(x,2,2)); first-max tie-break ---- */
+int nconv_b200_maxpool2x2_fwd(const float* x, float* y, int planes, int H, int W, void* stream);
+int nconv_b200_maxpool2x2_bwd(const float* gy, const float* x, float* gx, int planes, int H,
+                              int W, void* stream);
+
+/* ---- (a6) nearest upsample + channel concat — step1.py:78-90 --------------------------- */
+int nconv_b200_upcat_fwd(const float* skip, const float* low, float* out, int B, int Cs, int Cl,
+                         int H, int W, int HL, int WL, int skip_first, void* stream);
+int nconv_b200_upcat_bwd(const float* gout, float* gskip, float* glow, int B, int Cs, int Cl,
+                         int H, int W, int HL, int WL, int skip_first, void* stream);
+
+/* ---- (a4-a8) whole DNET.forward, inference — step1.py:51-94 ----------------------------
+ * params: 18 pointers {w,b} for nconv1,nconv2,nconv_down1..3,nconv4,nconv5,nconv6,nconv7.
+ * S: [B,1,H,W] -> out: [B,1,H,W] (crop generalised to [1:H+1,1:W+1]).
+ * conf_out (optional, may be NULL): [B,1,H,W] confidence of the last layer, same crop. */
+size_t nconv_b200_dnet_workspace_bytes(int B, int H, int W);
+int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out, int B, int H,
+                            int W, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- SETP2 building blocks — /root/reference/models/step2.py ---------------------------
+ * Direct convolution y = act(scale[o]*conv(cat[a,b]) + shift[o]) + residual, covering
+ * ConvBlock (:290-297), RGBEncoder (:134-154, BN folded to scale/shift), Basic2d (:178-195),
+ * Conv1x1 (:130), Conv3x3 head + residual (:156, :255-257).  K in {1,3}, stride in {1,2},
+ * pad = K/2.  scale/shift/residual/b may be NULL. */
+typedef struct {
+  const float* a;       /* [B,CA,H,W]                                            */
+  const float* b;       /* [B,CB,H,W] concatenated after a, or NULL               */
+  const float* w;       /* [CO,CA+CB,K,K]                                        */
+  const float* scale;   /* [CO] or NULL (=1)                                     */
+  const float* shift;   /* [CO] or NULL (=0)                                     */
+  const float* residual;/* [B,CO,HO,WO] added after the activation, or NULL      */
+  float* y;             /* [B,CO,HO,WO]                                          */
+  int B, CA, CB, CO, H, W, K, stride, relu;
+} nconv_b200_conv_desc;
+int nconv_b200_conv2d_fwd(const nconv_b200_conv_desc* d, void* stream);
+
+/* ConvTranspose2d(k=4,s=2,p=1,bias=False) of cat[a(1ch... CA), b(CB)] + scale/shift + ReLU —
+ * Basic2dTrans, step2.py:197-214; w: [CA+CB, CO, 4, 4]. */
+int nconv_b200_convT4x4s2_fwd(const float* a, const float* b, const float* w, const float* scale,
+                              const float* shift, float* y, int B, int CA, int CB, int CO, int H,
+                              int W, int relu, void* stream);
+
+/* F.interpolate(mode='bilinear', align_corners=True) to (HO,WO) — step2.py:252,271 */
+int nconv_b200_bilinear_ac_fwd(const float* x, float* y, int planes, int H, int W, int HO, int WO,
+                               void* stream);
+
+/* zero rows [0,top) and [H-bottom,H) and cols [0,left) — step2.py:122-124 */
+int nconv_b200_zero_border(float* x, int planes, int H, int W, int top, int bottom, int left,
+                           void* stream);
+
+/* BatchNorm (eval) -> per-channel scale/shift, optionally absorbing a conv bias:
+ * scale = gamma/sqrt(var+eps); shift = beta + (bias-mean)*scale. */
+int nconv_b200_bn_fold(const float* gamma, const float* beta, const float* mean, const float* var,
+                       const float* conv_bias, float* scale, float* shift, int C, float eps,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NCONV_B200_H_ */

@@ -1,0 +1,182 @@
+"""TEST INFRASTRUCTURE ONLY — generates tests/golden/*.npz by running the UNMODIFIED reference
+(/root/reference, imported through oracle/ref_shim.py) on CPU fp32 in this container.
+
+The reference ships no tests or golden vectors, and it is Python so it cannot
+travel to the GPU box; these fixtures are therefore the pin for both the oracle restatement
+(oracle/nconv_oracle.py) and the CUDA path.  Re-run:  python oracle/gen_golden.py
+Everything is seeded; inputs that are cheap to regenerate are stored as seeds, not tensors.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "realtime-depth-estimation-nconv_b200"))
+from oracle import ref_shim  # noqa: E402
+from nconv_b200.synthetic import (nconv_layer_case, NCONV_LAYER_CASES, sparse_depth_nyu,  # noqa: E402
+                                  sparse_depth_kitti, setp2_inputs, randomise_bn_stats)
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def state_fingerprint(sd) -> str:
+    """Order-independent fingerprint of a state_dict (used to prove RNG-identical init)."""
+    h = hashlib.sha256()
+    for k in sorted(sd):
+        v = sd[k]
+        h.update(k.encode())
+        h.update(_np(v.double() if v.is_floating_point() else v).tobytes())
+    return h.hexdigest()
+
+
+def gen_nconv_layers(r1):
+    """Per-layer forward + backward through the reference NConv2d (step1.py:97-172)."""
+    out = {}
+    for idx, case in enumerate(NCONV_LAYER_CASES):
+        ci, co, k, pad, B, H, W = case
+        torch.manual_seed(1000 + idx)
+        layer = r1.NConv2d(ci, co, (k, k), 'softplus', 'p' if k > 1 else 'k', padding=(pad, pad))
+        layer.train()
+        x, c, gy, gc = nconv_layer_case(idx)
+        x.requires_grad_(True); c.requires_grad_(True)
+        y, cout = layer(x, c)             # training mode: hook applies softplus in place first
+        (y * gy).sum().add((cout * gc).sum()).backward()
+        p = "case%d_" % idx
+        out[p + "w"] = _np(layer.weight); out[p + "b"] = _np(layer.bias)
+        out[p + "y"] = _np(y); out[p + "cout"] = _np(cout)
+        out[p + "gx"] = _np(x.grad); out[p + "gc"] = _np(c.grad)
+        out[p + "gw"] = _np(layer.weight.grad); out[p + "gb"] = _np(layer.bias.grad)
+    np.savez_compressed(os.path.join(OUT, "nconv2d_layers.npz"), **out)
+
+
+def _setp1_model(r1, seed):
+    torch.manual_seed(seed)
+    m = r1.SETP1_NCONV()
+    fp_init = state_fingerprint(m.state_dict())
+    m.train()
+    with torch.no_grad():
+        m(torch.zeros(1, 1, 16, 16))       # one training forward => softplus applied (KA4, KA10)
+    m.eval()
+    return m, fp_init
+
+
+def gen_setp1(r1):
+    m, fp_init = _setp1_model(r1, 0)
+    sd = {k: _np(v) for k, v in m.state_dict().items() if k.endswith(("weight", "bias")) and "bnorm" not in k}
+    out = {"sd_" + k: v for k, v in sd.items()}
+    out["init_fingerprint_seed0"] = np.array(fp_init)
+    out["post_hook_fingerprint"] = np.array(state_fingerprint(m.state_dict()))
+
+    # small frames (ragged: not multiples of the tile or of 8) incl. per-layer intermediates
+    acts = {}
+    hooks = []
+    for name in ("nconv1", "nconv2", "nconv_down1", "nconv_down2", "nconv_down3", "nconv4", "nconv5", "nconv6", "nconv7"):
+        hooks.append(getattr(m.d_net, name).register_forward_hook(
+            lambda mod, inp, outp, name=name: acts.__setitem__(name, outp)))
+    torch.manual_seed(11)
+    S = torch.rand(2, 1, 64, 96) * 9 + 1
+    S = S * (torch.rand_like(S) < 0.1)
+    with torch.no_grad():
+        y = m(S)
+    out["small_S"] = _np(S); out["small_out"] = _np(y)      # reference crop -> [2,1,65,97]
+    for name, (xo, co) in acts.items():
+        out["small_" + name + "_x"] = _np(xo); out["small_" + name + "_c"] = _np(co)
+    for h in hooks:
+        h.remove()
+    torch.manual_seed(12)
+    S = torch.rand(1, 1, 45, 70) * 9 + 1
+    S = S * (torch.rand_like(S) < 0.2)
+    with torch.no_grad():
+        y = m(S)
+    out["odd_S"] = _np(S); out["odd_out"] = _np(y)
+
+    # BASELINE.json config 1: NYU shape, 500 valid points (inputs regenerated from the seed)
+    S = sparse_depth_nyu(1, seed=0)
+    with torch.no_grad():
+        y = m(S)
+    out["nyu_out"] = _np(y)
+    # KITTI shape: the reference's hard-coded crop yields 353x640 (KA2)
+    S = sparse_depth_kitti(1, seed=2000)
+    with torch.no_grad():
+        y = m(S)
+    out["kitti_out"] = _np(y)
+    np.savez_compressed(os.path.join(OUT, "setp1.npz"), **out)
+
+
+def gen_setp1_train(r1):
+    """One training-mode forward/backward of the reference SETP1 (autograd through pools,
+    upsamples, cats and 18 convs) with a fixed linear loss, from a fresh seed-3 model."""
+    torch.manual_seed(3)
+    m = r1.SETP1_NCONV()
+    m.train()
+    torch.manual_seed(13)
+    S = torch.rand(2, 1, 40, 56) * 9 + 1
+    S = S * (torch.rand_like(S) < 0.15)
+    G = torch.randn(2, 1, 40, 56)
+    y = m(S)[:, :, :40, :56]
+    (y * G).sum().backward()
+    out = {"S": _np(S), "G": _np(G), "out": _np(y)}
+    for k, p in m.named_parameters():
+        if "bnorm" in k:
+            continue
+        out["w_" + k] = _np(p)               # post-hook (softplus'ed) values
+        out["g_" + k] = _np(p.grad)
+    np.savez_compressed(os.path.join(OUT, "setp1_train.npz"), **out)
+
+
+def gen_setp2(r1, r2):
+    """SETP2_BP_EXPORT / TRAIN-graph forward at 480x640 (the only size the reference's hard-coded
+    crop allows), eval mode, randomised BN running statistics (so the fold is exercised)."""
+    with ref_shim.two_arg_step1():
+        torch.manual_seed(5)
+        m = r2.SETP2_BP_EXPORT()
+        fp_init = state_fingerprint(m.state_dict())
+        m.train()
+        with torch.no_grad():
+            m.step1(torch.zeros(1, 1, 16, 16))
+        m.eval()
+        randomise_bn_stats(m, seed=55)
+        rgb0, d0, rgb1, d1 = setp2_inputs(1, seed=7)
+        acts = {}
+        hs = [getattr(m, n).register_forward_hook(lambda mod, i, o, n=n: acts.__setitem__(n, o))
+              for n in ("fuse0", "fuse1", "fuse2", "fuse3", "step1")]
+        with torch.no_grad():
+            o0, o1 = m(rgb0, d0, rgb1, d1)
+        for h in hs:
+            h.remove()
+    out = {"init_fingerprint_seed5": np.array(fp_init),
+           "eval_fingerprint": np.array(state_fingerprint(m.state_dict())),
+           "out0": _np(o0), "out1": _np(o1), "step1": _np(acts["step1"])}
+    for n in ("fuse0", "fuse1", "fuse2"):
+        out[n + "_depth"] = _np(acts[n][1])
+    # fuse3's depth was border-zeroed in place by the EXPORT forward; keep a checksum of features
+    out["fuse3_feat_sum"] = np.array(float(acts["fuse3"][0].double().sum()))
+    np.savez_compressed(os.path.join(OUT, "setp2_export.npz"), **out)
+
+
+def main():
+    assert ref_shim.reference_available(), "needs /root/reference"
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(8)
+    r1, r2 = ref_shim.load_reference()
+    gen_nconv_layers(r1)
+    gen_setp1(r1)
+    gen_setp1_train(r1)
+    gen_setp2(r1, r2)
+    for f in sorted(os.listdir(OUT)):
+        print(f, os.path.getsize(os.path.join(OUT, f)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,120 @@
+// Whole DNET.forward (inference) as one enqueue of 9 fused kernels —
+// /root/reference/models/step1.py:51-94.  The reference issues ~100 eager ATen kernels for the
+// same graph; here every max-pool is an extra epilogue output of the producing
+// NConv kernel, every nearest-upsample + concat is a load-side index map of the consuming one,
+// the threshold is the prologue of nconv1 and nconv6 -> nconv7 -> crop is a single kernel.
+#include "common.cuh"
+#include "nconv_b200.h"
+
+namespace {
+
+struct Level { int H, W; };
+
+struct DnetPlan {
+  Level l[4];
+  size_t off[32];
+  size_t total_floats;
+};
+
+// Buffer ids (each holds [n,8,H_l,W_l] floats)
+enum {
+  X1A, C1A, X1, C1, X1P, C1P, X2, C2, X2P, C2P, X3, C3, X3P, C3P, X4, C4, X34, C34, X23, C23, NBUF
+};
+static const int kBufLevel[NBUF] = {0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 2, 2, 1, 1};
+
+static DnetPlan make_plan(int n, int H, int W) {
+  DnetPlan p;
+  p.l[0] = {H, W};
+  for (int i = 1; i < 4; ++i) p.l[i] = {p.l[i - 1].H / 2, p.l[i - 1].W / 2};
+  size_t cur = 0;
+  for (int i = 0; i < NBUF; ++i) {
+    p.off[i] = cur;
+    size_t fl = (size_t)n * 8 * p.l[kBufLevel[i]].H * p.l[kBufLevel[i]].W;
+    cur += (fl + 63) & ~(size_t)63;  // keep every buffer 256-byte aligned
+  }
+  p.total_floats = cur;
+  return p;
+}
+
+}  // namespace
+
+extern "C" size_t nconv_b200_dnet_workspace_bytes(int B, int H, int W) {
+  if (B <= 0 || H < 8 || W < 8) return 0;
+  return make_plan(B, H, W).total_floats * sizeof(float);
+}
+
+extern "C" int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out,
+                                       int B, int H, int W, void* workspace, size_t workspace_bytes,
+                                       void* stream) {
+  if (!S || !params || !out || !workspace || B <= 0) return NCONV_ERR_BAD_ARG;
+  if (H < 8 || W < 8) return NCONV_ERR_BAD_ARG;  // three 2x2 pools must leave >= 1 pixel
+  for (int i = 0; i < 18; ++i)
+    if (!params[i]) return NCONV_ERR_BAD_ARG;
+  DnetPlan p = make_plan(B, H, W);
+  if (workspace_bytes < p.total_floats * sizeof(float)) return NCONV_ERR_WORKSPACE;
+  float* ws = (float*)workspace;
+  auto buf = [&](int id) { return ws + p.off[id]; };
+  const float eps = 1e-7f;  // step1.py:103
+
+  auto base = [&](int layer, int lvl) {
+    nconv_b200_fwd_desc d = {};
+    d.w = params[2 * layer]; d.bias = params[2 * layer + 1];
+    d.B = B; d.CO = 8; d.H = p.l[lvl].H; d.W = p.l[lvl].W;
+    d.a_first = 1; d.eps = eps; d.thr = 0.01f;  // step1.py:53
+    return d;
+  };
+  int rc;
+  {  // nconv1: threshold prologue, 1->8, 5x5 pad 2 (step1.py:53-56)
+    nconv_b200_fwd_desc d = base(0, 0);
+    d.xa = S; d.CA = 1; d.K = 5; d.pad = 2; d.flags = NCONV_B200_F_THRESH;
+    d.y = buf(X1A); d.cout = buf(C1A);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv2 + pools (step1.py:57-64)
+    nconv_b200_fwd_desc d = base(1, 0);
+    d.xa = buf(X1A); d.ca = buf(C1A); d.CA = 8; d.K = 5; d.pad = 2; d.flags = NCONV_B200_F_POOL;
+    d.y = buf(X1); d.cout = buf(C1); d.y_pool = buf(X1P); d.c_pool = buf(C1P);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv_down1 + pools (step1.py:65-69)
+    nconv_b200_fwd_desc d = base(2, 1);
+    d.xa = buf(X1P); d.ca = buf(C1P); d.CA = 8; d.K = 5; d.pad = 2; d.flags = NCONV_B200_F_POOL;
+    d.y = buf(X2); d.cout = buf(C2); d.y_pool = buf(X2P); d.c_pool = buf(C2P);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv_down2 + pools (step1.py:70-74)
+    nconv_b200_fwd_desc d = base(3, 2);
+    d.xa = buf(X2P); d.ca = buf(C2P); d.CA = 8; d.K = 5; d.pad = 2; d.flags = NCONV_B200_F_POOL;
+    d.y = buf(X3); d.cout = buf(C3); d.y_pool = buf(X3P); d.c_pool = buf(C3P);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv_down3 (step1.py:75)
+    nconv_b200_fwd_desc d = base(4, 3);
+    d.xa = buf(X3P); d.ca = buf(C3P); d.CA = 8; d.K = 5; d.pad = 2; d.flags = 0;
+    d.y = buf(X4); d.cout = buf(C4);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv4 on cat(skip x3, up(x4)) (step1.py:78-80)
+    nconv_b200_fwd_desc d = base(5, 2);
+    d.xa = buf(X3); d.ca = buf(C3); d.CA = 8; d.xb = buf(X4); d.cb = buf(C4); d.CB = 8;
+    d.HB = p.l[3].H; d.WB = p.l[3].W; d.K = 3; d.pad = 1; d.a_first = 1;
+    d.y = buf(X34); d.cout = buf(C34);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv5 on cat(skip x2, up(x34)) (step1.py:83-85)
+    nconv_b200_fwd_desc d = base(6, 1);
+    d.xa = buf(X2); d.ca = buf(C2); d.CA = 8; d.xb = buf(X34); d.cb = buf(C34); d.CB = 8;
+    d.HB = p.l[2].H; d.WB = p.l[2].W; d.K = 3; d.pad = 1; d.a_first = 1;
+    d.y = buf(X23); d.cout = buf(C23);
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  {  // nconv6 on cat(up(x23), skip x1) -> nconv7 -> crop (step1.py:88-94)
+    nconv_b200_fwd_desc d = base(7, 0);
+    d.xa = buf(X1); d.ca = buf(C1); d.CA = 8; d.xb = buf(X23); d.cb = buf(C23); d.CB = 8;
+    d.HB = p.l[1].H; d.WB = p.l[1].W; d.K = 3; d.pad = 0; d.a_first = 0;
+    d.flags = NCONV_B200_F_TAIL;
+    d.w_tail = params[16]; d.b_tail = params[17]; d.out_tail = out;
+    if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
+  }
+  return 0;
+}

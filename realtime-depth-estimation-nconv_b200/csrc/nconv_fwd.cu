@@ -1,0 +1,135 @@
+// NConv2d forward launchers (C ABI) — /root/reference/models/step1.py:116-149 and the fused
+// DNET stages (step1.py:51-94).  The kernel itself is nconv_tiled.cuh.
+#include "nconv_tiled.cuh"
+
+namespace nconv {
+
+// ---- generic fallback: any Ci/Co/kh/kw/pad, one thread per output pixel and output channel.
+// Same arithmetic, no tiling; used for shapes without a tiled instantiation.
+__global__ void nconv_fwd_generic(const float* __restrict__ x, const float* __restrict__ c,
+                                  const float* __restrict__ w, const float* __restrict__ bias,
+                                  float* __restrict__ y, float* __restrict__ cout, int B, int Ci,
+                                  int Co, int H, int W, int kh, int kw, int ph, int pw, int HO,
+                                  int WO, float eps) {
+  long long total = (long long)B * Co * HO * WO;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    int ox = (int)(idx % WO);
+    long long r = idx / WO;
+    int oy = (int)(r % HO); r /= HO;
+    int o = (int)(r % Co);
+    int b = (int)(r / Co);
+    float N = 0.f, D = 0.f, s = 0.f;
+    for (int i = 0; i < Ci; ++i)
+      for (int u = 0; u < kh; ++u) {
+        int gy = oy - ph + u;
+        for (int v = 0; v < kw; ++v) {
+          float wv = __ldg(&w[((o * Ci + i) * kh + u) * kw + v]);
+          s += wv;
+          int gx = ox - pw + v;
+          if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+            size_t off = (((size_t)b * Ci + i) * H + gy) * W + gx;
+            float cv = __ldg(&c[off]);
+            N = fmaf(wv, __ldg(&x[off]) * cv, N);
+            D = fmaf(wv, cv, D);
+          }
+        }
+      }
+    y[idx] = N / (D + eps) + __ldg(&bias[o]);
+    cout[idx] = D / s;
+  }
+}
+
+}  // namespace nconv
+
+using namespace nconv;
+
+#define NCONV_CASE(ca_, cb_, co_, cot_, k_, pad_, fl_)                                  \
+  if (d->CA == ca_ && d->CB == cb_ && d->CO == co_ && d->K == k_ && d->pad == pad_ &&  \
+      d->flags == fl_)                                                                  \
+    return launch_tiled<ca_, cb_, co_, cot_, k_, pad_, fl_>(a, st);
+
+extern "C" int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* stream) {
+  if (!d || !d->xa || !d->w || !d->bias) return NCONV_ERR_BAD_ARG;
+  if (d->B <= 0 || d->H <= 0 || d->W <= 0 || d->CA <= 0 || d->CO <= 0 || d->K <= 0 || d->pad < 0)
+    return NCONV_ERR_BAD_ARG;
+  const bool thresh = d->flags & NCONV_B200_F_THRESH, pool = d->flags & NCONV_B200_F_POOL,
+             tail = d->flags & NCONV_B200_F_TAIL;
+  if (!thresh && !d->ca) return NCONV_ERR_BAD_ARG;
+  if (d->CB > 0 && (!d->xb || !d->cb || d->HB <= 0 || d->WB <= 0)) return NCONV_ERR_BAD_ARG;
+  if (tail && (!d->w_tail || !d->b_tail || !d->out_tail)) return NCONV_ERR_BAD_ARG;
+  if (!tail && (!d->y || !d->cout)) return NCONV_ERR_BAD_ARG;
+  if (pool && (!d->y_pool || !d->c_pool)) return NCONV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  TiledArgs a = {};
+  a.xa = d->xa; a.ca = d->ca; a.xb = d->xb; a.cb = d->cb; a.w = d->w; a.bias = d->bias;
+  a.y = d->y; a.co = d->cout; a.yp = d->y_pool; a.cp = d->c_pool;
+  a.w7 = d->w_tail; a.b7 = d->b_tail; a.out = d->out_tail;
+  a.B = d->B; a.H = d->H; a.W = d->W; a.HB = d->HB; a.WB = d->WB;
+  a.HO = d->H + 2 * d->pad - d->K + 1; a.WO = d->W + 2 * d->pad - d->K + 1;
+  if (tail) { a.HO = d->H; a.WO = d->W; }
+  if (a.HO <= 0 || a.WO <= 0) return NCONV_ERR_BAD_ARG;
+  a.HP = a.HO / 2; a.WP = a.WO / 2;
+  a.a_first = d->a_first; a.eps = d->eps; a.thr = d->thr;
+  a.map_h = NearestMap::make(d->CB > 0 ? d->HB : d->H, d->H);
+  a.map_w = NearestMap::make(d->CB > 0 ? d->WB : d->W, d->W);
+  a.vec_ok = (d->W % 4 == 0) && (a.WO % 4 == 0) && aligned16(d->xa) &&
+             (thresh || aligned16(d->ca)) &&
+             (tail ? aligned16(d->out_tail) : (aligned16(d->y) && aligned16(d->cout)));
+
+  // The nconv6+nconv7 tail evaluates the valid 3x3 "centred", i.e. with pad-1 geometry.
+  if (tail) {
+    if (!(d->K == 3 && d->pad == 0)) return NCONV_ERR_UNSUPPORTED;
+    if (d->CA == 8 && d->CB == 8 && d->CO == 8)
+      return launch_tiled<8, 8, 8, 8, 3, 1, NCONV_B200_F_TAIL>(a, st);
+    return NCONV_ERR_UNSUPPORTED;
+  }
+  // DNET shapes (step1.py:38-49)
+  NCONV_CASE(1, 0, 8, 8, 5, 2, NCONV_B200_F_THRESH)
+  NCONV_CASE(1, 0, 8, 8, 5, 2, 0)
+  NCONV_CASE(8, 0, 8, 8, 5, 2, NCONV_B200_F_POOL)
+  NCONV_CASE(8, 0, 8, 8, 5, 2, 0)
+  NCONV_CASE(8, 8, 8, 8, 3, 1, 0)
+  NCONV_CASE(8, 8, 8, 8, 3, 0, 0)
+  NCONV_CASE(16, 0, 8, 8, 3, 1, 0)
+  NCONV_CASE(16, 0, 8, 8, 3, 0, 0)
+  NCONV_CASE(8, 0, 1, 1, 1, 2, 0)
+  NCONV_CASE(8, 0, 1, 1, 1, 0, 0)
+  // BASELINE.json config 2 microbench sweep
+  NCONV_CASE(1, 0, 2, 2, 3, 1, 0)
+  NCONV_CASE(2, 0, 2, 2, 3, 1, 0)
+  NCONV_CASE(4, 0, 4, 4, 3, 1, 0)
+  NCONV_CASE(16, 0, 16, 8, 3, 1, 0)
+  NCONV_CASE(1, 0, 2, 2, 5, 2, 0)
+  NCONV_CASE(2, 0, 2, 2, 5, 2, 0)
+  NCONV_CASE(4, 0, 4, 4, 5, 2, 0)
+  NCONV_CASE(16, 0, 16, 8, 5, 2, 0)
+  return NCONV_ERR_UNSUPPORTED;
+}
+
+extern "C" int nconv_b200_nconv2d_fwd(const float* x, const float* c, const float* w,
+                                      const float* bias, float* y, float* cout, int B, int Ci,
+                                      int Co, int H, int W, int kh, int kw, int ph, int pw,
+                                      float eps, void* stream) {
+  if (!x || !c || !w || !bias || !y || !cout) return NCONV_ERR_BAD_ARG;
+  if (B <= 0 || Ci <= 0 || Co <= 0 || H <= 0 || W <= 0 || kh <= 0 || kw <= 0 || ph < 0 || pw < 0)
+    return NCONV_ERR_BAD_ARG;
+  int HO = H + 2 * ph - kh + 1, WO = W + 2 * pw - kw + 1;
+  if (HO <= 0 || WO <= 0) return NCONV_ERR_BAD_ARG;
+  if (kh == kw && ph == pw) {
+    nconv_b200_fwd_desc d = {};
+    d.xa = x; d.ca = c; d.w = w; d.bias = bias; d.y = y; d.cout = cout;
+    d.B = B; d.CA = Ci; d.CB = 0; d.CO = Co; d.H = H; d.W = W; d.K = kh; d.pad = ph;
+    d.a_first = 1; d.flags = 0; d.eps = eps; d.thr = 0.f;
+    int rc = nconv_b200_nconv2d_fwd_fused(&d, stream);
+    if (rc != NCONV_ERR_UNSUPPORTED) return rc;
+  }
+  long long total = (long long)B * Co * HO * WO;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  nconv_fwd_generic<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, c, w, bias, y, cout, B, Ci, Co, H,
+                                                             W, kh, kw, ph, pw, HO, WO, eps);
+  count_launch();
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,290 @@
+"""Drop-in for the reference's `models/step2.py`: the RGB-guided refinement stack on top of
+SETP1_NCONV, same class names / constructor signatures / attribute (= state_dict) names /
+construction order (RNG-identical init), with every convolution, transposed convolution,
+BatchNorm fold, bilinear resize, concat, residual add and border fill executed by the
+sm_100a kernels behind `torch.ops.nconv_b200.*`.
+
+Reference: /root/reference/models/step2.py
+  SETP2_BP_TRAIN :22-77   SETP2_BP_EXPORT :80-126   Conv1x1 :130   RGBEncoder :134-154
+  Conv3x3 :156   UpCat :160-176   Basic2d :178-195   Basic2dTrans :197-214
+  NewFusionBlock :216-236   FusionResolutionBlock :238-259   FusionResolution0 :262-278
+  ConvBlock :290-297
+The dead classes of that file (ConvBlockBN, UpsampleBlock, FusionBlock, Fusion0, the duplicate
+EnforcePos/GenKernel) are never instantiated by the reference and are not reproduced.
+
+Generalisations (identical to the reference for its batch-1-per-stream use):
+outputs are split `[:B]/[B:]` instead of `[0:1]/[1:2]`.
+
+Scope note: the CUDA path implements inference semantics (BatchNorm with running statistics).
+Training-mode BatchNorm + conv backward for this stack is the next row; calling
+forward with BN modules in training mode raises instead of silently falling back.
+"""
+from __future__ import annotations
+
+import math
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+
+from nconv_b200 import ops as _ops  # noqa: F401
+from models.step1 import SETP1_NCONV
+
+_K = torch.ops.nconv_b200
+
+
+def _fold(bn: nn.BatchNorm2d, conv_bias):
+    if bn.training:
+        raise NotImplementedError(
+            "SETP2 CUDA path: BatchNorm in training mode (batch statistics) is not implemented yet; "
+            "call .eval() (there is no PyTorch fallback on purpose)")
+    return _K.bn_fold(bn.weight, bn.bias, bn.running_mean, bn.running_var, conv_bias, float(bn.eps))
+
+
+def _interp_size(n: int, factor) -> int:
+    # F.interpolate(scale_factor=1/f): output = floor(n * (1/f))  (step2.py:252,271)
+    return int(math.floor(float(n) * (1 / factor)))
+
+
+class SETP2_BP_TRAIN(nn.Module):
+    """step2.py:22-77."""
+
+    def __init__(self, step1_checkpoint_name):
+        super().__init__()
+        self.step1 = SETP1_NCONV()
+        checkpoint = torch.load("./checkpoints/{}.pth.tar".format(step1_checkpoint_name))
+        state_dict = checkpoint["state_dict"]
+        stripped = {(k[7:] if k.startswith("module.") else k): v for k, v in state_dict.items()}
+        self.step1.load_state_dict(stripped, strict=False)
+        for p in self.step1.parameters():
+            p.requires_grad = False
+        # The reference constructs five encoders and then overwrites four of them
+        # (step2.py:42-51); the RNG stream and the leftover `rgb_encoder4` are part of the contract.
+        self.rgb_encoder0 = RGBEncoder(3, 32, 1)
+        self.rgb_encoder1 = RGBEncoder(32, 32, 2)
+        self.rgb_encoder2 = RGBEncoder(32, 64, 2)
+        self.rgb_encoder3 = RGBEncoder(64, 64, 2)
+        self.rgb_encoder4 = RGBEncoder(64, 64, 2)
+        self.rgb_encoder0 = RGBEncoder(3, 32, 1)
+        self.rgb_encoder1 = RGBEncoder(32, 64, 2)
+        self.rgb_encoder2 = RGBEncoder(64, 64, 2)
+        self.rgb_encoder3 = RGBEncoder(64, 64, 2)
+        self.fuse0 = FusionResolution0(64, 8)
+        self.fuse1 = FusionResolutionBlock(64, 64, 4)
+        self.fuse2 = FusionResolutionBlock(64, 32, 2)
+        self.fuse3 = FusionResolutionBlock(32, 32, 1)
+
+    def forward(self, rgb0, depth0, rgb1, depth1):
+        depths, B = _setp2_trunk(self, rgb0, depth0, rgb1, depth1)
+        return [d[:B] for d in depths], [d[B:] for d in depths]
+
+
+class SETP2_BP_EXPORT(nn.Module):
+    """step2.py:80-126."""
+
+    def __init__(self):
+        super().__init__()
+        self.step1 = SETP1_NCONV()
+        self.rgb_encoder0 = RGBEncoder(3, 32, 1)
+        self.rgb_encoder1 = RGBEncoder(32, 64, 2)
+        self.rgb_encoder2 = RGBEncoder(64, 64, 2)
+        self.rgb_encoder3 = RGBEncoder(64, 64, 2)
+        self.fuse0 = FusionResolution0(64, 8)
+        self.fuse1 = FusionResolutionBlock(64, 64, 4)
+        self.fuse2 = FusionResolutionBlock(64, 32, 2)
+        self.fuse3 = FusionResolutionBlock(32, 32, 1)
+
+    def forward(self, rgb0, depth0, rgb1, depth1):
+        depths, B = _setp2_trunk(self, rgb0, depth0, rgb1, depth1)
+        out = depths[3]
+        _K.zero_border_(out, 45, 45, 20)          # step2.py:122-124
+        return out[:B], out[B:]
+
+
+def _setp2_trunk(m, rgb0, depth0, rgb1, depth1):
+    """Shared body of step2.py:60-75 / :105-120."""
+    B = rgb0.shape[0]
+    sparse = m.step1(depth0, depth1)
+    rgb = torch.cat((rgb0, rgb1), dim=0)
+    r0 = m.rgb_encoder0(rgb)
+    r1 = m.rgb_encoder1(r0)      # 1/2
+    r2 = m.rgb_encoder2(r1)      # 1/4
+    r3 = m.rgb_encoder3(r2)      # 1/8
+    f0, d0 = m.fuse0(r3, sparse)
+    f1, d1 = m.fuse1(r2, sparse, f0, d0)
+    f2, d2 = m.fuse2(r1, sparse, f1, d1)
+    f3, d3 = m.fuse3(r0, sparse, f2, d2)
+    return [d0, d1, d2, d3], B
+
+
+def Conv1x1(in_planes, out_planes, stride, bias=False, groups=1, dilation=1, padding_mode='zeros'):
+    """step2.py:130 (parameter container; the arithmetic runs in RGBEncoder.forward)."""
+    return nn.Conv2d(in_planes, out_planes, kernel_size=1, stride=stride, bias=bias)
+
+
+def Conv3x3(in_planes, stride=1, groups=1, dilation=1, padding_mode='zeros', bias=False):
+    """step2.py:156: C -> 1 depth-residual head."""
+    return nn.Conv2d(in_planes, 1, kernel_size=3, stride=stride, padding=dilation,
+                     padding_mode=padding_mode, groups=groups, bias=bias, dilation=dilation)
+
+
+class RGBEncoder(nn.Module):
+    """step2.py:134-154: ReLU(BN(conv3x3_s(x)+b)) + conv1x1_s(x)."""
+
+    def __init__(self, in_channel, out_channel, stride):
+        super().__init__()
+        self.stride = stride
+        self.encoder = nn.Sequential(
+            nn.Conv2d(in_channels=in_channel, out_channels=out_channel, kernel_size=3, stride=self.stride, padding=1),
+            nn.BatchNorm2d(out_channel),
+            nn.ReLU(inplace=True))
+        self.downsample = nn.Sequential(Conv1x1(in_channel, out_channel, self.stride))
+
+    def forward(self, x):
+        conv, bn = self.encoder[0], self.encoder[1]
+        scale, shift = _fold(bn, conv.bias)
+        t = _K.conv2d(x, None, conv.weight, scale, shift, None, self.stride, True)
+        return _K.conv2d(x, None, self.downsample[0].weight, None, None, t, self.stride, False)
+
+
+class Basic2d(nn.Module):
+    """step2.py:178-195: conv3x3 (+BN) + act.  Only the norm_layer=BatchNorm2d, act=ReLU use of
+    UpCat exists in the reference."""
+
+    def __init__(self, in_channels, out_channels, norm_layer=None, kernel_size=3, padding=1,
+                 padding_mode='zeros', act=nn.ReLU, stride=1):
+        super().__init__()
+        conv = nn.Conv2d(in_channels=in_channels, out_channels=out_channels, kernel_size=kernel_size,
+                         stride=stride, padding=padding, bias=not norm_layer, padding_mode=padding_mode)
+        self.conv = nn.Sequential(OrderedDict([('conv', conv)]))
+        if norm_layer:
+            self.conv.add_module('bn', norm_layer(out_channels))
+        self.conv.add_module('relu', act())
+        self._relu = act is nn.ReLU
+        if not (act is nn.ReLU or act is nn.Identity):
+            raise NotImplementedError("Basic2d: only ReLU / Identity activations")
+
+    def forward(self, x, x2=None):
+        conv = self.conv.conv
+        if hasattr(self.conv, 'bn'):
+            scale, shift = _fold(self.conv.bn, conv.bias)
+        else:
+            scale, shift = None, conv.bias
+        return _K.conv2d(x, x2, conv.weight, scale, shift, None, int(conv.stride[0]), self._relu)
+
+
+class Basic2dTrans(nn.Module):
+    """step2.py:197-214: ConvTranspose2d(4,2,1) + BN + ReLU."""
+
+    def __init__(self, in_channels, out_channels, norm_layer=None, act=nn.ReLU):
+        super().__init__()
+        if norm_layer is None:
+            bias = True
+            norm_layer = nn.Identity
+        else:
+            bias = False
+        self.conv = nn.ConvTranspose2d(in_channels=in_channels, out_channels=out_channels, kernel_size=4,
+                                       stride=2, padding=1, bias=bias)
+        self.bn = norm_layer(out_channels)
+        self.relu = act()
+        if act is not nn.ReLU:
+            raise NotImplementedError("Basic2dTrans: only ReLU")
+
+    def forward(self, x, x2=None):
+        if isinstance(self.bn, nn.BatchNorm2d):
+            scale, shift = _fold(self.bn, self.conv.bias)
+        else:
+            scale, shift = None, self.conv.bias
+        return _K.convT4x4s2(x, x2, self.conv.weight, scale, shift, True)
+
+
+class UpCat(nn.Module):
+    """step2.py:160-176.  forward(y, x, d): upf(cat[x, d]) then conv(cat[., y]); both concats are
+    two-source loads inside the kernels, never materialised."""
+
+    def __init__(self, in_channels, out_channels, norm_layer=nn.BatchNorm2d, kernel_size=3, padding=1,
+                 padding_mode='zeros', act=nn.ReLU):
+        super().__init__()
+        self.upf = Basic2dTrans(in_channels + 1, out_channels, norm_layer=norm_layer, act=act)
+        self.conv = Basic2d(out_channels * 2, out_channels, norm_layer=norm_layer, kernel_size=kernel_size,
+                            padding=padding, padding_mode=padding_mode, act=act)
+
+    def forward(self, y, x, d):
+        fout = self.upf(x, d)
+        return self.conv(fout, y)
+
+
+class ConvBlock(nn.Module):
+    """step2.py:290-297: ReLU(conv3x3 p1 + bias)."""
+
+    def __init__(self, in_channels, out_channels, kernel_size=3, stride=1, padding=1):
+        super().__init__()
+        self.conv = nn.Conv2d(in_channels, out_channels, kernel_size, stride, padding)
+        self.relu = nn.ReLU()
+
+    def forward(self, x, x2=None):
+        return _K.conv2d(x, x2, self.conv.weight, None, self.conv.bias, None, int(self.conv.stride[0]), True)
+
+
+class NewFusionBlock(nn.Module):
+    """step2.py:216-236."""
+
+    def __init__(self, rgb_channels, out_channels):
+        super().__init__()
+        self.rgb_conv = ConvBlock(rgb_channels, rgb_channels)
+        self.depth_conv = ConvBlock(1, rgb_channels)
+        self.fuse_conv1 = ConvBlock(rgb_channels * 2, rgb_channels)
+        self.fuse_conv2 = ConvBlock(rgb_channels, out_channels)
+        self.fuse_conv3 = ConvBlock(out_channels, out_channels)
+
+    def forward(self, rgb, depth):
+        rgb_feat = self.rgb_conv(rgb)
+        depth_feat = self.depth_conv(depth)
+        fused = self.fuse_conv1(rgb_feat, depth_feat)      # cat((rgb_feat, depth_feat), 1)
+        fused = self.fuse_conv2(fused)
+        return self.fuse_conv3(fused)
+
+
+class FusionResolutionBlock(nn.Module):
+    """step2.py:238-259.  Called as block(rgb, sparse, prev_features, prev_depth) (:72-74); the
+    reference's parameter names are swapped relative to that order but the data flow is
+    upcat(rgb, prev_depth, prev_features) -> cat[prev_depth(1), prev_features(C)]."""
+
+    def __init__(self, in_channel, out_channel, downsample_factor):
+        super().__init__()
+        self.upcat = UpCat(in_channel, in_channel)
+        self.fuse = NewFusionBlock(in_channel, out_channel)
+        self.conv = Conv3x3(out_channel, 1)
+        self.downsample_factor = downsample_factor
+
+    def forward(self, rgb, depth, depth_last_step, fusion_festure):
+        fout = self.upcat(rgb, fusion_festure, depth_last_step)
+        depth = _resize(depth, self.downsample_factor)
+        fout = self.fuse(fout, depth)
+        dout = _K.conv2d(fout, None, self.conv.weight, None, None, depth, 1, False)   # depth + res
+        return fout, dout
+
+
+class FusionResolution0(nn.Module):
+    """step2.py:262-278."""
+
+    def __init__(self, in_channel, downsample_factor):
+        super().__init__()
+        self.fuse = NewFusionBlock(in_channel, in_channel)
+        self.conv = Conv3x3(in_channel, 1)
+        self.downsample_factor = downsample_factor
+
+    def forward(self, rgb, depth):
+        depth = _resize(depth, self.downsample_factor)
+        fout = self.fuse(rgb, depth)
+        dout = _K.conv2d(fout, None, self.conv.weight, None, None, depth, 1, False)
+        return fout, dout
+
+
+def _resize(depth, factor):
+    """F.interpolate(depth, scale_factor=1/factor, mode='bilinear', align_corners=True)."""
+    H, W = depth.shape[2:]
+    HO, WO = _interp_size(H, factor), _interp_size(W, factor)
+    if (HO, WO) == (H, W):
+        return depth       # align-corners bilinear to the same size is the identity
+    return _K.bilinear_ac(depth, HO, WO)

@@ -1,0 +1,97 @@
+"""ctypes binding of `csrc/libnconv_b200.so` (the C ABI declared in include/nconv_b200.h).
+
+There is no fallback: if the library is missing this module raises, and every op in
+`nconv_b200.ops` is CUDA-only.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_longlong, c_size_t, c_ulonglong, c_void_p
+
+PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(PKG_ROOT, "csrc", "libnconv_b200.so")
+
+F_THRESH, F_POOL, F_TAIL = 1, 2, 4
+
+
+class FwdDesc(Structure):
+    """nconv_b200_fwd_desc"""
+    _fields_ = [
+        ("xa", c_void_p), ("ca", c_void_p), ("xb", c_void_p), ("cb", c_void_p),
+        ("w", c_void_p), ("bias", c_void_p),
+        ("y", c_void_p), ("cout", c_void_p), ("y_pool", c_void_p), ("c_pool", c_void_p),
+        ("w_tail", c_void_p), ("b_tail", c_void_p), ("out_tail", c_void_p),
+        ("B", c_int), ("CA", c_int), ("CB", c_int), ("CO", c_int), ("H", c_int), ("W", c_int),
+        ("HB", c_int), ("WB", c_int), ("K", c_int), ("pad", c_int),
+        ("a_first", c_int), ("flags", c_int), ("eps", c_float), ("thr", c_float),
+    ]
+
+
+class ConvDesc(Structure):
+    """nconv_b200_conv_desc"""
+    _fields_ = [
+        ("a", c_void_p), ("b", c_void_p), ("w", c_void_p), ("scale", c_void_p),
+        ("shift", c_void_p), ("residual", c_void_p), ("y", c_void_p),
+        ("B", c_int), ("CA", c_int), ("CB", c_int), ("CO", c_int), ("H", c_int), ("W", c_int),
+        ("K", c_int), ("stride", c_int), ("relu", c_int),
+    ]
+
+
+# name -> (restype, argtypes); must list every symbol include/nconv_b200.h declares
+SIGNATURES = {
+    "nconv_b200_abi_version": (c_int, []),
+    "nconv_b200_error_string": (c_char_p, [c_int]),
+    "nconv_b200_launch_count": (c_ulonglong, []),
+    "nconv_b200_nconv2d_fwd": (c_int, [c_void_p] * 6 + [c_int] * 9 + [c_float, c_void_p]),
+    "nconv_b200_nconv2d_fwd_fused": (c_int, [POINTER(FwdDesc), c_void_p]),
+    "nconv_b200_nconv2d_bwd_workspace_bytes": (c_size_t, [c_int] * 9),
+    "nconv_b200_nconv2d_bwd": (c_int, [c_void_p] * 12 + [c_int] * 9 + [c_float, c_void_p, c_size_t, c_void_p]),
+    "nconv_b200_enforce_pos": (c_int, [c_void_p, c_longlong, c_int, c_int, c_void_p]),
+    "nconv_b200_confidence_mask": (c_int, [c_void_p, c_void_p, c_longlong, c_float, c_void_p]),
+    "nconv_b200_maxpool2x2_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "nconv_b200_maxpool2x2_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "nconv_b200_upcat_fwd": (c_int, [c_void_p] * 3 + [c_int] * 8 + [c_void_p]),
+    "nconv_b200_upcat_bwd": (c_int, [c_void_p] * 3 + [c_int] * 8 + [c_void_p]),
+    "nconv_b200_dnet_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "nconv_b200_dnet_forward": (c_int, [c_void_p, POINTER(c_void_p), c_void_p, c_int, c_int, c_int,
+                                        c_void_p, c_size_t, c_void_p]),
+    "nconv_b200_conv2d_fwd": (c_int, [POINTER(ConvDesc), c_void_p]),
+    "nconv_b200_convT4x4s2_fwd": (c_int, [c_void_p] * 6 + [c_int] * 7 + [c_void_p]),
+    "nconv_b200_bilinear_ac_fwd": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p]),
+    "nconv_b200_zero_border": (c_int, [c_void_p] + [c_int] * 6 + [c_void_p]),
+    "nconv_b200_bn_fold": (c_int, [c_void_p] * 7 + [c_int, c_float, c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load the C-ABI library; raise (loudly) if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "nconv_b200: %s not found. Build it with `python __graft_entry__.py build` "
+            "(nvcc, sm_100a). There is no CPU or PyTorch fallback for this path." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so is stale
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def error_string(code: int) -> str:
+    return load().nconv_b200_error_string(code).decode()
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        raise RuntimeError("%s failed: [%d] %s" % (what, code, error_string(code)))
+
+
+def launch_count() -> int:
+    return int(load().nconv_b200_launch_count())

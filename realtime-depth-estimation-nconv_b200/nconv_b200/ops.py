@@ -1,0 +1,386 @@
+"""torch.library registration of the nconv_b200 C-ABI launchers.
+
+Every op is CUDA-only (there is deliberately no CPU implementation — BASELINE.json north_star:
+"no CPU fallback"); PyTorch supplies device memory, the current stream and autograd plumbing.
+Schemas live in the `nconv_b200` namespace:  torch.ops.nconv_b200.<op>.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import byref, c_void_p
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import ConvDesc, FwdDesc, check
+
+_C = _lib.load()
+
+_LIB = torch.library.Library("nconv_b200", "DEF")
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else c_void_p(t.data_ptr())
+
+
+def _stream(t: torch.Tensor):
+    return c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _prep(t: torch.Tensor, name: str) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        raise TypeError("nconv_b200: %s must be float32, got %s" % (name, t.dtype))
+    if not t.is_cuda:
+        raise RuntimeError("nconv_b200: %s must be a CUDA tensor (no CPU path exists)" % name)
+    return t.contiguous()
+
+
+def _prep_opt(t, name):
+    return None if t is None else _prep(t, name)
+
+
+def _define(schema: str, impl, fake=None):
+    name = schema.split("(")[0]
+    _LIB.define(schema)
+    _LIB.impl(name, impl, "CUDA")
+    if fake is not None:
+        torch.library.register_fake("nconv_b200::" + name, fake)
+
+
+# --------------------------------------------------------------------------------------
+# NConv2d forward / backward
+# --------------------------------------------------------------------------------------
+def _out_hw(H, W, kh, kw, ph, pw):
+    return H + 2 * ph - kh + 1, W + 2 * pw - kw + 1
+
+
+def _nconv2d(x, c, weight, bias, ph: int, pw: int, eps: float):
+    x = _prep(x, "data"); c = _prep(c, "conf"); weight = _prep(weight, "weight"); bias = _prep(bias, "bias")
+    if x.dim() != 4 or x.shape != c.shape:
+        raise ValueError("nconv2d: data and conf must be [B,C,H,W] of the same shape")
+    B, Ci, H, W = x.shape
+    Co, Ciw, kh, kw = weight.shape
+    if Ciw != Ci or bias.numel() != Co:
+        raise ValueError("nconv2d: weight/bias shape mismatch")
+    HO, WO = _out_hw(H, W, kh, kw, ph, pw)
+    if HO <= 0 or WO <= 0:
+        raise ValueError("nconv2d: empty output")
+    y = torch.empty((B, Co, HO, WO), device=x.device, dtype=torch.float32)
+    co = torch.empty_like(y)
+    if B == 0:
+        return y, co
+    with torch.cuda.device(x.device):
+        check(_C.nconv_b200_nconv2d_fwd(_p(x), _p(c), _p(weight), _p(bias), _p(y), _p(co), B, Ci, Co, H, W,
+                                        kh, kw, ph, pw, eps, _stream(x)), "nconv2d_fwd")
+    return y, co
+
+
+def _nconv2d_fake(x, c, weight, bias, ph, pw, eps):
+    B, Ci, H, W = x.shape
+    Co, _, kh, kw = weight.shape
+    HO, WO = _out_hw(H, W, kh, kw, ph, pw)
+    return x.new_empty((B, Co, HO, WO)), x.new_empty((B, Co, HO, WO))
+
+
+_define("nconv2d(Tensor data, Tensor conf, Tensor weight, Tensor bias, int ph, int pw, float eps) -> (Tensor, Tensor)",
+        _nconv2d, _nconv2d_fake)
+
+
+def _nconv2d_backward(gy, gco, x, c, weight, bias, y, co, ph: int, pw: int, eps: float,
+                      need_gx: bool, need_gc: bool, need_gw: bool):
+    gy = _prep(gy, "gy"); gco = _prep_opt(gco, "gcout")
+    x = _prep(x, "data"); c = _prep(c, "conf"); weight = _prep(weight, "weight"); bias = _prep(bias, "bias")
+    y = _prep(y, "y"); co = _prep(co, "cout")
+    B, Ci, H, W = x.shape
+    Co, _, kh, kw = weight.shape
+    gx = torch.empty_like(x) if need_gx else None
+    gc = torch.empty_like(x) if need_gc else None
+    gw = torch.empty_like(weight) if need_gw else None
+    gb = torch.empty_like(bias) if need_gw else None
+    if B > 0:
+        nbytes = int(_C.nconv_b200_nconv2d_bwd_workspace_bytes(B, Ci, Co, H, W, kh, kw, ph, pw))
+        ws = torch.empty(nbytes, device=x.device, dtype=torch.uint8)
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_nconv2d_bwd(_p(gy), _p(gco), _p(x), _p(c), _p(weight), _p(bias), _p(y), _p(co),
+                                            _p(gx), _p(gc), _p(gw), _p(gb), B, Ci, Co, H, W, kh, kw, ph, pw,
+                                            eps, _p(ws), nbytes, _stream(x)), "nconv2d_bwd")
+    else:
+        for t in (gx, gc, gw, gb):
+            if t is not None:
+                t.zero_()
+    z = x.new_empty(0)
+    return (gx if gx is not None else z, gc if gc is not None else z,
+            gw if gw is not None else z, gb if gb is not None else z)
+
+
+def _nconv2d_backward_fake(gy, gco, x, c, weight, bias, y, co, ph, pw, eps, need_gx, need_gc, need_gw):
+    z = x.new_empty(0)
+    return (torch.empty_like(x) if need_gx else z, torch.empty_like(x) if need_gc else z,
+            torch.empty_like(weight) if need_gw else z, torch.empty_like(bias) if need_gw else z)
+
+
+_define("nconv2d_backward(Tensor gy, Tensor? gcout, Tensor data, Tensor conf, Tensor weight, Tensor bias, "
+        "Tensor y, Tensor cout, int ph, int pw, float eps, bool need_gx, bool need_gc, bool need_gw) "
+        "-> (Tensor, Tensor, Tensor, Tensor)", _nconv2d_backward, _nconv2d_backward_fake)
+
+
+def _nconv2d_setup(ctx, inputs, output):
+    x, c, weight, bias, ph, pw, eps = inputs
+    y, co = output
+    ctx.save_for_backward(x, c, weight, bias, y, co)
+    ctx.cfg = (ph, pw, eps)
+
+
+def _nconv2d_bwd(ctx, gy, gco):
+    x, c, weight, bias, y, co = ctx.saved_tensors
+    ph, pw, eps = ctx.cfg
+    need_gx, need_gc, need_gw, need_gb = ctx.needs_input_grad[:4]
+    if gy is None:
+        gy = torch.zeros_like(y)
+    gx, gc, gw, gb = torch.ops.nconv_b200.nconv2d_backward(
+        gy, gco, x, c, weight, bias, y, co, ph, pw, eps, need_gx, need_gc, need_gw or need_gb)
+    return (gx if need_gx else None, gc if need_gc else None, gw if need_gw else None,
+            gb if need_gb else None, None, None, None)
+
+
+torch.library.register_autograd("nconv_b200::nconv2d", _nconv2d_bwd, setup_context=_nconv2d_setup)
+
+
+# --------------------------------------------------------------------------------------
+# EnforcePos, threshold, pool, upsample+concat
+# --------------------------------------------------------------------------------------
+POS_MODES = {"softplus": 0, "exp": 1, "sigmoid": 2, "softmax": 3}
+
+
+def _enforce_pos_(w, mode: int, group: int) -> None:
+    if not w.is_cuda or w.dtype != torch.float32 or not w.is_contiguous():
+        raise RuntimeError("enforce_pos_: weight must be a contiguous float32 CUDA tensor")
+    if w.numel():
+        with torch.cuda.device(w.device):
+            check(_C.nconv_b200_enforce_pos(_p(w), w.numel(), mode, group, _stream(w)), "enforce_pos")
+
+
+_define("enforce_pos_(Tensor(a!) w, int mode, int group) -> ()", _enforce_pos_, lambda w, mode, group: None)
+
+
+def _confidence_mask(s, thr: float):
+    s = _prep(s, "S")
+    c = torch.empty_like(s)
+    if s.numel():
+        with torch.cuda.device(s.device):
+            check(_C.nconv_b200_confidence_mask(_p(s), _p(c), s.numel(), thr, _stream(s)), "confidence_mask")
+    return c
+
+
+_define("confidence_mask(Tensor s, float thr) -> Tensor", _confidence_mask, lambda s, thr: torch.empty_like(s))
+
+
+def _maxpool2x2(x):
+    x = _prep(x, "x")
+    B, C, H, W = x.shape
+    y = torch.empty((B, C, H // 2, W // 2), device=x.device, dtype=torch.float32)
+    if y.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_maxpool2x2_fwd(_p(x), _p(y), B * C, H, W, _stream(x)), "maxpool2x2_fwd")
+    return y
+
+
+def _maxpool2x2_backward(gy, x):
+    gy = _prep(gy, "gy"); x = _prep(x, "x")
+    B, C, H, W = x.shape
+    gx = torch.empty_like(x)
+    if x.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_maxpool2x2_bwd(_p(gy), _p(x), _p(gx), B * C, H, W, _stream(x)), "maxpool2x2_bwd")
+    return gx
+
+
+_define("maxpool2x2(Tensor x) -> Tensor", _maxpool2x2,
+        lambda x: x.new_empty((x.shape[0], x.shape[1], x.shape[2] // 2, x.shape[3] // 2)))
+_define("maxpool2x2_backward(Tensor gy, Tensor x) -> Tensor", _maxpool2x2_backward, lambda gy, x: torch.empty_like(x))
+torch.library.register_autograd(
+    "nconv_b200::maxpool2x2",
+    lambda ctx, gy: torch.ops.nconv_b200.maxpool2x2_backward(gy, ctx.saved_tensors[0]),
+    setup_context=lambda ctx, inputs, output: ctx.save_for_backward(inputs[0]))
+
+
+def _upcat(skip, low, skip_first: bool):
+    skip = _prep(skip, "skip"); low = _prep(low, "low")
+    B, Cs, H, W = skip.shape
+    Bl, Cl, HL, WL = low.shape
+    if Bl != B:
+        raise ValueError("upcat: batch mismatch")
+    out = torch.empty((B, Cs + Cl, H, W), device=skip.device, dtype=torch.float32)
+    if out.numel():
+        with torch.cuda.device(skip.device):
+            check(_C.nconv_b200_upcat_fwd(_p(skip), _p(low), _p(out), B, Cs, Cl, H, W, HL, WL, int(skip_first),
+                                          _stream(skip)), "upcat_fwd")
+    return out
+
+
+def _upcat_backward(gout, Cs: int, Cl: int, HL: int, WL: int, skip_first: bool):
+    gout = _prep(gout, "gout")
+    B, C, H, W = gout.shape
+    gskip = torch.empty((B, Cs, H, W), device=gout.device, dtype=torch.float32)
+    glow = torch.empty((B, Cl, HL, WL), device=gout.device, dtype=torch.float32)
+    if gout.numel():
+        with torch.cuda.device(gout.device):
+            check(_C.nconv_b200_upcat_bwd(_p(gout), _p(gskip), _p(glow), B, Cs, Cl, H, W, HL, WL, int(skip_first),
+                                          _stream(gout)), "upcat_bwd")
+    return gskip, glow
+
+
+_define("upcat(Tensor skip, Tensor low, bool skip_first) -> Tensor", _upcat,
+        lambda skip, low, skip_first: skip.new_empty((skip.shape[0], skip.shape[1] + low.shape[1], skip.shape[2], skip.shape[3])))
+_define("upcat_backward(Tensor gout, int Cs, int Cl, int HL, int WL, bool skip_first) -> (Tensor, Tensor)",
+        _upcat_backward,
+        lambda gout, Cs, Cl, HL, WL, skip_first: (gout.new_empty((gout.shape[0], Cs, gout.shape[2], gout.shape[3])),
+                                                  gout.new_empty((gout.shape[0], Cl, HL, WL))))
+
+
+def _upcat_setup(ctx, inputs, output):
+    skip, low, skip_first = inputs
+    ctx.cfg = (skip.shape[1], low.shape[1], low.shape[2], low.shape[3], skip_first)
+
+
+def _upcat_bwd(ctx, gout):
+    gs, gl = torch.ops.nconv_b200.upcat_backward(gout, *ctx.cfg)
+    return gs, gl, None
+
+
+torch.library.register_autograd("nconv_b200::upcat", _upcat_bwd, setup_context=_upcat_setup)
+
+
+# --------------------------------------------------------------------------------------
+# whole DNET forward (inference)
+# --------------------------------------------------------------------------------------
+def _dnet_forward(S, params: Sequence[torch.Tensor]):
+    S = _prep(S, "S")
+    if S.dim() != 4 or S.shape[1] != 1:
+        raise ValueError("dnet_forward: S must be [B,1,H,W]")
+    if len(params) != 18:
+        raise ValueError("dnet_forward: expected 18 parameter tensors (w,b for 9 layers)")
+    params = [_prep(p, "param") for p in params]
+    B, _, H, W = S.shape
+    if H < 8 or W < 8:
+        raise ValueError("dnet_forward: H and W must be >= 8 (three 2x2 pools)")
+    out = torch.empty_like(S)
+    if B == 0:
+        return out
+    nbytes = int(_C.nconv_b200_dnet_workspace_bytes(B, H, W))
+    ws = torch.empty(nbytes, device=S.device, dtype=torch.uint8)
+    arr = (c_void_p * 18)(*[p.data_ptr() for p in params])
+    with torch.cuda.device(S.device):
+        check(_C.nconv_b200_dnet_forward(_p(S), arr, _p(out), B, H, W, _p(ws), nbytes, _stream(S)), "dnet_forward")
+    return out
+
+
+_define("dnet_forward(Tensor S, Tensor[] params) -> Tensor", _dnet_forward, lambda S, params: torch.empty_like(S))
+
+
+# --------------------------------------------------------------------------------------
+# SETP2 building blocks
+# --------------------------------------------------------------------------------------
+def _conv_out(H, K, stride):
+    return (H + 2 * (K // 2) - K) // stride + 1
+
+
+def _conv2d(a, b, weight, scale, shift, residual, stride: int, relu: bool):
+    a = _prep(a, "a"); b = _prep_opt(b, "b"); weight = _prep(weight, "weight")
+    scale = _prep_opt(scale, "scale"); shift = _prep_opt(shift, "shift"); residual = _prep_opt(residual, "residual")
+    B, CA, H, W = a.shape
+    CB = 0 if b is None else b.shape[1]
+    CO, CI, K, K2 = weight.shape
+    if K != K2 or CI != CA + CB:
+        raise ValueError("conv2d: weight shape mismatch")
+    if b is not None and (b.shape[0] != B or b.shape[2:] != a.shape[2:]):
+        raise ValueError("conv2d: second source shape mismatch")
+    HO, WO = _conv_out(H, K, stride), _conv_out(W, K, stride)
+    y = torch.empty((B, CO, HO, WO), device=a.device, dtype=torch.float32)
+    if residual is not None and residual.shape != y.shape:
+        raise ValueError("conv2d: residual shape mismatch")
+    if y.numel():
+        d = ConvDesc(_p(a), _p(b), _p(weight), _p(scale), _p(shift), _p(residual), _p(y),
+                     B, CA, CB, CO, H, W, K, stride, int(relu))
+        with torch.cuda.device(a.device):
+            check(_C.nconv_b200_conv2d_fwd(byref(d), _stream(a)), "conv2d_fwd")
+    return y
+
+
+def _conv2d_fake(a, b, weight, scale, shift, residual, stride, relu):
+    K = weight.shape[2]
+    return a.new_empty((a.shape[0], weight.shape[0], _conv_out(a.shape[2], K, stride), _conv_out(a.shape[3], K, stride)))
+
+
+_define("conv2d(Tensor a, Tensor? b, Tensor weight, Tensor? scale, Tensor? shift, Tensor? residual, "
+        "int stride, bool relu) -> Tensor", _conv2d, _conv2d_fake)
+
+
+def _convT4x4s2(a, b, weight, scale, shift, relu: bool):
+    a = _prep(a, "a"); b = _prep_opt(b, "b"); weight = _prep(weight, "weight")
+    scale = _prep_opt(scale, "scale"); shift = _prep_opt(shift, "shift")
+    B, CA, H, W = a.shape
+    CB = 0 if b is None else b.shape[1]
+    CI, CO, kh, kw = weight.shape
+    if (kh, kw) != (4, 4) or CI != CA + CB:
+        raise ValueError("convT4x4s2: weight must be [CA+CB, CO, 4, 4]")
+    y = torch.empty((B, CO, 2 * H, 2 * W), device=a.device, dtype=torch.float32)
+    if y.numel():
+        with torch.cuda.device(a.device):
+            check(_C.nconv_b200_convT4x4s2_fwd(_p(a), _p(b), _p(weight), _p(scale), _p(shift), _p(y), B, CA, CB,
+                                               CO, H, W, int(relu), _stream(a)), "convT4x4s2_fwd")
+    return y
+
+
+_define("convT4x4s2(Tensor a, Tensor? b, Tensor weight, Tensor? scale, Tensor? shift, bool relu) -> Tensor",
+        _convT4x4s2,
+        lambda a, b, weight, scale, shift, relu: a.new_empty((a.shape[0], weight.shape[1], 2 * a.shape[2], 2 * a.shape[3])))
+
+
+def _bilinear_ac(x, HO: int, WO: int):
+    x = _prep(x, "x")
+    B, C, H, W = x.shape
+    y = torch.empty((B, C, HO, WO), device=x.device, dtype=torch.float32)
+    if y.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_bilinear_ac_fwd(_p(x), _p(y), B * C, H, W, HO, WO, _stream(x)), "bilinear_ac_fwd")
+    return y
+
+
+_define("bilinear_ac(Tensor x, int HO, int WO) -> Tensor", _bilinear_ac,
+        lambda x, HO, WO: x.new_empty((x.shape[0], x.shape[1], HO, WO)))
+
+
+def _zero_border_(x, top: int, bottom: int, left: int) -> None:
+    if not x.is_cuda or x.dtype != torch.float32 or not x.is_contiguous():
+        raise RuntimeError("zero_border_: x must be a contiguous float32 CUDA tensor")
+    B, C, H, W = x.shape
+    if x.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_zero_border(_p(x), B * C, H, W, min(top, H), min(bottom, H), min(left, W),
+                                            _stream(x)), "zero_border")
+
+
+_define("zero_border_(Tensor(a!) x, int top, int bottom, int left) -> ()", _zero_border_,
+        lambda x, top, bottom, left: None)
+
+
+def _bn_fold(gamma, beta, mean, var, conv_bias, eps: float):
+    gamma = _prep(gamma, "gamma"); beta = _prep(beta, "beta"); mean = _prep(mean, "mean"); var = _prep(var, "var")
+    conv_bias = _prep_opt(conv_bias, "conv_bias")
+    scale = torch.empty_like(gamma)
+    shift = torch.empty_like(gamma)
+    with torch.cuda.device(gamma.device):
+        check(_C.nconv_b200_bn_fold(_p(gamma), _p(beta), _p(mean), _p(var), _p(conv_bias), _p(scale), _p(shift),
+                                    gamma.numel(), eps, _stream(gamma)), "bn_fold")
+    return scale, shift
+
+
+_define("bn_fold(Tensor gamma, Tensor beta, Tensor mean, Tensor var, Tensor? conv_bias, float eps) -> (Tensor, Tensor)",
+        _bn_fold, lambda gamma, beta, mean, var, conv_bias, eps: (torch.empty_like(gamma), torch.empty_like(gamma)))
+
+
+def launch_count() -> int:
+    """Kernels enqueued by libnconv_b200.so in this process so far."""
+    return _lib.launch_count()
