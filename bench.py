@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py — SETP1+SETP2 inference frames/s at 480x640 (BASELINE.json metric) on N B200s.
+
+  python bench.py --gpus 1 --steps K --warmup W                 # this repo's CUDA path
+  torchrun ... bench.py --gpus N ...                            # one rank per GPU, batch-sharded
+  python bench.py --impl reference ...                          # the reference algorithm on host cores
+
+A step = one pass of the hot path (SETP1_NCONV + the RGB-guided SETP2 stack, SETP2_BP_EXPORT
+semantics) over one batch of synthetic frames.  Per GPU: 32 frames (16 per stream), i.e.
+BASELINE config 4 at N=1; frames are independent, so ranks process disjoint batches with no
+data-path collective (weak scaling: global batch = 32 x N).
+
+Printed JSON (rank 0, one line): value = frames/s with inputs resident in HBM; e2e = frames/s
+through the public module call with pinned HOST inputs and a HOST result (H2D + D2H inside the
+timed region); roofline = the dominant kernel of the step from per-launch CUDA events recorded
+by the library on the launching stream during the timed steps; cpu_baseline = the CPU oracle
+port (oracle/nconv_oracle.py: the reference's own ATen call sequence) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "realtime-depth-estimation-nconv_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+METRIC = "setp1+setp2_inference_frames_per_s_480x640"
+UNIT = "frames/s"
+H, W = 480, 640
+FRAMES_PER_STREAM = 16          # x2 streams = 32 frames per GPU (BASELINE config 4)
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_tflops": float(d["bf16_tflops"]),
+                "bf16_tflops_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def oracle_model_and_inputs(frames_per_stream: int, seed: int):
+    from oracle import nconv_oracle as O
+    from nconv_b200.synthetic import setp2_inputs
+    sd = O.synthetic_state_dict(5)
+    return O, sd, setp2_inputs(frames_per_stream, seed=seed, H=H, W=W)
+
+
+def time_cpu_oracle(frames_per_stream: int, min_seconds: float, max_reps: int, warmup: int):
+    """The reference's algorithm on the host cores: oracle/nconv_oracle.py issues the same ATen
+    calls as /root/reference/models/step1.py + step2.py (eval mode, EXPORT graph)."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    O, sd, inp = oracle_model_and_inputs(frames_per_stream, seed=7)
+    with torch.no_grad():
+        for _ in range(warmup):
+            O.setp2_forward(sd, *inp, export=True)
+        times = []
+        t_all = time.perf_counter()
+        while len(times) < max_reps and (len(times) < 1 or time.perf_counter() - t_all < min_seconds):
+            t0 = time.perf_counter()
+            O.setp2_forward(sd, *inp, export=True)
+            times.append(time.perf_counter() - t0)
+    return times, 2 * frames_per_stream, torch.get_num_threads()
+
+
+def run_reference(args):
+    """--impl reference: rank 0 alone times the CPU implementation; other ranks exit 0."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    fps_frames = 1                                   # 1 frame per stream = 2 frames per step
+    torch.set_num_threads(os.cpu_count() or 1)
+    O, sd, inp = oracle_model_and_inputs(fps_frames, seed=7)
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            O.setp2_forward(sd, *inp, export=True)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            O.setp2_forward(sd, *inp, export=True)
+        dt = time.perf_counter() - t0
+    frames = 2 * fps_frames * args.steps
+    value = frames / dt
+    sample = "%d steps x 2 frames (1 per stream) of the config-4 workload, torch CPU fp32, %d threads" % (
+        args.steps, torch.get_num_threads())
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(n_gpus: int):
+    return {"workload": "BASELINE config 4: SETP1_NCONV + SETP2 (EXPORT graph, eval) inference, synthetic RGB + "
+                        "500-point sparse depth at 480x640, 32 frames per GPU (16 per stream)",
+            "frames_per_gpu": 2 * FRAMES_PER_STREAM, "global_batch": 2 * FRAMES_PER_STREAM * n_gpus,
+            "height": H, "width": W, "parallelism": "batch-sharded x%d, no collective" % n_gpus,
+            "l2": "inputs (157 MB/step) and activations (>10 GB/step) exceed the 126 MB L2; no explicit flush"}
+
+
+def build_model(dev):
+    from models.step2 import SETP2_BP_EXPORT
+    from oracle import nconv_oracle as O          # weights only: the same tensors the CPU arm uses
+    torch.manual_seed(5)
+    m = SETP2_BP_EXPORT()
+    missing = m.load_state_dict(O.synthetic_state_dict(5), strict=False)
+    assert not missing.unexpected_keys and all("bnorm" in k for k in missing.missing_keys)
+    return m.eval().to(dev)
+
+
+def summarise_kernels(records, steps):
+    by = {}
+    for label, ms, fl, by_ in records:
+        d = by.setdefault(label, {"ms": 0.0, "n": 0, "flops": 0.0, "bytes": 0.0})
+        d["ms"] += ms; d["n"] += 1; d["flops"] += fl; d["bytes"] += by_
+    total = sum(d["ms"] for d in by.values()) or 1.0
+    rows = []
+    for label, d in sorted(by.items(), key=lambda kv: -kv[1]["ms"]):
+        avg_ms = d["ms"] / d["n"]
+        rows.append({"kernel": label, "launches_per_step": d["n"] / steps, "avg_ms": avg_ms,
+                     "share": d["ms"] / total, "flops": d["flops"] / d["n"], "bytes": d["bytes"] / d["n"],
+                     "gbs": d["bytes"] / d["n"] / avg_ms / 1e6 if avg_ms > 0 else 0.0,
+                     "tflops": d["flops"] / d["n"] / avg_ms / 1e9 if avg_ms > 0 else 0.0})
+    return rows
+
+
+def roofline_of(row, peaks, sustained=True):
+    """Bound = whichever of the HBM time and the tensor-pipe time of the launch is longer."""
+    tf_peak = peaks["bf16_tflops_sustained" if sustained else "bf16_tflops"]
+    t_hbm = row["bytes"] / (peaks["hbm_gbs"] * 1e9)
+    t_tc = row["flops"] / (tf_peak * 1e12)
+    if t_hbm >= t_tc:
+        return {"kernel": row["kernel"], "bound": "hbm", "achieved": row["gbs"], "peak": peaks["hbm_gbs"],
+                "unit": "GB/s", "frac": row["gbs"] / peaks["hbm_gbs"], "traffic": None,
+                "peak_source": peaks["source"], "avg_ms": row["avg_ms"], "share_of_step": row["share"]}
+    return {"kernel": row["kernel"], "bound": "tensor", "achieved": row["tflops"], "peak": tf_peak,
+            "unit": "TFLOP/s", "frac": row["tflops"] / tf_peak, "traffic": None,
+            "peak_source": peaks["source"], "avg_ms": row["avg_ms"], "share_of_step": row["share"]}
+
+
+def run_b200(args):
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from nconv_b200 import _lib, ops
+    from nconv_b200.synthetic import setp2_inputs
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    model = build_model(dev)
+    host = [t.pin_memory() for t in setp2_inputs(FRAMES_PER_STREAM, seed=7 + rank, H=H, W=W)]
+    resident = [t.to(dev) for t in host]
+    out_host = torch.empty(2 * FRAMES_PER_STREAM, 1, H, W).pin_memory()
+    frames = 2 * FRAMES_PER_STREAM
+    h2d = sum(t.numel() * 4 for t in host)
+    d2h = out_host.numel() * 4
+
+    def step_resident():
+        with torch.no_grad():
+            return model(*resident)
+
+    def step_e2e():
+        with torch.no_grad():
+            dv = [t.to(dev, non_blocking=True) for t in host]
+            o0, o1 = model(*dv)
+            out_host[:FRAMES_PER_STREAM].copy_(o0, non_blocking=True)
+            out_host[FRAMES_PER_STREAM:].copy_(o1, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller reads the host result
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    torch.cuda.synchronize()
+
+    # ---- timed region: K steps, inputs resident in HBM -------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    _lib.profile_enable(True)
+    n0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier(); torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        step_resident()
+    e1.record()
+    torch.cuda.synchronize(); barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = ops.launch_count() - n0
+    records = _lib.profile_records()
+    _lib.profile_enable(False)
+
+    # ---- e2e: pinned host inputs -> module call -> host result ------------------------------
+    for _ in range(2):
+        step_e2e()
+    barrier(); torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        step_e2e()
+    e1.record()
+    torch.cuda.synchronize(); barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = measured_peaks()
+    rows = summarise_kernels(records, args.steps)
+    roof = roofline_of(rows[0], peaks) if rows else None
+    nconv_rows = [r for r in rows if r["kernel"].startswith("nconv_fwd")]
+    line = {
+        "metric": METRIC, "value": frames * world * args.steps / (ms / 1e3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(world),
+        "e2e": {"value": frames * world * args.steps / (ms_e2e / 1e3), "unit": UNIT,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roof,
+        "nconv_roofline": [roofline_of(r, peaks) for r in nconv_rows[:3]],
+        "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()} for r in rows[:12]],
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        times, nfr, cores = time_cpu_oracle(1, min_seconds=10.0, max_reps=8, warmup=1)
+        best = sorted(times)[len(times) // 2]
+        line["cpu_baseline"] = {"value": nfr / best, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": "%d reps x 2 frames (1 per stream) of the same workload, median; "
+                                          "oracle/nconv_oracle.py on torch CPU fp32" % len(times)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -37,6 +37,15 @@ const char* nconv_b200_error_string(int code);
 /* number of kernels this library has enqueued in the calling process (all devices) */
 unsigned long long nconv_b200_launch_count(void);
 
+/* Optional per-launch timing for the bench's roofline leg (no reference counterpart): when
+ * enabled every launcher brackets its kernel with two CUDA events on the launching stream and
+ * records a label and the launch's algorithmic flops/bytes.  enable(on) also clears the records.
+ * profile_get returns the cudaEventElapsedTime status (synchronise the stream first). */
+int nconv_b200_profile_enable(int on);
+int nconv_b200_profile_count(void);
+int nconv_b200_profile_get(int i, char* label, int label_cap, float* ms, double* flops,
+                           double* bytes);
+
 /* ---- (a3) NConv2d.forward — /root/reference/models/step1.py:116-149 -------------------
  * D = conv(c,W); N = conv(x*c,W); y = N/(D+eps)+b; cout = D/sum(W[o]).  stride 1, dil 1,
  * groups 1, zero padding (ph,pw).  One fused kernel. */

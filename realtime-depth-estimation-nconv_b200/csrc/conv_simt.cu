@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "nconv_b200.h"
 #include "launch_count.h"
+#include <cstdio>
 
 namespace nconv {
 
@@ -186,8 +187,15 @@ static int launch_conv(const ConvArgs& a, cudaStream_t st) {
     }
   }
   dim3 grid(ceil_div(a.WO, CT_TW), ceil_div(a.HO, C::TH), a.B * (a.CO / CO_T));
-  kern<<<grid, CT_THREADS, C::BYTES, st>>>(a);
-  count_launch();
+  const int CI = a.CA + a.CB;
+  const double pin = (double)a.B * a.H * a.W, pout = (double)a.B * a.HO * a.WO;
+  char label[64];
+  snprintf(label, sizeof(label), "conv%dx%d s%d %d->%d @%dx%d", K, K, S, CI, a.CO, a.H, a.W);
+  {
+    LaunchScope ls(st, label, 2.0 * CI * a.CO * K * K * pout,
+                   4.0 * (CI * pin + a.CO * pout * (a.residual ? 2.0 : 1.0)));
+    kern<<<grid, CT_THREADS, C::BYTES, st>>>(a);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -339,7 +347,13 @@ extern "C" int nconv_b200_convT4x4s2_fwd(const float* a, const float* b, const f
   t.a = a; t.b = b; t.w = w; t.scale = scale; t.shift = shift; t.y = y;
   t.B = B; t.CA = CA; t.CB = CB; t.CO = CO; t.H = H; t.W = W; t.relu = relu;
   dim3 grid(ceil_div(W, TT_TWP), ceil_div(H, TT_TH), B * (CO / TT_CO));
-  convT4x4s2_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t);
-  count_launch();
+  char label[64];
+  snprintf(label, sizeof(label), "convT4x4s2 %d->%d @%dx%d", CA + CB, CO, H, W);
+  {
+    const double pin = (double)B * H * W;
+    LaunchScope ls((cudaStream_t)stream, label, 2.0 * (CA + CB) * CO * 16 * pin,
+                   4.0 * ((CA + CB) * pin + 4.0 * CO * pin));
+    convT4x4s2_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t);
+  }
   return (int)cudaGetLastError();
 }

@@ -5,10 +5,43 @@
 #include "common.cuh"
 #include "nconv_b200.h"
 #include "launch_count.h"
+#include <cstdio>
+#include <mutex>
+#include <vector>
 
 namespace nconv {
 
 std::atomic<unsigned long long> g_launch_count{0};
+std::atomic<int> g_profile_on{0};
+
+// ---- optional per-launch event timing (bench.py roofline leg) ------------------------------
+struct ProfRecord {
+  char label[64];
+  double flops, bytes;
+  cudaEvent_t a, b;
+};
+static std::mutex g_prof_mu;
+static std::vector<ProfRecord*> g_prof;
+
+void profile_open(cudaStream_t st, const char* label, double flops, double bytes, void** token) {
+  ProfRecord* r = new ProfRecord;
+  snprintf(r->label, sizeof(r->label), "%s", label);
+  r->flops = flops; r->bytes = bytes;
+  if (cudaEventCreate(&r->a) != cudaSuccess || cudaEventCreate(&r->b) != cudaSuccess) { delete r; return; }
+  cudaEventRecord(r->a, st);
+  *token = r;
+}
+void profile_close(cudaStream_t st, void* token) {
+  ProfRecord* r = (ProfRecord*)token;
+  cudaEventRecord(r->b, st);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof.push_back(r);
+}
+static void profile_clear() {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (ProfRecord* r : g_prof) { cudaEventDestroy(r->a); cudaEventDestroy(r->b); delete r; }
+  g_prof.clear();
+}
 
 static inline int grid_for(long long n, int block = 256) {
   long long g = (n + block - 1) / block;
@@ -233,6 +266,28 @@ extern "C" unsigned long long nconv_b200_launch_count(void) {
   return g_launch_count.load(std::memory_order_relaxed);
 }
 
+extern "C" int nconv_b200_profile_enable(int on) {
+  profile_clear();
+  g_profile_on.store(on ? 1 : 0, std::memory_order_relaxed);
+  return 0;
+}
+
+extern "C" int nconv_b200_profile_count(void) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  return (int)g_prof.size();
+}
+
+extern "C" int nconv_b200_profile_get(int i, char* label, int label_cap, float* ms, double* flops,
+                                      double* bytes) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (i < 0 || i >= (int)g_prof.size() || !label || label_cap <= 0 || !ms || !flops || !bytes)
+    return NCONV_ERR_BAD_ARG;
+  ProfRecord* r = g_prof[i];
+  snprintf(label, label_cap, "%s", r->label);
+  *flops = r->flops; *bytes = r->bytes;
+  return (int)cudaEventElapsedTime(ms, r->a, r->b);
+}
+
 extern "C" const char* nconv_b200_error_string(int code) {
   switch (code) {
     case 0: return "success";
@@ -246,8 +301,10 @@ extern "C" const char* nconv_b200_error_string(int code) {
 extern "C" int nconv_b200_enforce_pos(float* w, long long n, int mode, int group, void* stream) {
   if (!w || n <= 0 || mode < 0 || mode > 3) return NCONV_ERR_BAD_ARG;
   if (mode == 3 && (group <= 0 || n % group != 0)) return NCONV_ERR_BAD_ARG;
-  enforce_pos_kernel<<<grid_for(mode == 3 ? n / group : n), 256, 0, (cudaStream_t)stream>>>(w, n, mode, group);
-  count_launch();
+  {
+    LaunchScope ls((cudaStream_t)stream, "enforce_pos", 0.0, 0.0);
+    enforce_pos_kernel<<<grid_for(mode == 3 ? n / group : n), 256, 0, (cudaStream_t)stream>>>(w, n, mode, group);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -255,8 +312,10 @@ extern "C" int nconv_b200_confidence_mask(const float* s, float* c, long long n,
                                           void* stream) {
   if (!s || !c || n < 0) return NCONV_ERR_BAD_ARG;
   if (n == 0) return 0;
-  confidence_mask_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(s, c, n, thr);
-  count_launch();
+  {
+    LaunchScope ls((cudaStream_t)stream, "confidence_mask", 0.0, 0.0);
+    confidence_mask_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(s, c, n, thr);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -264,9 +323,11 @@ extern "C" int nconv_b200_maxpool2x2_fwd(const float* x, float* y, int planes, i
                                          void* stream) {
   if (!x || !y || planes <= 0 || H < 2 || W < 2) return NCONV_ERR_BAD_ARG;
   int HP = H / 2, WP = W / 2;
-  maxpool2x2_fwd_kernel<<<grid_for((long long)planes * HP * WP), 256, 0, (cudaStream_t)stream>>>(
+  {
+    LaunchScope ls((cudaStream_t)stream, "maxpool2x2_fwd", 0.0, 0.0);
+    maxpool2x2_fwd_kernel<<<grid_for((long long)planes * HP * WP), 256, 0, (cudaStream_t)stream>>>(
       x, y, planes, H, W, HP, WP);
-  count_launch();
+  }
   return (int)cudaGetLastError();
 }
 
@@ -275,8 +336,10 @@ extern "C" int nconv_b200_maxpool2x2_bwd(const float* gy, const float* x, float*
   if (!gy || !x || !gx || planes <= 0 || H < 2 || W < 2) return NCONV_ERR_BAD_ARG;
   int HP = H / 2, WP = W / 2;
   long long cells = (long long)planes * ((H + 1) / 2) * ((W + 1) / 2);
-  maxpool2x2_bwd_kernel<<<grid_for(cells), 256, 0, (cudaStream_t)stream>>>(gy, x, gx, planes, H, W, HP, WP);
-  count_launch();
+  {
+    LaunchScope ls((cudaStream_t)stream, "maxpool2x2_bwd", 0.0, 0.0);
+    maxpool2x2_bwd_kernel<<<grid_for(cells), 256, 0, (cudaStream_t)stream>>>(gy, x, gx, planes, H, W, HP, WP);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -286,9 +349,11 @@ extern "C" int nconv_b200_upcat_fwd(const float* skip, const float* low, float* 
   if (!skip || !low || !out || B <= 0 || Cs <= 0 || Cl <= 0 || H <= 0 || W <= 0 || HL <= 0 || WL <= 0)
     return NCONV_ERR_BAD_ARG;
   long long total = (long long)B * (Cs + Cl) * H * W;
-  upcat_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+  {
+    LaunchScope ls((cudaStream_t)stream, "upcat_fwd", 0.0, 0.0);
+    upcat_fwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
       skip, low, out, B, Cs, Cl, H, W, HL, WL, skip_first, NearestMap::make(HL, H), NearestMap::make(WL, W));
-  count_launch();
+  }
   return (int)cudaGetLastError();
 }
 
@@ -299,13 +364,17 @@ extern "C" int nconv_b200_upcat_bwd(const float* gout, float* gskip, float* glow
     return NCONV_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   if (gskip) {
-    upcat_bwd_skip_kernel<<<grid_for((long long)B * Cs * H * W), 256, 0, st>>>(gout, gskip, B, Cs, Cl, H, W, skip_first);
-    count_launch();
+    {
+      LaunchScope ls(st, "upcat_bwd_skip", 0.0, 0.0);
+      upcat_bwd_skip_kernel<<<grid_for((long long)B * Cs * H * W), 256, 0, st>>>(gout, gskip, B, Cs, Cl, H, W, skip_first);
+    }
   }
   if (glow) {
-    upcat_bwd_low_kernel<<<grid_for((long long)B * Cl * HL * WL), 256, 0, st>>>(
+    {
+      LaunchScope ls(st, "upcat_bwd_low", 0.0, 0.0);
+      upcat_bwd_low_kernel<<<grid_for((long long)B * Cl * HL * WL), 256, 0, st>>>(
         gout, glow, B, Cs, Cl, H, W, HL, WL, skip_first, NearestMap::make(HL, H), NearestMap::make(WL, W));
-    count_launch();
+    }
   }
   return (int)cudaGetLastError();
 }
@@ -315,18 +384,22 @@ extern "C" int nconv_b200_bilinear_ac_fwd(const float* x, float* y, int planes, 
   if (!x || !y || planes <= 0 || H <= 0 || W <= 0 || HO <= 0 || WO <= 0) return NCONV_ERR_BAD_ARG;
   float sh = HO > 1 ? (float)(H - 1) / (float)(HO - 1) : 0.f;
   float sw = WO > 1 ? (float)(W - 1) / (float)(WO - 1) : 0.f;
-  bilinear_ac_kernel<<<grid_for((long long)planes * HO * WO), 256, 0, (cudaStream_t)stream>>>(
+  {
+    LaunchScope ls((cudaStream_t)stream, "bilinear_ac", 0.0, 0.0);
+    bilinear_ac_kernel<<<grid_for((long long)planes * HO * WO), 256, 0, (cudaStream_t)stream>>>(
       x, y, planes, H, W, HO, WO, sh, sw);
-  count_launch();
+  }
   return (int)cudaGetLastError();
 }
 
 extern "C" int nconv_b200_zero_border(float* x, int planes, int H, int W, int top, int bottom,
                                       int left, void* stream) {
   if (!x || planes <= 0 || H <= 0 || W <= 0 || top < 0 || bottom < 0 || left < 0) return NCONV_ERR_BAD_ARG;
-  zero_border_kernel<<<grid_for((long long)planes * H * W), 256, 0, (cudaStream_t)stream>>>(
+  {
+    LaunchScope ls((cudaStream_t)stream, "zero_border", 0.0, 0.0);
+    zero_border_kernel<<<grid_for((long long)planes * H * W), 256, 0, (cudaStream_t)stream>>>(
       x, planes, H, W, top, bottom, left);
-  count_launch();
+  }
   return (int)cudaGetLastError();
 }
 
@@ -334,8 +407,10 @@ extern "C" int nconv_b200_bn_fold(const float* gamma, const float* beta, const f
                                   const float* var, const float* conv_bias, float* scale,
                                   float* shift, int C, float eps, void* stream) {
   if (!gamma || !beta || !mean || !var || !scale || !shift || C <= 0) return NCONV_ERR_BAD_ARG;
-  bn_fold_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, mean, var, conv_bias,
+  {
+    LaunchScope ls((cudaStream_t)stream, "bn_fold", 0.0, 0.0);
+    bn_fold_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, mean, var, conv_bias,
                                                                   scale, shift, C, eps);
-  count_launch();
+  }
   return (int)cudaGetLastError();
 }

@@ -12,6 +12,7 @@
 // correlation of nconv_tiled.cuh run on (gN,gD) with flipped weights; (3) weight gradient as a
 // persistent tiled reduction with per-CTA partials and a fixed-order (deterministic) final sum.
 #include "nconv_tiled.cuh"
+#include <cstdio>
 
 namespace nconv {
 
@@ -351,12 +352,20 @@ static int launch_wgrad(WGradArgs a, float* ws_partial, float* gw, float* gb, cu
   if (ctas_x > ntiles) ctas_x = ntiles;
   a.partial = ws_partial;
   a.chan_part = ws_partial + (size_t)chunks * ctas_x * C::OUT_PER_CTA;
-  kern<<<dim3(ctas_x, chunks), WG_THREADS, C::BYTES, st>>>(a);
-  count_launch();
+  char label[64];
+  snprintf(label, sizeof(label), "nconv_wgrad %d->%d k%d", CI, CO, K);
+  {
+    // reads gy, gcout, y, cout once per input-channel chunk and x, c once per output chunk
+    const double pin = (double)a.B * a.H * a.W, pout = (double)a.B * a.HO * a.WO;
+    LaunchScope ls(st, label, 4.0 * CI * CO * K * K * pout, 4.0 * (2.0 * CI * pin + 4.0 * CO * pout));
+    kern<<<dim3(ctas_x, chunks), WG_THREADS, C::BYTES, st>>>(a);
+  }
   NCONV_RETURN_IF_ERR(cudaGetLastError());
   const int total = CO * CI * K * K + CO;
-  nconv_wgrad_final<CI, CO, K><<<ceil_div(total, 128), 128, 0, st>>>(a.partial, a.chan_part, a.wsum, gw, gb, ctas_x);
-  count_launch();
+  {
+    LaunchScope ls(st, "nconv_wgrad_final", 0.0, 4.0 * (double)chunks * ctas_x * C::OUT_PER_CTA);
+    nconv_wgrad_final<CI, CO, K><<<ceil_div(total, 128), 128, 0, st>>>(a.partial, a.chan_part, a.wsum, gw, gb, ctas_x);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -440,8 +449,10 @@ extern "C" int nconv_b200_nconv2d_bwd(const float* gy, const float* gcout, const
   float* wsum = (float*)workspace;
   float* part = wsum + align_up((size_t)Co, 64);
 
-  wsum_kernel<<<Co, 32, 0, st>>>(w, wsum, Co, Ci * kh * kw);
-  count_launch();
+  {
+    LaunchScope ls(st, "wsum", 0.0, 4.0 * Co * Ci * kh * kw);
+    wsum_kernel<<<Co, 32, 0, st>>>(w, wsum, Co, Ci * kh * kw);
+  }
   NCONV_RETURN_IF_ERR(cudaGetLastError());
 
   const bool square = (kh == kw) && (ph == pw);
@@ -462,9 +473,12 @@ extern "C" int nconv_b200_nconv2d_bwd(const float* gy, const float* gcout, const
       long long total = (long long)B * Ci * H * W;
       int blocks = (int)((total + 255) / 256);
       if (blocks > 148 * 32) blocks = 148 * 32;
-      nconv_bwd_data_generic<<<blocks, 256, 0, st>>>(gy, gcout, x, c, w, bias, y, cout, wsum, gx, gc, B,
-                                                     Ci, Co, H, W, kh, kw, ph, pw, HO, WO, eps);
-      count_launch();
+      {
+        LaunchScope ls(st, "nconv_bwd_data_generic", 4.0 * Ci * Co * kh * kw * (double)B * H * W,
+                       4.0 * B * (4.0 * Ci * H * W + 4.0 * Co * HO * WO));
+        nconv_bwd_data_generic<<<blocks, 256, 0, st>>>(gy, gcout, x, c, w, bias, y, cout, wsum, gx, gc, B,
+                                                       Ci, Co, H, W, kh, kw, ph, pw, HO, WO, eps);
+      }
       rc = (int)cudaGetLastError();
     }
     if (rc) return rc;
@@ -479,10 +493,13 @@ extern "C" int nconv_b200_nconv2d_bwd(const float* gy, const float* gcout, const
       rc = wgrad_dispatch(wa, part, gw, gb, Ci, Co, kh, st);
     }
     if (rc == NCONV_ERR_UNSUPPORTED) {
-      nconv_bwd_weight_generic<<<Co * Ci * kh * kw + Co, 256, 0, st>>>(gy, gcout, x, c, bias, y, cout, wsum,
-                                                                       gw, gb, B, Ci, Co, H, W, kh, kw,
-                                                                       ph, pw, HO, WO, eps);
-      count_launch();
+      {
+        LaunchScope ls(st, "nconv_bwd_weight_generic", 4.0 * Ci * Co * kh * kw * (double)B * HO * WO,
+                       4.0 * B * (2.0 * Ci * H * W + 4.0 * Co * HO * WO));
+        nconv_bwd_weight_generic<<<Co * Ci * kh * kw + Co, 256, 0, st>>>(gy, gcout, x, c, bias, y, cout, wsum,
+                                                                         gw, gb, B, Ci, Co, H, W, kh, kw,
+                                                                         ph, pw, HO, WO, eps);
+      }
       rc = (int)cudaGetLastError();
     }
     if (rc) return rc;

@@ -128,8 +128,11 @@ extern "C" int nconv_b200_nconv2d_fwd(const float* x, const float* c, const floa
   long long total = (long long)B * Co * HO * WO;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 32) blocks = 148 * 32;
-  nconv_fwd_generic<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, c, w, bias, y, cout, B, Ci, Co, H,
-                                                             W, kh, kw, ph, pw, HO, WO, eps);
-  count_launch();
+  {
+    LaunchScope ls((cudaStream_t)stream, "nconv_fwd_generic", 4.0 * Ci * Co * kh * kw * (double)B * HO * WO,
+                   4.0 * B * (2.0 * Ci * H * W + 2.0 * Co * HO * WO));
+    nconv_fwd_generic<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, c, w, bias, y, cout, B, Ci, Co, H,
+                                                               W, kh, kw, ph, pw, HO, WO, eps);
+  }
   return (int)cudaGetLastError();
 }

@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "nconv_b200.h"
 #include "launch_count.h"
+#include <cstdio>
 
 namespace nconv {
 
@@ -413,8 +414,32 @@ static int launch_tiled(const TiledArgs& a, cudaStream_t st) {
   const bool tail = (FLAGS & NCONV_B200_F_TAIL) != 0;
   int ow = tail ? a.W : a.WO, oh = tail ? a.H : a.HO;
   dim3 grid(ceil_div(ow, TW), ceil_div(oh, TH), a.B * (CO / CO_T));
-  kern<<<grid, NTHREADS, SM::BYTES, st>>>(a);
-  count_launch();
+  // Algorithmic work of this launch.  Forward: both streams of both sources are read once
+  // (the low-resolution source at its own size, one plane instead of two under F_THRESH) and
+  // every output written once.  Backward-data: gy, gcout, y, cout in; x, c in; gx, gc out.
+  constexpr bool BWD = (FLAGS & F_BWD) != 0;
+  constexpr bool THRESH = (FLAGS & NCONV_B200_F_THRESH) != 0;
+  constexpr bool POOL = (FLAGS & NCONV_B200_F_POOL) != 0;
+  const double px_in = (double)a.B * a.H * a.W, px_out = (double)a.B * oh * ow;
+  double bytes, flops;
+  if (BWD) {
+    bytes = 4.0 * (4.0 * CA * px_in + 4.0 * CO * px_out);
+    flops = 4.0 * CA * CO * K * K * px_out;
+  } else if (tail) {
+    bytes = 4.0 * (2.0 * CA * px_in + 2.0 * CB * a.B * a.HB * a.WB + px_out);
+    flops = 4.0 * (CA + CB) * CO * K * K * px_out + 4.0 * CO * px_out;
+  } else {
+    bytes = 4.0 * ((THRESH ? 1.0 : 2.0) * CA * px_in + 2.0 * CB * a.B * a.HB * a.WB + 2.0 * CO * px_out +
+                   (POOL ? 2.0 * CO * a.B * a.HP * a.WP : 0.0));
+    flops = 4.0 * (CA + CB) * CO * K * K * px_out;
+  }
+  char label[64];
+  snprintf(label, sizeof(label), "%s %d+%d->%d k%d f%d", BWD ? "nconv_bwd_data" : "nconv_fwd", CA, CB, CO, K,
+           FLAGS & 7);
+  {
+    LaunchScope ls(st, label, flops, bytes);
+    kern<<<grid, NTHREADS, SM::BYTES, st>>>(a);
+  }
   return (int)cudaGetLastError();
 }
 

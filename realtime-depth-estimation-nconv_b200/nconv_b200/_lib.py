@@ -43,6 +43,10 @@ SIGNATURES = {
     "nconv_b200_abi_version": (c_int, []),
     "nconv_b200_error_string": (c_char_p, [c_int]),
     "nconv_b200_launch_count": (c_ulonglong, []),
+    "nconv_b200_profile_enable": (c_int, [c_int]),
+    "nconv_b200_profile_count": (c_int, []),
+    "nconv_b200_profile_get": (c_int, [c_int, ctypes.c_char_p, c_int, POINTER(c_float), POINTER(ctypes.c_double),
+                                       POINTER(ctypes.c_double)]),
     "nconv_b200_nconv2d_fwd": (c_int, [c_void_p] * 6 + [c_int] * 9 + [c_float, c_void_p]),
     "nconv_b200_nconv2d_fwd_fused": (c_int, [POINTER(FwdDesc), c_void_p]),
     "nconv_b200_nconv2d_bwd_workspace_bytes": (c_size_t, [c_int] * 9),
@@ -95,3 +99,22 @@ def check(code: int, what: str) -> None:
 
 def launch_count() -> int:
     return int(load().nconv_b200_launch_count())
+
+
+def profile_enable(on: bool) -> None:
+    """Per-launch CUDA-event timing inside the library (bench.py's roofline leg)."""
+    check(load().nconv_b200_profile_enable(int(on)), "profile_enable")
+
+
+def profile_records():
+    """[(label, ms, flops, bytes)] for every launch since profile_enable(True).  The caller
+    must have synchronised the device."""
+    lib = load()
+    out = []
+    buf = ctypes.create_string_buffer(64)
+    ms, fl, by = c_float(), ctypes.c_double(), ctypes.c_double()
+    for i in range(lib.nconv_b200_profile_count()):
+        check(lib.nconv_b200_profile_get(i, buf, 64, ctypes.byref(ms), ctypes.byref(fl), ctypes.byref(by)),
+              "profile_get")
+        out.append((buf.value.decode(), float(ms.value), float(fl.value), float(by.value)))
+    return out

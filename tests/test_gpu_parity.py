@@ -1,0 +1,324 @@
+"""GPU parity: the sm_100a CUDA path (through the C ABI / torch.ops.nconv_b200.*) against the
+golden vectors of the unmodified reference and against the CPU oracle on the same seeded inputs.
+
+Tolerance (BASELINE.json north_star): fp32 depth/confidence max-rel <= 1e-4, with |ref| floored
+at 1e-3 (`O.max_rel_err`); gradients: max-abs error <= 1e-4 x max|ref| per tensor; 2x2 max-pool
+values and argmax routing bit-exact on identical inputs (first max in row-major window order,
+strict `>`, NaN propagates)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import REL_TOL, T
+from oracle import nconv_oracle as O
+from nconv_b200.synthetic import (NCONV_LAYER_CASES, nconv_layer_case, sparse_depth_kitti, sparse_depth_nyu,
+                                  setp2_inputs, randomise_bn_stats)
+
+pytestmark = pytest.mark.gpu
+GRAD_TOL = 1e-4
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def grad_err(a, ref):
+    ref = ref.double().cpu()
+    return float((a.double().cpu() - ref).abs().max()) / (float(ref.abs().max()) + 1e-30)
+
+
+@pytest.fixture(scope="module")
+def K():
+    import nconv_b200.ops  # noqa: F401  (raises if the .so is missing: no fallback)
+    return torch.ops.nconv_b200
+
+
+# ---------------------------------------------------------------------------------------------
+# NConv2d layer: forward + backward vs reference goldens (step1.py:116-149 + autograd)
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("idx", range(len(NCONV_LAYER_CASES)))
+def test_nconv2d_layer_vs_reference_golden(golden, K, idx):
+    g = golden("nconv2d_layers.npz")
+    ci, co, k, pad, B, H, W = NCONV_LAYER_CASES[idx]
+    x, c, gy, gc = (t.to(dev()) for t in nconv_layer_case(idx))
+    p = "case%d_" % idx
+    w = T(g[p + "w"]).to(dev()).requires_grad_(True)
+    b = T(g[p + "b"]).to(dev()).requires_grad_(True)
+    x.requires_grad_(True); c.requires_grad_(True)
+    before = __import__("nconv_b200.ops", fromlist=["x"]).launch_count()
+    y, cout = K.nconv2d(x, c, w, b, pad, pad, 1e-7)
+    assert __import__("nconv_b200.ops", fromlist=["x"]).launch_count() > before   # our kernel ran
+    assert O.max_rel_err(y, T(g[p + "y"])) <= REL_TOL
+    assert O.max_rel_err(cout, T(g[p + "cout"])) <= REL_TOL
+    ((y * gy).sum() + (cout * gc).sum()).backward()
+    for name, t in (("gx", x.grad), ("gc", c.grad), ("gw", w.grad), ("gb", b.grad)):
+        assert grad_err(t, T(g[p + name])) <= GRAD_TOL, name
+
+
+def test_nconv2d_module_hook_semantics(K):
+    """KA4: training forward overwrites the stored weight with softplus(w, beta=10) in place;
+    eval leaves it alone; the gradient is straight-through (w.r.t. the transformed weight)."""
+    from models.step1 import NConv2d
+    torch.manual_seed(21)
+    layer = NConv2d(4, 4, (3, 3), 'softplus', 'k', padding=(1, 1)).to(dev())
+    w0 = layer.weight.detach().clone()
+    x = torch.rand(1, 4, 12, 20, device=dev()) * 5
+    c = (torch.rand(1, 4, 12, 20, device=dev()) > 0.5).float()
+    layer.eval()
+    layer(x, c)
+    assert torch.equal(layer.weight.detach(), w0)
+    layer.train()
+    y, co = layer(x, c)
+    w1 = F.softplus(w0.cpu(), beta=10)
+    assert O.max_rel_err(layer.weight, w1, floor=1e-6) <= 2e-6
+    yr, cr = O.nconv2d(x.cpu(), c.cpu(), layer.weight.detach().cpu(), layer.bias.detach().cpu(), (1, 1))
+    assert O.max_rel_err(y, yr) <= REL_TOL and O.max_rel_err(co, cr) <= REL_TOL
+    y.sum().backward()
+    assert layer.weight.grad is not None and layer.bnorm.weight.grad is None      # KA5
+    layer(x, c)                                  # hook fires again: weights drift (softplus twice)
+    assert O.max_rel_err(layer.weight, F.softplus(w1, beta=10), floor=1e-6) <= 4e-6
+
+
+@pytest.mark.parametrize("mode", ["softplus", "exp", "sigmoid", "softmax"])
+def test_enforce_pos_modes(K, mode):
+    """step1.py:197-212, all four pos_fn options."""
+    torch.manual_seed(5)
+    w = torch.randn(6, 3, 5, 5) * 2
+    w[0, 0, 0, :3] = torch.tensor([2.5, 1.9999, -30.0])      # across the softplus threshold
+    q = w.clone().to(dev())
+    from nconv_b200.ops import POS_MODES
+    K.enforce_pos_(q, POS_MODES[mode], 25)
+    if mode == "softplus":
+        ref = F.softplus(w, beta=10)
+    elif mode == "exp":
+        ref = torch.exp(w)
+    elif mode == "sigmoid":
+        ref = torch.sigmoid(w)
+    else:
+        ref = F.softmax(w.view(6, 3, -1), -1).view_as(w)
+    assert O.max_rel_err(q, ref, floor=1e-6) <= 1e-5
+
+
+# ---------------------------------------------------------------------------------------------
+# pools / upsample+concat: bit-exact
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(2, 3, 8, 12), (1, 8, 9, 13), (1, 1, 2, 2), (2, 8, 60, 80)])
+def test_maxpool_bit_exact_with_ties_and_nan(K, shape):
+    torch.manual_seed(3)
+    x = torch.randint(0, 3, shape).float()                  # heavy ties (KA9)
+    x[0, 0, 0, 1] = float("nan")
+    x.requires_grad_(True)
+    ref = F.max_pool2d(x, 2, 2)
+    gy = torch.randn_like(ref)
+    ref.backward(gy)
+    xg = x.detach().to(dev()).requires_grad_(True)
+    out = K.maxpool2x2(xg)
+    assert torch.equal(torch.nan_to_num(out.cpu(), nan=-7.0), torch.nan_to_num(ref.detach(), nan=-7.0))
+    out.backward(gy.to(dev()))
+    assert torch.equal(xg.grad.cpu(), x.grad)              # routing = argmax indices, bit-exact
+
+
+def test_maxpool_constant_plane_indices(K):
+    """KA6: on a constant 4x4 plane the argmax indices are [0,2,8,10]."""
+    x = torch.ones(1, 1, 4, 4, device=dev(), requires_grad=True)
+    K.maxpool2x2(x).backward(torch.ones(1, 1, 2, 2, device=dev()))
+    assert x.grad.flatten().nonzero().flatten().tolist() == [0, 2, 8, 10]
+
+
+@pytest.mark.parametrize("skip_first", [True, False])
+@pytest.mark.parametrize("hw", [((10, 14), (5, 7)), ((11, 15), (5, 7)), ((6, 8), (6, 8))])
+def test_upcat_bit_exact(K, skip_first, hw):
+    (H, W), (HL, WL) = hw
+    torch.manual_seed(4)
+    skip = torch.randn(2, 3, H, W, requires_grad=True)
+    low = torch.randn(2, 5, HL, WL, requires_grad=True)
+    up = F.interpolate(low, (H, W), mode="nearest")
+    ref = torch.cat((skip, up), 1) if skip_first else torch.cat((up, skip), 1)
+    g = torch.randn_like(ref)
+    ref.backward(g)
+    s2 = skip.detach().to(dev()).requires_grad_(True)
+    l2 = low.detach().to(dev()).requires_grad_(True)
+    out = K.upcat(s2, l2, skip_first)
+    assert torch.equal(out.cpu(), ref.detach())
+    out.backward(g.to(dev()))
+    assert torch.equal(s2.grad.cpu(), skip.grad)
+    assert O.max_rel_err(l2.grad, low.grad, floor=1e-6) <= 1e-6
+
+
+# ---------------------------------------------------------------------------------------------
+# SETP1 whole net (fused 9-kernel pipeline and staged training graph)
+# ---------------------------------------------------------------------------------------------
+def _load_setp1(g):
+    from models.step1 import SETP1_NCONV
+    m = SETP1_NCONV()
+    sd = m.state_dict()
+    for k in g.files:
+        if k.startswith("sd_"):
+            sd[k[3:]] = T(g[k])
+    m.load_state_dict(sd)
+    return m.to(dev()).eval()
+
+
+def test_setp1_small_fused_and_staged(golden):
+    g = golden("setp1.npz")
+    m = _load_setp1(g)
+    S = T(g["small_S"]).to(dev())
+    ref = T(g["small_out"])[:, :, :64, :96]
+    with torch.no_grad():
+        out = m(S)                                           # fused pipeline
+    assert out.shape == (2, 1, 64, 96)
+    assert O.max_rel_err(out, ref) <= REL_TOL
+    S2 = S.clone().requires_grad_(True)                      # forces the staged graph
+    out2, conf2 = m.d_net(S2, return_confidence=True)
+    assert O.max_rel_err(out2, ref) <= REL_TOL
+    assert O.max_rel_err(conf2, T(g["small_nconv7_c"])[:, :, 1:65, 1:97]) <= REL_TOL
+    # two-tensor call style of step2.py:62 / void_train_step1.py:61
+    with torch.no_grad():
+        out3 = m(S[:1], S[1:])
+    assert torch.equal(out3, out)
+
+
+def test_setp1_odd_size(golden):
+    g = golden("setp1.npz")
+    m = _load_setp1(g)
+    with torch.no_grad():
+        out = m(T(g["odd_S"]).to(dev()))
+    assert O.max_rel_err(out, T(g["odd_out"])[:, :, :45, :70]) <= REL_TOL
+
+
+def test_setp1_nyu_config1(golden):
+    g = golden("setp1.npz")
+    m = _load_setp1(g)
+    with torch.no_grad():
+        out = m(sparse_depth_nyu(1, seed=0).to(dev()))
+    assert O.max_rel_err(out, T(g["nyu_out"])) <= REL_TOL
+    b7 = float(T(g["sd_d_net.nconv7.bias"])[0])
+    o = out[0, 0].cpu()
+    for ring in (o[0], o[-1], o[:, 0], o[:, -1]):            # KA3
+        assert torch.all(ring == b7)
+
+
+def test_setp1_kitti_overlap_and_full(golden):
+    g = golden("setp1.npz")
+    m = _load_setp1(g)
+    S = sparse_depth_kitti(1, seed=2000)
+    with torch.no_grad():
+        out = m(S.to(dev()))
+    assert out.shape == (1, 1, 352, 1216)
+    assert O.max_rel_err(out[..., :640], T(g["kitti_out"])[:, :, :352]) <= REL_TOL
+    sd = {k[3:]: T(g[k]) for k in g.files if k.startswith("sd_")}
+    assert O.max_rel_err(out, O.dnet_forward(S, sd)) <= REL_TOL
+
+
+def test_setp1_training_step_vs_reference_golden(golden):
+    """One training-mode forward/backward (hook + staged graph + analytic backward kernels)."""
+    from models.step1 import SETP1_NCONV
+    g = golden("setp1_train.npz")
+    torch.manual_seed(3)
+    m = SETP1_NCONV().to(dev())
+    m.train()
+    S = T(g["S"]).to(dev())
+    y = m(S)
+    assert O.max_rel_err(y, T(g["out"])) <= REL_TOL
+    (y * T(g["G"]).to(dev())).sum().backward()
+    for k, p in m.named_parameters():
+        if "bnorm" in k:
+            assert p.grad is None
+            continue
+        assert O.max_rel_err(p, T(g["w_" + k]), floor=1e-6) <= 1e-5, k
+        assert grad_err(p.grad, T(g["g_" + k])) <= 5e-4, k
+
+
+def test_batch_sharding_is_bit_identical(golden):
+    """frames are independent, so a shard's result equals the full-batch result."""
+    g = golden("setp1.npz")
+    m = _load_setp1(g)
+    S = sparse_depth_nyu(4, seed=9, H=96, W=128, points=200).to(dev())
+    with torch.no_grad():
+        full = m(S)
+        parts = torch.cat([m(S[i:i + 2]) for i in (0, 2)], 0)
+    assert torch.equal(full, parts)
+
+
+# ---------------------------------------------------------------------------------------------
+# SETP2 blocks and whole EXPORT graph
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cfg", [
+    # CA, CB, CO, K, stride, relu, affine, residual, H, W
+    (3, 0, 32, 3, 1, True, True, False, 20, 36), (3, 0, 32, 1, 1, False, False, True, 20, 36),
+    (32, 0, 64, 3, 2, True, True, False, 20, 36), (32, 0, 64, 1, 2, False, False, True, 20, 36),
+    (64, 64, 64, 3, 1, True, True, False, 15, 20), (1, 0, 64, 3, 1, True, True, False, 15, 21),
+    (64, 0, 1, 3, 1, False, False, True, 15, 20), (32, 0, 1, 3, 1, False, False, True, 17, 23),
+    (64, 0, 32, 3, 1, True, True, False, 16, 24),
+])
+def test_conv2d_block(K, cfg):
+    CA, CB, CO, k, s, relu, affine, residual, H, W = cfg
+    torch.manual_seed(CA * 100 + CO + k)
+    a = torch.randn(2, CA, H, W)
+    b = torch.randn(2, CB, H, W) if CB else None
+    w = torch.randn(CO, CA + CB, k, k) / (3 * (CA + CB)) ** 0.5
+    scale = torch.rand(CO) + 0.5 if affine else None
+    shift = torch.randn(CO) if affine else None
+    xin = a if b is None else torch.cat((a, b), 1)
+    ref = F.conv2d(xin, w, None, s, k // 2)
+    if affine:
+        ref = ref * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
+    if relu:
+        ref = F.relu(ref)
+    res = torch.randn_like(ref) if residual else None
+    if residual:
+        ref = ref + res
+    to = lambda t: None if t is None else t.to(dev())
+    out = K.conv2d(to(a), to(b), to(w), to(scale), to(shift), to(res), s, relu)
+    assert float((out.cpu() - ref).abs().max()) <= 1e-4 * max(1.0, float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("cfg", [(1, 64, 64, 15, 20), (1, 32, 32, 9, 13), (1, 8, 16, 5, 6)])
+def test_convT4x4s2_block(K, cfg):
+    CA, CB, CO, H, W = cfg
+    torch.manual_seed(77)
+    a = torch.randn(2, CA, H, W); b = torch.randn(2, CB, H, W)
+    w = torch.randn(CA + CB, CO, 4, 4) / (4 * (CA + CB)) ** 0.5
+    scale = torch.rand(CO) + 0.5; shift = torch.randn(CO)
+    ref = F.conv_transpose2d(torch.cat((a, b), 1), w, None, 2, 1)
+    ref = F.relu(ref * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1))
+    out = K.convT4x4s2(a.to(dev()), b.to(dev()), w.to(dev()), scale.to(dev()), shift.to(dev()), True)
+    assert float((out.cpu() - ref).abs().max()) <= 1e-4 * max(1.0, float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("hw", [((480, 640), 8), ((480, 640), 4), ((480, 640), 2), ((45, 70), 4), ((16, 24), 8)])
+def test_bilinear_align_corners(K, hw):
+    (H, W), f = hw
+    torch.manual_seed(8)
+    x = torch.rand(2, 1, H, W) * 10
+    ref = F.interpolate(x, scale_factor=1 / f, mode="bilinear", align_corners=True)
+    out = K.bilinear_ac(x.to(dev()), ref.shape[2], ref.shape[3])
+    assert O.max_rel_err(out, ref) <= 1e-5
+
+
+def test_setp2_export_vs_reference_golden(golden):
+    from models.step2 import SETP2_BP_EXPORT
+    g = golden("setp2_export.npz")
+    torch.manual_seed(5)
+    m = SETP2_BP_EXPORT()
+    sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    m.load_state_dict(O.apply_enforce_pos(sd, prefix="step1.d_net."))
+    m.eval()
+    randomise_bn_stats(m, seed=55)
+    m.to(dev())
+    rgb0, d0, rgb1, d1 = (t.to(dev()) for t in setp2_inputs(1, seed=7))
+    with torch.no_grad():
+        o0, o1 = m(rgb0, d0, rgb1, d1)
+    # SETP2 is a 38-conv fp32 stack on O(100) activations: same 1e-4 max-rel bound, |ref| floor 1e-3
+    assert O.max_rel_err(o0, T(g["out0"])) <= REL_TOL
+    assert O.max_rel_err(o1, T(g["out1"])) <= REL_TOL
+    assert torch.all(o0[:, :, :45] == 0) and torch.all(o0[:, :, -45:] == 0) and torch.all(o0[..., :20] == 0)
+
+
+def test_setp2_train_mode_bn_raises():
+    """No silent fallback: batch-statistics BatchNorm is not implemented on the CUDA path yet."""
+    from models.step2 import RGBEncoder
+    enc = RGBEncoder(3, 32, 1).to(dev()).train()
+    with pytest.raises(NotImplementedError):
+        enc(torch.rand(1, 3, 8, 8, device=dev()))
