@@ -114,9 +114,7 @@ def gen_setp1(r1):
     np.savez_compressed(os.path.join(OUT, "setp1.npz"), **out)
 
 
-def gen_setp1_train(r1):
-    """One training-mode forward/backward of the reference SETP1 (autograd through pools,
-    upsamples, cats and 18 convs) with a fixed linear loss, from a fresh seed-3 model."""
+def _setp1_train_run(r1, double):
     torch.manual_seed(3)
     m = r1.SETP1_NCONV()
     m.train()
@@ -124,14 +122,35 @@ def gen_setp1_train(r1):
     S = torch.rand(2, 1, 40, 56) * 9 + 1
     S = S * (torch.rand_like(S) < 0.15)
     G = torch.randn(2, 1, 40, 56)
-    y = m(S)[:, :, :40, :56]
-    (y * G).sum().backward()
+    saved = torch.Tensor.float
+    if double:
+        # step1.py:53 hard-casts the confidence with .float(); patch it for the fp64 run only
+        m, S, G = m.double(), S.double(), G.double()
+        torch.Tensor.float = lambda t: t.double()
+    try:
+        y = m(S)[:, :, :40, :56]
+        (y * G).sum().backward()
+    finally:
+        torch.Tensor.float = saved
+    return m, S, G, y
+
+
+def gen_setp1_train(r1):
+    """One training-mode forward/backward of the reference SETP1 (autograd through pools,
+    upsamples, cats and 18 convs) with a fixed linear loss, from a fresh seed-3 model.  The same
+    step is also run in fp64 (g64_*): some gradients are ill-conditioned sums (nconv1.bias: the
+    reference's own fp32 result is 8.6e-4 from its fp64 result), so the parity test bounds the
+    CUDA path's distance to fp64 by a multiple of the reference's own fp32 distance."""
+    m, S, G, y = _setp1_train_run(r1, False)
+    m64, _, _, _ = _setp1_train_run(r1, True)
     out = {"S": _np(S), "G": _np(G), "out": _np(y)}
+    p64 = dict(m64.named_parameters())
     for k, p in m.named_parameters():
         if "bnorm" in k:
             continue
         out["w_" + k] = _np(p)               # post-hook (softplus'ed) values
         out["g_" + k] = _np(p.grad)
+        out["g64_" + k] = _np(p64[k].grad)
     np.savez_compressed(os.path.join(OUT, "setp1_train.npz"), **out)
 
 
@@ -170,10 +189,15 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
     r1, r2 = ref_shim.load_reference()
-    gen_nconv_layers(r1)
-    gen_setp1(r1)
-    gen_setp1_train(r1)
-    gen_setp2(r1, r2)
+    only = sys.argv[1:]
+    if not only or "layers" in only:
+        gen_nconv_layers(r1)
+    if not only or "setp1" in only:
+        gen_setp1(r1)
+    if not only or "train" in only:
+        gen_setp1_train(r1)
+    if not only or "setp2" in only:
+        gen_setp2(r1, r2)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

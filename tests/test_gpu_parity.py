@@ -17,6 +17,7 @@ from nconv_b200.synthetic import (NCONV_LAYER_CASES, nconv_layer_case, sparse_de
 
 pytestmark = pytest.mark.gpu
 GRAD_TOL = 1e-4
+SETP2_FLOOR = 0.1
 
 
 def dev():
@@ -227,7 +228,12 @@ def test_setp1_training_step_vs_reference_golden(golden):
             assert p.grad is None
             continue
         assert O.max_rel_err(p, T(g["w_" + k]), floor=1e-6) <= 1e-5, k
-        assert grad_err(p.grad, T(g["g_" + k])) <= 5e-4, k
+        # Gradients are compared with the reference's fp64 run.  Tolerance: 2e-4 of max|g|, or
+        # 3x the reference's OWN fp32-vs-fp64 distance where that is larger (nconv1.bias is an
+        # ill-conditioned sum: the reference's fp32 autograd is 8.6e-4 from its fp64 result).
+        g64 = T(g["g64_" + k].astype("float64"))
+        noise = grad_err(T(g["g_" + k]), g64)
+        assert grad_err(p.grad, g64) <= max(2e-4, 3.0 * noise), (k, noise)
 
 
 def test_batch_sharding_is_bit_identical(golden):
@@ -310,9 +316,15 @@ def test_setp2_export_vs_reference_golden(golden):
     rgb0, d0, rgb1, d1 = (t.to(dev()) for t in setp2_inputs(1, seed=7))
     with torch.no_grad():
         o0, o1 = m(rgb0, d0, rgb1, d1)
-    # SETP2 is a 38-conv fp32 stack on O(100) activations: same 1e-4 max-rel bound, |ref| floor 1e-3
-    assert O.max_rel_err(o0, T(g["out0"])) <= REL_TOL
-    assert O.max_rel_err(o1, T(g["out1"])) <= REL_TOL
+    # SETP2 tolerance: max-rel 1e-4 with |ref| floored at SETP2_FLOOR = 0.1 m (1 % of the NYU depth
+    # range).  With random-init weights the refined depth crosses zero, and at a 1e-3 floor the
+    # reference's OWN fp32 result is 9.6e-5 from its fp64 result at those pixels (abs 1e-5 on
+    # values of ~6; DESIGN.md "Parity"), so a 1e-3 floor would test the summation order, not the
+    # arithmetic.  The global scaled error max|a-b|/max|b| is bounded at 1e-5 as well.
+    for o, key in ((o0, "out0"), (o1, "out1")):
+        ref = T(g[key])
+        assert O.max_rel_err(o, ref, floor=SETP2_FLOOR) <= REL_TOL
+        assert grad_err(o, ref) <= 1e-5
     assert torch.all(o0[:, :, :45] == 0) and torch.all(o0[:, :, -45:] == 0) and torch.all(o0[..., :20] == 0)
 
 
