@@ -155,6 +155,33 @@ int nconv_b200_bn_fold(const float* gamma, const float* beta, const float* mean,
                        const float* conv_bias, float* scale, float* shift, int C, float eps,
                        void* stream);
 
+/* ---- tensor-core path of the RGB-guided stack (step2.py ConvBlock :290-297, Basic2d :178-195) --
+ * Activations in "P8": [B][ceil(C/8)][hi|lo][H+2][W+2][8] bf16 with a one-pixel zero ring (see
+ * csrc/p8.cuh); buffers are nconv_b200_p8_bytes() long (includes tail slack that tile loads may
+ * over-read).  pack/unpack convert from/to contiguous fp32 NCHW (pack also writes the zero ring);
+ * kernels write interior pixels only, zero_ring re-establishes the ring of a reused buffer. */
+size_t nconv_b200_p8_bytes(int B, int C, int H, int W);
+int nconv_b200_p8_pack(const float* x, void* p8, int B, int C, int H, int W, void* stream);
+int nconv_b200_p8_unpack(const void* p8, float* x, int B, int C, int H, int W, void* stream);
+int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream);
+
+/* weights [CO][CI][3][3] fp32 -> per-K-stage packed split-bf16 image consumed by conv3x3_tc */
+size_t nconv_b200_tc_wpack_bytes(int CO, int CI);
+int nconv_b200_tc_pack_weights(const float* w, void* wpack, int CO, int CI, void* stream);
+
+/* y = act(scale[o]*conv3x3(cat[a,b]) + shift[o]), stride 1, pad 1, tcgen05 bf16x3 (fp32-class
+ * accuracy).  CA, CB multiples of 16; CO in {32, 64}.  a, b, y are P8 buffers. */
+typedef struct {
+  const void* a;        /* P8 [B,CA,H,W]                                       */
+  const void* b;        /* P8 [B,CB,H,W] concatenated after a, or NULL         */
+  const void* wpack;    /* nconv_b200_tc_pack_weights(w [CO][CA+CB][3][3])     */
+  const float* scale;   /* [CO] or NULL (=1)                                   */
+  const float* shift;   /* [CO] or NULL (=0)                                   */
+  void* y;              /* P8 [B,CO,H,W]                                       */
+  int B, CA, CB, CO, H, W, relu;
+} nconv_b200_tc_desc;
+int nconv_b200_conv3x3_tc(const nconv_b200_tc_desc* d, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

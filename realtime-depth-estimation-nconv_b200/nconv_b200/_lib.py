@@ -38,6 +38,15 @@ class ConvDesc(Structure):
     ]
 
 
+class TcDesc(Structure):
+    """nconv_b200_tc_desc"""
+    _fields_ = [
+        ("a", c_void_p), ("b", c_void_p), ("wpack", c_void_p), ("scale", c_void_p), ("shift", c_void_p),
+        ("y", c_void_p),
+        ("B", c_int), ("CA", c_int), ("CB", c_int), ("CO", c_int), ("H", c_int), ("W", c_int), ("relu", c_int),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/nconv_b200.h declares
 SIGNATURES = {
     "nconv_b200_abi_version": (c_int, []),
@@ -65,6 +74,13 @@ SIGNATURES = {
     "nconv_b200_bilinear_ac_fwd": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p]),
     "nconv_b200_zero_border": (c_int, [c_void_p] + [c_int] * 6 + [c_void_p]),
     "nconv_b200_bn_fold": (c_int, [c_void_p] * 7 + [c_int, c_float, c_void_p]),
+    "nconv_b200_p8_bytes": (c_size_t, [c_int] * 4),
+    "nconv_b200_p8_pack": (c_int, [c_void_p, c_void_p] + [c_int] * 4 + [c_void_p]),
+    "nconv_b200_p8_unpack": (c_int, [c_void_p, c_void_p] + [c_int] * 4 + [c_void_p]),
+    "nconv_b200_p8_zero_ring": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p]),
+    "nconv_b200_tc_wpack_bytes": (c_size_t, [c_int, c_int]),
+    "nconv_b200_tc_pack_weights": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "nconv_b200_conv3x3_tc": (c_int, [POINTER(TcDesc), c_void_p]),
 }
 
 _lib = None

@@ -13,7 +13,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import ConvDesc, FwdDesc, check
+from ._lib import ConvDesc, FwdDesc, TcDesc, check
 
 _C = _lib.load()
 
@@ -379,6 +379,67 @@ def _bn_fold(gamma, beta, mean, var, conv_bias, eps: float):
 
 _define("bn_fold(Tensor gamma, Tensor beta, Tensor mean, Tensor var, Tensor? conv_bias, float eps) -> (Tensor, Tensor)",
         _bn_fold, lambda gamma, beta, mean, var, conv_bias, eps: (torch.empty_like(gamma), torch.empty_like(gamma)))
+
+
+# --------------------------------------------------------------------------------------
+# tensor-core path: P8 activations + tcgen05 bf16x3 3x3 convolution
+# --------------------------------------------------------------------------------------
+class P8:
+    """A [B,C,H,W] activation held in the P8 device layout (csrc/p8.cuh).  `buf` is a uint8 CUDA
+    tensor of nconv_b200_p8_bytes(); kernels read and write it through raw pointers."""
+    __slots__ = ("buf", "B", "C", "H", "W")
+
+    def __init__(self, buf, B, C, H, W):
+        self.buf, self.B, self.C, self.H, self.W = buf, B, C, H, W
+
+    @staticmethod
+    def empty(B, C, H, W, device, zero_ring=True):
+        n = int(_C.nconv_b200_p8_bytes(B, C, H, W))
+        t = P8(torch.empty(n, device=device, dtype=torch.uint8), B, C, H, W)
+        if zero_ring:
+            with torch.cuda.device(device):
+                check(_C.nconv_b200_p8_zero_ring(_p(t.buf), B, C, H, W, _stream(t.buf)), "p8_zero_ring")
+        return t
+
+    @staticmethod
+    def pack(x):
+        x = _prep(x, "x")
+        B, C, H, W = x.shape
+        t = P8.empty(B, C, H, W, x.device, zero_ring=False)
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_p8_pack(_p(x), _p(t.buf), B, C, H, W, _stream(x)), "p8_pack")
+        return t
+
+    def unpack(self):
+        x = torch.empty((self.B, self.C, self.H, self.W), device=self.buf.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_p8_unpack(_p(self.buf), _p(x), self.B, self.C, self.H, self.W, _stream(x)), "p8_unpack")
+        return x
+
+
+def tc_pack_weights(weight):
+    weight = _prep(weight, "weight")
+    CO, CI, kh, kw = weight.shape
+    if (kh, kw) != (3, 3) or CI % 16:
+        raise ValueError("tc_pack_weights: weight must be [CO, CI%16==0, 3, 3]")
+    wp = torch.empty(int(_C.nconv_b200_tc_wpack_bytes(CO, CI)), device=weight.device, dtype=torch.uint8)
+    with torch.cuda.device(weight.device):
+        check(_C.nconv_b200_tc_pack_weights(_p(weight), _p(wp), CO, CI, _stream(weight)), "tc_pack_weights")
+    return wp
+
+
+def conv3x3_tc(a: "P8", b, wpack, CO: int, scale, shift, relu: bool, out=None) -> "P8":
+    """y = act(scale*conv3x3(cat[a,b]) + shift) on the tcgen05 path; a, b, y are P8."""
+    CB = 0 if b is None else b.C
+    if b is not None and (b.B, b.H, b.W) != (a.B, a.H, a.W):
+        raise ValueError("conv3x3_tc: source shape mismatch")
+    scale = _prep_opt(scale, "scale"); shift = _prep_opt(shift, "shift")
+    y = out if out is not None else P8.empty(a.B, CO, a.H, a.W, a.buf.device)
+    d = TcDesc(_p(a.buf), None if b is None else _p(b.buf), _p(wpack), _p(scale), _p(shift), _p(y.buf),
+               a.B, a.C, CB, CO, a.H, a.W, int(relu))
+    with torch.cuda.device(a.buf.device):
+        check(_C.nconv_b200_conv3x3_tc(byref(d), _stream(a.buf)), "conv3x3_tc")
+    return y
 
 
 def launch_count() -> int:

@@ -334,3 +334,56 @@ def test_setp2_train_mode_bn_raises():
     enc = RGBEncoder(3, 32, 1).to(dev()).train()
     with pytest.raises(NotImplementedError):
         enc(torch.rand(1, 3, 8, 8, device=dev()))
+
+
+# ---------------------------------------------------------------------------------------------
+# tensor-core path: P8 layout round trip and the tcgen05 bf16x3 conv3x3 vs fp64 F.conv2d
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(2, 5, 7, 9), (1, 32, 16, 24), (2, 64, 33, 70)])
+def test_p8_roundtrip(shape):
+    from nconv_b200.ops import P8
+    torch.manual_seed(3)
+    x = (torch.randn(*shape) * 10).to(dev())
+    y = P8.pack(x).unpack()
+    # hi+lo bf16 keeps 16 mantissa bits
+    assert O.max_rel_err(y, x, floor=1e-6) <= 2.0 ** -16
+
+
+@pytest.mark.parametrize("cfg", [
+    # CA, CB, CO, B, H, W, relu, affine
+    (32, 0, 32, 2, 24, 80, True, True),
+    (64, 0, 64, 1, 12, 80, True, False),
+    (64, 64, 64, 2, 30, 40, True, True),
+    (32, 32, 32, 1, 37, 101, False, True),       # ragged: partial tiles in both directions
+    (64, 0, 32, 1, 60, 80, True, False),
+    (32, 0, 32, 1, 5, 7, True, True),            # smaller than one tile
+])
+def test_conv3x3_tc_vs_fp64(cfg):
+    from nconv_b200.ops import P8, tc_pack_weights, conv3x3_tc
+    CA, CB, CO, B, H, W, relu, affine = cfg
+    g = torch.Generator().manual_seed(sum(cfg[:6]))
+    a = torch.randn(B, CA, H, W, generator=g) * 3
+    b = torch.randn(B, CB, H, W, generator=g) * 3 if CB else None
+    w = torch.randn(CO, CA + CB, 3, 3, generator=g) / (3 * (CA + CB) ** 0.5)
+    scale = torch.rand(CO, generator=g) + 0.5 if affine else None
+    shift = torch.randn(CO, generator=g)
+    x = a if b is None else torch.cat((a, b), 1)
+    ref = F.conv2d(x.double(), w.double(), padding=1)
+    if scale is not None:
+        ref = ref * scale.double().view(1, -1, 1, 1)
+    ref = ref + shift.double().view(1, -1, 1, 1)
+    if relu:
+        ref = ref.relu()
+    pa = P8.pack(a.to(dev()))
+    pb = P8.pack(b.to(dev())) if b is not None else None
+    wp = tc_pack_weights(w.to(dev()))
+    y = conv3x3_tc(pa, pb, wp, CO, None if scale is None else scale.to(dev()), shift.to(dev()), relu)
+    out = y.unpack()
+    torch.cuda.synchronize()
+    # bf16x3: fp32-class accuracy, stated as 2e-5 of the output scale (fp32 conv itself is ~1e-6)
+    assert grad_err(out, ref) <= 2e-5
+    # the zero ring of the output must be intact (kernels write interior pixels only)
+    raw = y.buf[: 2 * ((CO + 7) // 8) * B * (H + 2) * (W + 2) * 16].view(torch.bfloat16)
+    raw = raw.view(B, CO // 8, 2, H + 2, W + 2, 8).float()
+    assert float(raw[:, :, :, 0].abs().max()) == 0 and float(raw[:, :, :, -1].abs().max()) == 0
+    assert float(raw[:, :, :, :, 0].abs().max()) == 0 and float(raw[:, :, :, :, -1].abs().max()) == 0
