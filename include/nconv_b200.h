@@ -165,22 +165,38 @@ int nconv_b200_p8_pack(const float* x, void* p8, int B, int C, int H, int W, voi
 int nconv_b200_p8_unpack(const void* p8, float* x, int B, int C, int H, int W, void* stream);
 int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream);
 
-/* weights [CO][CI][3][3] fp32 -> per-K-stage packed split-bf16 image consumed by conv3x3_tc */
-size_t nconv_b200_tc_wpack_bytes(int CO, int CI);
-int nconv_b200_tc_pack_weights(const float* w, void* wpack, int CO, int CI, void* stream);
+/* P8Q: the four spatial phases of an activation, for stride-2 consumers (csrc/p8.cuh). */
+size_t nconv_b200_p8q_bytes(int B, int C, int H, int W);
+int nconv_b200_p8q_zero_ring(void* p8q, int B, int C, int H, int W, void* stream);
+int nconv_b200_p8q_pack(const float* x, void* p8q, int B, int C, int H, int W, void* stream);
 
-/* y = act(scale[o]*conv3x3(cat[a,b]) + shift[o]), stride 1, pad 1, tcgen05 bf16x3 (fp32-class
- * accuracy).  CA, CB multiples of 16; CO in {32, 64}.  a, b, y are P8 buffers. */
+/* Tensor-core convolution modes */
+#define NCONV_B200_TC_S1 0 /* 3x3 stride 1 pad 1: ConvBlock step2.py:290-297, Basic2d :178-195       */
+#define NCONV_B200_TC_S2 1 /* 3x3 stride 2 pad 1 (+1x1 stride 2 residual): RGBEncoder :134-154       */
+#define NCONV_B200_TC_T 2  /* ConvTranspose2d 4x4 stride 2 pad 1: Basic2dTrans :197-214             */
+
+/* weights -> per-K-stage packed split-bf16 image consumed by conv_tc.
+ *   S1: w [CO][CA+CB][3][3];  S2: w [CO][CA+CB][3][3] and optionally w1 [CO][CA+CB][1][1];
+ *   T : w [CA+CB][CO][4][4] (CA == 1: the lone depth channel of cat[depth, features]). */
+size_t nconv_b200_tc_wpack_bytes(int mode, int CO, int CA, int CB, int has_1x1);
+int nconv_b200_tc_pack_weights(int mode, const float* w, const float* w1, void* wpack, int CO, int CA,
+                               int CB, void* stream);
+
+/* y = act(scale[o]*conv(cat[a,b]) + shift[o]) (+ conv1x1_s2(cat[a,b]) in mode S2 with has_1x1),
+ * tcgen05 bf16x3 (fp32-class accuracy).  CA, CB multiples of 16 (mode T: CA may be 1); CO in
+ * {32, 64}.  a, b: P8 (S1, T) or P8Q (S2) of size H x W; y: P8 of the output size (S1: HxW,
+ * S2: H/2 x W/2, T: 2H x 2W); yq: optional P8Q copy of y for a stride-2 consumer. */
 typedef struct {
-  const void* a;        /* P8 [B,CA,H,W]                                       */
-  const void* b;        /* P8 [B,CB,H,W] concatenated after a, or NULL         */
-  const void* wpack;    /* nconv_b200_tc_pack_weights(w [CO][CA+CB][3][3])     */
+  const void* a;
+  const void* b;        /* concatenated after a, or NULL                        */
+  const void* wpack;
   const float* scale;   /* [CO] or NULL (=1)                                   */
   const float* shift;   /* [CO] or NULL (=0)                                   */
-  void* y;              /* P8 [B,CO,H,W]                                       */
-  int B, CA, CB, CO, H, W, relu;
+  void* y;
+  void* yq;             /* or NULL                                             */
+  int B, CA, CB, CO, H, W, relu, mode, has_1x1;
 } nconv_b200_tc_desc;
-int nconv_b200_conv3x3_tc(const nconv_b200_tc_desc* d, void* stream);
+int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream);
 
 #ifdef __cplusplus
 }

@@ -35,6 +35,28 @@ struct P8Geom {
   __host__ __device__ size_t total_elems() const { return (size_t)B * C8 * 2 * plane_elems(); }
 };
 
+
+// "P8Q": the same activation split into its four spatial phases, for stride-2 consumers
+// (RGBEncoder's 3x3/s2 and 1x1/s2 convolutions, step2.py:134-154).  H and W even:
+//
+//     p8q[n][chunk][part][phase = (y&1)*2 + (x&1)][1 + y/2][1 + x/2][c%8],  planes (H/2+1) x (W/2+1)
+//
+// Row 0 and column 0 of every plane are zero (the pad-1 halo of a stride-2 3x3 only ever reaches
+// one pixel up/left in phase space), so a stride-2 tap is again "phase plane + flat pixel shift".
+struct P8QGeom {
+  int B, C8, Hq1, Wq1;
+  __host__ __device__ static P8QGeom make(int B, int C, int H, int W) {
+    P8QGeom g; g.B = B; g.C8 = (C + 7) / 8; g.Hq1 = H / 2 + 1; g.Wq1 = W / 2 + 1; return g;
+  }
+  __host__ __device__ size_t phase_elems() const { return (size_t)Hq1 * Wq1 * 8; }
+  __host__ __device__ size_t slab_elems() const { return 4 * phase_elems(); }
+  __host__ __device__ size_t slab(int n, int chunk, int part) const { return (((size_t)n * C8 + chunk) * 2 + part) * slab_elems(); }
+  __host__ __device__ size_t pixel(int y, int x) const {   // full-resolution interior coords
+    return (size_t)((y & 1) * 2 + (x & 1)) * phase_elems() + ((size_t)((y >> 1) + 1) * Wq1 + ((x >> 1) + 1)) * 8;
+  }
+  __host__ __device__ size_t total_elems() const { return (size_t)B * C8 * 2 * slab_elems(); }
+};
+
 constexpr size_t P8_TAIL_SLACK_BYTES = 8192;   // tile loads may over-read one staged row past the end
 
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {

@@ -1,131 +1,97 @@
-// tcgen05 implicit-GEMM 3x3 / stride-1 / pad-1 convolution for the dense layers of the RGB-guided
-// stack (/root/reference/models/step2.py: ConvBlock :290-297, Basic2d :178-195 — the 19 layers
-// with Ci in {32,64,128} and Co in {32,64} that hold 92 % of SETP2's flops).
+// tcgen05 implicit-GEMM convolutions for the dense layers of the RGB-guided stack
+// (/root/reference/models/step2.py): 98.8 % of SETP2's flops are convolutions with Ci,Co >= 32
+// (SURVEY App. A table 2).  One kernel, three tap tables:
 //
-//   y = act(scale[o] * conv3x3(cat[a, b]) + shift[o])            (scale/shift: folded eval BN or bias)
+//   S1  3x3 / stride 1 / pad 1         ConvBlock :290-297, Basic2d :178-195 (two-source concat)
+//   S2  3x3 / stride 2 / pad 1 (+ the 1x1 / stride 2 residual branch)      RGBEncoder :134-154
+//   T   ConvTranspose2d 4x4 / stride 2 / pad 1 as four sub-pixel 2x2 convolutions
+//                                                                          Basic2dTrans :197-214
 //
-// Arithmetic: bf16x3 split precision.  Activations live in P8 (p8.cuh: hi/lo bf16, 16 mantissa
+//   y = act(scale[o] * conv(cat[a, b]) + shift[o]) (+ conv1x1_s2(cat[a, b]) for S2)
+//
+// Arithmetic: bf16x3 split precision.  Activations live in P8 / P8Q (p8.cuh: hi/lo bf16, 16 mantissa
 // bits), weights are split the same way, and every K=16 slice issues three tcgen05.mma
-// (hi*hi + lo*hi + hi*lo) into one fp32 TMEM accumulator: ~2^-17 relative per product, i.e. fp32-class
-// results (parity bound 1e-4, measured in tests/test_gpu_parity.py) at 1/3 of the bf16 tensor rate.
+// (hi*hi + lo*hi + hi*lo) into one fp32 TMEM accumulator: ~2^-17 relative per product, i.e.
+// fp32-class results (parity bound 1e-4, measured in tests/test_gpu_parity.py) at 1/3 of the bf16
+// tensor rate.
 //
 // Structure (one persistent CTA per SM, 192 threads, warp-specialised):
-//   warp 0     producer: per K-stage (16 input channels) bulk-copies (cp.async.bulk, TMA engine,
-//              mbarrier complete_tx) the halo tile rows of the 2x2 (hi|lo x chunk) planes and the
-//              stage's packed weights into a 2-deep shared-memory ring
-//   warp 1     one thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128 pixels, N=Co, K=16):
-//              the CTA tile is R rows x Wt columns of outputs, laid out FLAT in shared memory with
-//              row pitch P = Wt+2, so 128 consecutive staged pixels are one A tile and tap (u,v) is
-//              the descriptor start address + (u*P+v)*16 B.  Halo columns produce garbage rows
-//              that the epilogue drops (2/P of the MMA rows).
+//   warp 0     producer: per K-stage (16 input channels) bulk-copies (cp.async.bulk on the TMA
+//              engine, mbarrier complete_tx) the halo rows of the staged planes and the stage's
+//              packed weights into a 2-deep shared-memory ring
+//   warp 1     one thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128 anchors, N=Co, K=16).
+//              The CTA tile is R rows x Wt columns of anchors (output pixels; input pixels for T)
+//              staged FLAT with row pitch P = Wt+2, so 128 consecutive staged pixels are one
+//              K-major no-swizzle A tile and a tap is "descriptor start address + shift*16 B"
+//              (implicit im2col; for S2 the shift is taken inside one of the four phase planes).
+//              Halo columns yield garbage rows that the epilogue drops (2/P of the MMA rows).
 //   warps 2-5  epilogue: tcgen05.ld the fp32 accumulators (double-buffered in TMEM so the next
-//              tile's MMAs overlap), scale/shift/ReLU, split to hi/lo bf16, 16-byte coalesced
-//              stores into the P8 output.
+//              tile's MMAs overlap), scale/shift/ReLU (+ residual accumulator), split to hi/lo
+//              bf16, 16-byte stores into the P8 output (and its P8Q copy for a stride-2 consumer).
 #include "common.cuh"
 #include "launch_count.h"
 #include "nconv_b200.h"
 #include "p8.cuh"
+#include "tc_ptx.cuh"
 #include <cstdio>
 
 namespace nconv {
 
 constexpr int TC_THREADS = 192;
 constexpr int TC_STAGES = 2;
-constexpr int TC_SMEM_MAX = 227 * 1024 - 1024;   // dynamic part; static barriers take the rest
+constexpr int TC_SMEM_MAX = 227 * 1024 - 1024;   // dynamic part; static barriers etc. take the rest
+constexpr int TC_MAX_TAPS = 17;
 
-struct TcArgs {
-  const __nv_bfloat16* src[2];  // P8 sources (src[1] may be null)
-  int c8[2];                    // chunks (planes/2) per image of each source
-  int pairs[2];                 // 16-channel K-stages taken from each source
-  const __nv_bfloat16* wpack;   // [kstage][tap][part][j][CO][8]
-  const float* scale;           // [CO] or null
-  const float* shift;           // [CO] or null
-  __nv_bfloat16* out;           // P8 [B][CO/8][2][Hp][Wp][8]
-  int B, H, W, Hp, Wp;
-  int R, Wt, P, T, rows_alloc;  // tile: R x Wt outputs, pitch P, T M-tiles of 128, staged rows
-  int tiles_x, tiles_y, ntiles;
-  int relu;
+enum { TC_S1 = 0, TC_S2 = 1, TC_T = 2 };
+
+struct TcTap {
+  uint32_t a_off;   // byte offset of the tap's hi A tile inside a stage (plane group base + shift*16)
+  uint16_t w_idx;   // weight tap block inside the stage's packed weights
+  uint8_t dgrp;     // accumulator group
+  uint8_t first;    // first tap into its accumulator group (overwrites at K-stage 0)
 };
 
-// ---- PTX wrappers -----------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-  return ok;
-}
-// Bounded wait: a protocol bug must fault (trap -> launch error), never hang the GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 22)) __trap();
-  }
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// K-major, no-swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
-// rows of 16 B, 8-row core matrices `sbo` bytes apart, the two K-chunks of a K=16 slice `lbo` apart.
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
-         ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | ((uint64_t)1 << 46);
-}
+struct TcArgs {
+  const __nv_bfloat16* src[2];  // sources (P8, or P8Q for S2); src[1] may be null
+  int c8[2];                    // chunks per image of each source (1: a lone channel, duplicated as both K-chunks)
+  int pairs[2];                 // K-stages (16 channels) taken from each source
+  size_t slab_elems;            // elements per (n, chunk, part) slab of a source
+  size_t grp_elems;             // elements per plane group inside a slab (P8Q phase plane)
+  int src_pitch, src_rows;      // source plane geometry (pixels per row, rows)
+  const __nv_bfloat16* wpack;   // [kstage][wtap][part][j][CO][8]
+  const float* scale;           // [CO] or null
+  const float* shift;           // [CO] or null
+  __nv_bfloat16* out;           // P8 [B][CO/8][2][OH+2][OW+2][8]
+  __nv_bfloat16* outq;          // optional P8Q copy of the output
+  int B, AH, AW, OH, OW;        // anchor grid and output size
+  int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, ntaps, ntaps_w;
+  int tiles_x, tiles_y, ntiles;
+  int relu, mode;
+  TcTap taps[TC_MAX_TAPS];
+};
 
 template <int N>
-__global__ void __launch_bounds__(TC_THREADS, 1) conv3x3_tc_kernel(const TcArgs a) {
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_full[TC_STAGES], s_empty[TC_STAGES], s_tfull[2], s_tempty[2];
   __shared__ uint32_t s_tmem_base;
+  __shared__ TcTap s_taps[TC_MAX_TAPS];
+  __shared__ float s_scale[N], s_shift[N];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t a_plane_bytes = (uint32_t)a.rows_alloc * a.P * 16;       // one (part, j) plane
-  const uint32_t a_stage_bytes = 4 * a_plane_bytes;
+  const uint32_t a_plane_bytes = (uint32_t)a.rows_alloc * a.P * 16;       // one (group, part, j) plane
+  const uint32_t a_stage_bytes = (uint32_t)a.G * 4 * a_plane_bytes;
   constexpr uint32_t B_TAP_BYTES = 2 * 2 * N * 16;                        // [part][j][N][16 B]
-  constexpr uint32_t B_STAGE_BYTES = 9 * B_TAP_BYTES;
-  const uint32_t stage_bytes = a_stage_bytes + B_STAGE_BYTES;
+  const uint32_t b_stage_bytes = (uint32_t)a.ntaps_w * B_TAP_BYTES;
+  const uint32_t stage_bytes = a_stage_bytes + b_stage_bytes;
   const uint32_t smem_base = smem_u32(smem);
   const int nk = a.pairs[0] + a.pairs[1];
 
+  if (threadIdx.x < a.ntaps) s_taps[threadIdx.x] = a.taps[threadIdx.x];
+  if (threadIdx.x < N) {
+    s_scale[threadIdx.x] = a.scale ? __ldg(a.scale + threadIdx.x) : 1.f;
+    s_shift[threadIdx.x] = a.shift ? __ldg(a.shift + threadIdx.x) : 0.f;
+  }
   if (threadIdx.x == 0) {
     for (int s = 0; s < TC_STAGES; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 4); }
@@ -143,30 +109,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv3x3_tc_kernel(const TcArgs 
   if (warp == 0) {
     // ===================== producer =====================
     uint32_t stage = 0, phase = 0;
+    const uint32_t row_bytes = (uint32_t)a.P * 16;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
       const int tx = tile % a.tiles_x, ty = (tile / a.tiles_x) % a.tiles_y, n = tile / (a.tiles_x * a.tiles_y);
-      const int y0 = ty * a.R, x0 = tx * a.Wt;                 // padded coords of the first staged row / col
-      int nrow = a.R + 2;
-      if (y0 + nrow > a.Hp) nrow = a.Hp - y0;
-      const uint32_t row_bytes = (uint32_t)a.P * 16;
+      const int y0 = ty * a.R, x0 = tx * a.Wt;                 // plane coords of the first staged row / col
+      int nrow = a.rows_ld;
+      if (y0 + nrow > a.src_rows) nrow = a.src_rows - y0;
+      const int ncopy = a.G * 4 * nrow;
       for (int k = 0; k < nk; ++k) {
         const int si = (k < a.pairs[0]) ? 0 : 1;
-        const int c0 = 2 * (si == 0 ? k : k - a.pairs[0]);
+        const bool lone = a.c8[si] == 1;
+        const int c0 = lone ? 0 : 2 * (si == 0 ? k : k - a.pairs[0]);
         mbar_wait(smem_u32(&s_empty[stage]), phase ^ 1);
         const uint32_t full = smem_u32(&s_full[stage]);
         const uint32_t sa = smem_base + stage * stage_bytes;
         if (lane == 0) {
-          mbar_arrive_expect_tx(full, 4u * nrow * row_bytes + B_STAGE_BYTES);
-          bulk_g2s(sa + a_stage_bytes, a.wpack + (size_t)k * (B_STAGE_BYTES / 2), B_STAGE_BYTES, full);
+          mbar_arrive_expect_tx(full, (uint32_t)ncopy * row_bytes + b_stage_bytes);
+          bulk_g2s(sa + a_stage_bytes, a.wpack + (size_t)k * (b_stage_bytes / 2), b_stage_bytes, full);
         }
         __syncwarp();
-        const size_t plane_elems = (size_t)a.Hp * a.Wp * 8;
-        for (int i = lane; i < 4 * nrow; i += 32) {
-          const int pj = i / nrow, r = i - pj * nrow;          // pj = part*2 + j
-          const int part = pj >> 1, j = pj & 1;
-          const __nv_bfloat16* g = a.src[si] + (((size_t)n * a.c8[si] + c0 + j) * 2 + part) * plane_elems +
-                                   ((size_t)(y0 + r) * a.Wp + x0) * 8;
-          bulk_g2s(sa + pj * a_plane_bytes + r * row_bytes, g, row_bytes, full);
+        for (int i = lane; i < ncopy; i += 32) {
+          const int pl = i / nrow, r = i - pl * nrow;          // pl = (g*2 + part)*2 + j
+          const int j = pl & 1, part = (pl >> 1) & 1, g = pl >> 2;
+          const int chunk = lone ? 0 : c0 + j;
+          const __nv_bfloat16* gp = a.src[si] + (((size_t)n * a.c8[si] + chunk) * 2 + part) * a.slab_elems +
+                                    (size_t)g * a.grp_elems + ((size_t)(y0 + r) * a.src_pitch + x0) * 8;
+          bulk_g2s(sa + pl * a_plane_bytes + r * row_bytes, gp, row_bytes, full);
         }
         __syncwarp();
         if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
@@ -187,20 +155,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv3x3_tc_kernel(const TcArgs 
           const uint32_t sa = smem_base + stage * stage_bytes;
           const uint32_t sb = sa + a_stage_bytes;
           for (int t = 0; t < a.T; ++t) {
-            const uint32_t d = tmem_base + buf * 256 + t * N;
-            uint32_t acc = (k > 0) ? 1u : 0u;
-#pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const int u = tap / 3, v = tap - 3 * u;
-              const uint32_t aoff = (uint32_t)(u * a.P + v + t * 128) * 16;
-              const uint64_t a_hi = umma_desc(sa + aoff, a_plane_bytes, 128);
-              const uint64_t a_lo = umma_desc(sa + 2 * a_plane_bytes + aoff, a_plane_bytes, 128);
-              const uint64_t b_hi = umma_desc(sb + tap * B_TAP_BYTES, N * 16, 128);
-              const uint64_t b_lo = umma_desc(sb + tap * B_TAP_BYTES + 2 * N * 16, N * 16, 128);
-              umma_bf16(d, a_hi, b_hi, IDESC, acc);
+            for (int i = 0; i < a.ntaps; ++i) {
+              const TcTap tp = s_taps[i];
+              const uint32_t d = tmem_base + buf * 256 + (tp.dgrp * a.T + t) * N;
+              const uint32_t aaddr = sa + tp.a_off + (uint32_t)t * 128 * 16;
+              const uint64_t a_hi = umma_desc(aaddr, a_plane_bytes, 128);
+              const uint64_t a_lo = umma_desc(aaddr + 2 * a_plane_bytes, a_plane_bytes, 128);
+              const uint32_t baddr = sb + tp.w_idx * B_TAP_BYTES;
+              const uint64_t b_hi = umma_desc(baddr, N * 16, 128);
+              const uint64_t b_lo = umma_desc(baddr + 2 * N * 16, N * 16, 128);
+              umma_bf16(d, a_hi, b_hi, IDESC, (k > 0 || !tp.first) ? 1u : 0u);
               umma_bf16(d, a_lo, b_hi, IDESC, 1u);
               umma_bf16(d, a_hi, b_lo, IDESC, 1u);
-              acc = 1u;
             }
           }
           umma_commit(smem_u32(&s_empty[stage]));                       // frees the smem slot when the MMAs retire
@@ -214,42 +180,53 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv3x3_tc_kernel(const TcArgs 
     // ===================== epilogue (warps 2..5) =====================
     const int q = warp & 3;                                    // TMEM lane quarter this warp may access
     uint32_t it = 0;
-    const size_t plane_elems = (size_t)a.Hp * a.Wp * 8;
+    const size_t oplane = (size_t)(a.OH + 2) * (a.OW + 2) * 8;
+    const P8QGeom qg = P8QGeom::make(a.B, N, a.OH, a.OW);
+    const int nphase = (a.mode == TC_T) ? 4 : 1;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
       const int tx = tile % a.tiles_x, ty = (tile / a.tiles_x) % a.tiles_y, n = tile / (a.tiles_x * a.tiles_y);
-      const int y0 = ty * a.R, x0 = tx * a.Wt;
       mbar_wait(smem_u32(&s_tfull[buf]), tphase);
       tc_fence_after();
       for (int t = 0; t < a.T; ++t) {
-        const int m = t * 128 + q * 32 + lane;                 // flat staged position of this thread's pixel
+        const int m = t * 128 + q * 32 + lane;                 // flat staged position of this thread's anchor
         const int r = m / a.P, c = m - r * a.P;
-        const int oy = y0 + r, ox = x0 + c;
-        const bool valid = (r < a.R) && (c < a.Wt) && (oy < a.H) && (ox < a.W);
-        __nv_bfloat16* obase = a.out + ((size_t)n * (N / 8) * 2) * plane_elems + ((size_t)(oy + 1) * a.Wp + (ox + 1)) * 8;
+        const int ay = ty * a.R + r, ax = tx * a.Wt + c;
+        const bool valid = (r < a.R) && (c < a.Wt) && (ay < a.AH) && (ax < a.AW);
+        for (int ph = 0; ph < nphase; ++ph) {
+          const int oy = (a.mode == TC_T) ? 2 * ay + (ph >> 1) : ay;
+          const int ox = (a.mode == TC_T) ? 2 * ax + (ph & 1) : ax;
+          __nv_bfloat16* obase = a.out + ((size_t)n * (N / 8) * 2) * oplane + ((size_t)(oy + 1) * (a.OW + 2) + (ox + 1)) * 8;
+          const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256;
 #pragma unroll
-        for (int cb = 0; cb < N / 32; ++cb) {
-          uint32_t v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256 + t * N + cb * 32, v);
-          tmem_ld_wait();
-          if (valid) {
+          for (int cb = 0; cb < N / 32; ++cb) {
+            uint32_t v[32], w[32];
+            tmem_ld32(tcol + (ph * a.T + t) * N + cb * 32, v);
+            if (a.ngrp == 2) tmem_ld32(tcol + (a.T + t) * N + cb * 32, w);      // S2 residual branch
+            tmem_ld_wait();
+            if (valid) {
 #pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
-              float f[8];
+              for (int ch = 0; ch < 4; ++ch) {
+                float f[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                const int o = cb * 32 + ch * 8 + e;
-                float x = __uint_as_float(v[ch * 8 + e]);
-                const float sc = a.scale ? __ldg(a.scale + o) : 1.f;
-                const float sh = a.shift ? __ldg(a.shift + o) : 0.f;
-                x = fmaf(x, sc, sh);
-                f[e] = a.relu ? fmaxf(x, 0.f) : x;
+                for (int e = 0; e < 8; ++e) {
+                  const int o = cb * 32 + ch * 8 + e;
+                  float x = fmaf(__uint_as_float(v[ch * 8 + e]), s_scale[o], s_shift[o]);
+                  if (a.relu) x = fmaxf(x, 0.f);
+                  if (a.ngrp == 2) x += __uint_as_float(w[ch * 8 + e]);
+                  f[e] = x;
+                }
+                uint4 hi, lo;
+                split8(f, hi, lo);
+                __nv_bfloat16* p = obase + (size_t)(cb * 4 + ch) * 2 * oplane;
+                *reinterpret_cast<uint4*>(p) = hi;
+                *reinterpret_cast<uint4*>(p + oplane) = lo;
+                if (a.outq) {
+                  __nv_bfloat16* pq = a.outq + qg.slab(n, cb * 4 + ch, 0) + qg.pixel(oy, ox);
+                  *reinterpret_cast<uint4*>(pq) = hi;
+                  *reinterpret_cast<uint4*>(pq + qg.slab_elems()) = lo;
+                }
               }
-              uint4 hi, lo;
-              split8(f, hi, lo);
-              __nv_bfloat16* p = obase + (size_t)(cb * 4 + ch) * 2 * plane_elems;
-              *reinterpret_cast<uint4*>(p) = hi;
-              *reinterpret_cast<uint4*>(p + plane_elems) = lo;
             }
           }
         }
@@ -268,110 +245,72 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv3x3_tc_kernel(const TcArgs 
   }
 }
 
-// ---- weight packing: w [CO][CI][3][3] fp32 -> [kstage][tap][part][j][CO][8] split bf16 -----------
-__global__ void tc_pack_weights_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int CO, int CI) {
-  const int total = (CI / 16) * 9 * 2 * CO * 8;   // (kstage, tap, j, co, e); both parts written together
+}  // namespace nconv
+
+namespace nconv {
+
+// ---- weight packing -> [kstage][wtap][part][j][CO][8] split bf16 -----------------------------------
+//   S1: w [CO][CI][3][3]                     9 taps
+//   S2: w [CO][CI][3][3] (+ w1 [CO][CI] 1x1) 9 (+1) taps
+//   T : w [CI][CO][4][4]                     16 taps; `lead` leading input channels (the depth channel of
+//       cat[depth, features], step2.py:174) take a K-stage of their own, zero-filled to 16.
+__global__ void tc_pack_weights_kernel(const float* __restrict__ w, const float* __restrict__ w1,
+                                       __nv_bfloat16* __restrict__ wp, int CO, int CI, int mode, int lead,
+                                       int nstage, int ntw) {
+  const int total = nstage * ntw * 2 * CO * 8;   // (kstage, wtap, j, co, e); both parts written together
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
     int e = idx & 7;
     int r = idx >> 3;
     int co = r % CO; r /= CO;
     int j = r & 1; r >>= 1;
-    int tap = r % 9;
-    int ks = r / 9;
-    const int ci = ks * 16 + j * 8 + e;
+    int wt = r % ntw;
+    int ks = r / ntw;
+    int ci;
+    if (lead && ks < lead) ci = (j == 0 && e == 0) ? ks : -1;
+    else ci = lead + (ks - lead) * 16 + j * 8 + e;
+    float v = 0.f;
+    if (ci >= 0 && ci < CI) {
+      if (mode == TC_T) v = __ldg(w + ((size_t)ci * CO + co) * 16 + wt);
+      else if (wt < 9) v = __ldg(w + ((size_t)co * CI + ci) * 9 + wt);
+      else v = __ldg(w1 + (size_t)co * CI + ci);
+    }
     __nv_bfloat16 hi, lo;
-    split_bf16(__ldg(w + ((size_t)co * CI + ci) * 9 + tap), hi, lo);
-    const size_t base = ((size_t)(ks * 9 + tap) * 2) * 2 * CO * 8;     // [part][j][CO][8]
+    split_bf16(v, hi, lo);
+    const size_t base = ((size_t)(ks * ntw + wt) * 2) * 2 * CO * 8;     // [part][j][CO][8]
     wp[base + ((size_t)(0 * 2 + j) * CO + co) * 8 + e] = hi;
     wp[base + ((size_t)(1 * 2 + j) * CO + co) * 8 + e] = lo;
   }
 }
 
-// ---- P8 <-> NCHW fp32 (boundaries of the stack and tests) ----------------------------------------
-__global__ void p8_pack_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ p8, int B, int C, int H, int W) {
-  const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * g.Hp * g.Wp;
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    int xx = (int)(idx % g.Wp);
-    size_t r = idx / g.Wp;
-    int yy = (int)(r % g.Hp); r /= g.Hp;
-    int ch = (int)(r % g.C8);
-    int n = (int)(r / g.C8);
-    float f[8];
-    const bool inside = yy >= 1 && yy <= H && xx >= 1 && xx <= W;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int c = ch * 8 + e;
-      f[e] = (inside && c < C) ? __ldg(x + (((size_t)n * C + c) * H + (yy - 1)) * W + (xx - 1)) : 0.f;
-    }
-    uint4 hi, lo;
-    split8(f, hi, lo);
-    const size_t off = ((size_t)yy * g.Wp + xx) * 8;
-    *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 0) + off) = hi;
-    *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 1) + off) = lo;
-  }
-}
-
-__global__ void p8_unpack_kernel(const __nv_bfloat16* __restrict__ p8, float* __restrict__ x, int B, int C, int H, int W) {
-  const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * H * W;
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    int xx = (int)(idx % W);
-    size_t r = idx / W;
-    int yy = (int)(r % H); r /= H;
-    int ch = (int)(r % g.C8);
-    int n = (int)(r / g.C8);
-    const size_t off = g.pixel(yy, xx);
-    const uint4 hi = *reinterpret_cast<const uint4*>(p8 + g.plane(n, ch, 0) + off);
-    const uint4 lo = *reinterpret_cast<const uint4*>(p8 + g.plane(n, ch, 1) + off);
-    float f[8];
-    join8(hi, lo, f);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int c = ch * 8 + e;
-      if (c < C) x[(((size_t)n * C + c) * H + yy) * W + xx] = f[e];
-    }
-  }
-}
-
-// zero ring (rows 0 and Hp-1, columns 0 and Wp-1) of every plane
-__global__ void p8_zero_ring_kernel(__nv_bfloat16* __restrict__ p8, int planes, int Hp, int Wp) {
-  const int per = 2 * Wp + 2 * (Hp - 2);
-  const size_t total = (size_t)planes * per;
-  const uint4 z = make_uint4(0, 0, 0, 0);
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    int i = (int)(idx % per);
-    size_t pl = idx / per;
-    int y, x;
-    if (i < Wp) { y = 0; x = i; }
-    else if (i < 2 * Wp) { y = Hp - 1; x = i - Wp; }
-    else { int k = i - 2 * Wp; y = 1 + (k >> 1); x = (k & 1) ? Wp - 1 : 0; }
-    *reinterpret_cast<uint4*>(p8 + (pl * Hp * Wp + (size_t)y * Wp + x) * 8) = z;
-  }
-}
+static inline int tc_lead(int mode, int CA) { return (mode == TC_T && CA == 1) ? 1 : 0; }
+static inline int tc_nstage(int mode, int CA, int CB) { return tc_lead(mode, CA) ? 1 + CB / 16 : (CA + CB) / 16; }
+static inline int tc_ntaps_w(int mode, bool has_1x1) { return mode == TC_T ? 16 : (mode == TC_S2 && has_1x1 ? 10 : 9); }
 
 // ---- tile geometry ---------------------------------------------------------------------------------
-struct TcPlan { int R, Wt, P, T, rows_alloc, tiles_x, tiles_y; size_t smem; bool ok; };
+struct TcPlan { int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, tiles_x, tiles_y; size_t smem; bool ok; };
 
-static TcPlan tc_plan(int H, int W, int N) {
+static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw) {
   TcPlan best = {}; best.ok = false;
   double best_cost = 1e300;
-  const int tmax = 256 / N;                            // accumulator columns per TMEM buffer
-  for (int Wt = 16; Wt <= 254 && Wt <= W + 15; ++Wt) {
-    const int P = Wt + 2;
-    for (int R = 1; R <= 32; ++R) {
-      const int flat = R * P - 2;
+  const int tmax = 256 / (N * ngrp);                   // accumulator columns per TMEM buffer
+  const int hc = (mode == TC_S2) ? 1 : 2, hr = hc;     // halo columns / rows of the staged tile
+  const int G = (mode == TC_S2) ? 4 : 1;
+  for (int Wt = 8; Wt <= 250 && Wt <= AW + 7; ++Wt) {
+    const int P = Wt + hc;
+    for (int R = 1; R <= 40; ++R) {
+      const int flat = R * P - hc;
       const int T = (flat + 127) / 128;
       if (T > tmax) break;
-      const int rows_alloc = (T * 128 + 2 * P + 2 + P - 1) / P;
-      const size_t smem = (size_t)TC_STAGES * (4ull * rows_alloc * P * 16 + 9ull * 2 * 2 * N * 16) + 256;
+      const int maxshift = hr * P + hc;
+      const int rows_alloc = (T * 128 + maxshift + P) / P;
+      const size_t smem = (size_t)TC_STAGES * ((size_t)G * 4 * rows_alloc * P * 16 + (size_t)ntw * 2 * 2 * N * 16);
       if (smem > (size_t)TC_SMEM_MAX) continue;
-      const int tx = (W + Wt - 1) / Wt, ty = (H + R - 1) / R;
-      // MMA rows issued, plus a load term (halo rows re-read), in arbitrary but comparable units
-      const double cost = (double)tx * ty * (T * 128.0 + 0.35 * (R + 2) * P);
+      const int tx = (AW + Wt - 1) / Wt, ty = (AH + R - 1) / R;
+      // MMA rows issued per tile (x taps, constant) plus a load term for re-read halo rows and weights
+      const double cost = (double)tx * ty * (T * 128.0 + 0.25 * G * (R + hr) * P + 0.02 * ntw * N);
       if (cost < best_cost) {
         best_cost = cost;
-        best = {R, Wt, P, T, rows_alloc, tx, ty, smem, true};
+        best = {R, Wt, P, T, rows_alloc, R + hr, G, ngrp, tx, ty, smem, true};
       }
     }
   }
@@ -379,112 +318,139 @@ static TcPlan tc_plan(int H, int W, int N) {
 }
 
 template <int N>
-static int launch_tc(TcArgs a, const TcPlan& p, cudaStream_t st) {
-  auto kern = conv3x3_tc_kernel<N>;
-  static int max_smem_set[NCONV_MAX_DEVICES] = {};
-  int dev = 0;
-  NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
-  if (dev >= NCONV_MAX_DEVICES || max_smem_set[dev] < (int)p.smem) {
-    NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX));
-    if (dev < NCONV_MAX_DEVICES) max_smem_set[dev] = TC_SMEM_MAX;
-  }
+static int launch_tc(const TcArgs& a, const TcPlan& p, cudaStream_t st) {
+  auto kern = conv_tc_kernel<N>;
+  static bool attr_done[NCONV_MAX_DEVICES] = {};
   static int sm_count[NCONV_MAX_DEVICES] = {};
-  int sms = (dev < NCONV_MAX_DEVICES) ? sm_count[dev] : 0;
+  int dev = 0, sms = 0;
+  NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
+  if (dev >= NCONV_MAX_DEVICES || !attr_done[dev]) {
+    NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX));
+    if (dev < NCONV_MAX_DEVICES) attr_done[dev] = true;
+  }
+  if (dev < NCONV_MAX_DEVICES) sms = sm_count[dev];
   if (sms == 0) {
     NCONV_RETURN_IF_ERR(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (dev < NCONV_MAX_DEVICES) sm_count[dev] = sms;
   }
   const int grid = a.ntiles < sms ? a.ntiles : sms;
-  const int CI = 16 * (a.pairs[0] + a.pairs[1]);
-  const double px = (double)a.B * a.H * a.W;
+  const int nk = a.pairs[0] + a.pairs[1];
+  const double opx = (double)a.B * a.OH * a.OW, apx = (double)a.B * a.AH * a.AW;
+  const double ipx = (a.mode == TC_S2) ? 4.0 * apx : apx;
+  const int CI = 16 * nk;
+  // flops: real taps per output pixel (9, 9+1, or 4 of the 16 per output phase)
+  const double taps_per_out = (a.mode == TC_T) ? 4.0 : (double)a.ntaps;
   char label[64];
-  snprintf(label, sizeof(label), "tc_conv3x3 %d->%d @%dx%d", CI, N, a.H, a.W);
+  snprintf(label, sizeof(label), "tc_conv%s %d->%d @%dx%d", a.mode == TC_S1 ? "3x3" : (a.mode == TC_S2 ? "3x3s2" : "T4x4s2"),
+           CI, N, a.OH, a.OW);
   {
-    // algorithmic: fp32-equivalent activations in and out (P8 is the same 4 B per value)
-    LaunchScope ls(st, label, 2.0 * CI * N * 9 * px, 4.0 * (CI + N) * px);
+    // algorithmic bytes: fp32-equivalent activations in and out (P8 holds the same 4 B per value)
+    LaunchScope ls(st, label, 2.0 * CI * N * taps_per_out * opx, 4.0 * (CI * ipx + N * opx * (a.outq ? 2.0 : 1.0)));
     kern<<<grid, TC_THREADS, p.smem, st>>>(a);
   }
   return (int)cudaGetLastError();
+}
+
+static void tc_build_taps(TcArgs& a, int mode, bool has_1x1) {
+  const uint32_t plane = (uint32_t)a.rows_alloc * a.P * 16;
+  int n = 0;
+  if (mode == TC_S1) {
+    for (int u = 0; u < 3; ++u)
+      for (int v = 0; v < 3; ++v) {
+        const TcTap tp = {(uint32_t)(u * a.P + v) * 16, (uint16_t)(u * 3 + v), 0, (uint8_t)(n == 0)};
+        a.taps[n++] = tp;
+      }
+  } else if (mode == TC_S2) {
+    // input row 2y+u-1: u=0 -> odd phase, phase row y-1 (staged row r); u=1 -> even phase, row y
+    // (staged r+1); u=2 -> odd phase, row y (staged r+1).  Same along x.
+    for (int u = 0; u < 3; ++u)
+      for (int v = 0; v < 3; ++v) {
+        const int py = (u == 1) ? 0 : 1, rs = (u == 0) ? 0 : 1;
+        const int px = (v == 1) ? 0 : 1, cs = (v == 0) ? 0 : 1;
+        const TcTap tp = {(uint32_t)(py * 2 + px) * 4 * plane + (uint32_t)(rs * a.P + cs) * 16, (uint16_t)(u * 3 + v), 0,
+                          (uint8_t)(n == 0)};
+        a.taps[n++] = tp;
+      }
+    if (has_1x1) {
+      const TcTap tp = {(uint32_t)(a.P + 1) * 16, 9, 1, 1};                // x[2y, 2x]: phase (0,0)
+      a.taps[n++] = tp;
+    }
+  } else {
+    // out[2a+py, 2b+px] += in[a+py-t, b+px-s] * W[.., (1-py)+2t, (1-px)+2s]
+    bool seen[4] = {false, false, false, false};
+    for (int kh = 0; kh < 4; ++kh)
+      for (int kw = 0; kw < 4; ++kw) {
+        const int py = 1 - (kh & 1), dy = py - (kh >> 1);
+        const int px = 1 - (kw & 1), dx = px - (kw >> 1);
+        const int g = py * 2 + px;
+        const TcTap tp = {(uint32_t)((1 + dy) * a.P + (1 + dx)) * 16, (uint16_t)(kh * 4 + kw), (uint8_t)g, (uint8_t)(!seen[g])};
+        a.taps[n++] = tp;
+        seen[g] = true;
+      }
+  }
+  a.ntaps = n;
 }
 
 }  // namespace nconv
 
 using namespace nconv;
 
-extern "C" size_t nconv_b200_p8_bytes(int B, int C, int H, int W) {
-  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
-  return P8Geom::make(B, C, H, W).total_elems() * sizeof(__nv_bfloat16) + P8_TAIL_SLACK_BYTES;
+extern "C" size_t nconv_b200_tc_wpack_bytes(int mode, int CO, int CA, int CB, int has_1x1) {
+  if (CO <= 0 || CA <= 0 || CB < 0 || mode < 0 || mode > 2) return 0;
+  return (size_t)tc_nstage(mode, CA, CB) * tc_ntaps_w(mode, has_1x1 != 0) * 2 * 2 * CO * 8 * sizeof(__nv_bfloat16);
 }
 
-extern "C" int nconv_b200_p8_pack(const float* x, void* p8, int B, int C, int H, int W, void* stream) {
-  if (!x || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
-  const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * g.Hp * g.Wp;
-  int blocks = (int)((total + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
+extern "C" int nconv_b200_tc_pack_weights(int mode, const float* w, const float* w1, void* wpack, int CO, int CA,
+                                          int CB, void* stream) {
+  if (!w || !wpack || CO <= 0 || CA <= 0 || CB < 0 || mode < 0 || mode > 2) return NCONV_ERR_BAD_ARG;
+  const int lead = tc_lead(mode, CA);
+  if ((!lead && CA % 16) || CB % 16) return NCONV_ERR_UNSUPPORTED;
+  if (w1 && mode != TC_S2) return NCONV_ERR_BAD_ARG;
+  const int nstage = tc_nstage(mode, CA, CB), ntw = tc_ntaps_w(mode, w1 != nullptr);
+  const int total = nstage * ntw * 2 * CO * 8;
   {
-    LaunchScope ls((cudaStream_t)stream, "p8_pack", 0.0, 8.0 * B * C * H * W);
-    p8_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)p8, B, C, H, W);
+    LaunchScope ls((cudaStream_t)stream, "tc_pack_weights", 0.0, 8.0 * CO * (CA + CB) * ntw);
+    tc_pack_weights_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, w1, (__nv_bfloat16*)wpack, CO,
+                                                                                 CA + CB, mode, lead, nstage, ntw);
   }
   return (int)cudaGetLastError();
 }
 
-extern "C" int nconv_b200_p8_unpack(const void* p8, float* x, int B, int C, int H, int W, void* stream) {
-  if (!x || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
-  const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * H * W;
-  int blocks = (int)((total + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
-  {
-    LaunchScope ls((cudaStream_t)stream, "p8_unpack", 0.0, 8.0 * B * C * H * W);
-    p8_unpack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)p8, x, B, C, H, W);
-  }
-  return (int)cudaGetLastError();
-}
-
-extern "C" int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream) {
-  if (!p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
-  const P8Geom g = P8Geom::make(B, C, H, W);
-  const int planes = B * g.C8 * 2;
-  const size_t total = (size_t)planes * (2 * g.Wp + 2 * (g.Hp - 2));
-  int blocks = (int)((total + 255) / 256); if (blocks > 148 * 8) blocks = 148 * 8;
-  {
-    LaunchScope ls((cudaStream_t)stream, "p8_zero_ring", 0.0, 16.0 * total);
-    p8_zero_ring_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)p8, planes, g.Hp, g.Wp);
-  }
-  return (int)cudaGetLastError();
-}
-
-extern "C" size_t nconv_b200_tc_wpack_bytes(int CO, int CI) {
-  if (CO <= 0 || CI <= 0 || CI % 16) return 0;
-  return (size_t)(CI / 16) * 9 * 2 * 2 * CO * 8 * sizeof(__nv_bfloat16);
-}
-
-extern "C" int nconv_b200_tc_pack_weights(const float* w, void* wpack, int CO, int CI, void* stream) {
-  if (!w || !wpack || CO <= 0 || CI <= 0 || CI % 16) return NCONV_ERR_BAD_ARG;
-  const int total = (CI / 16) * 9 * 2 * CO * 8;
-  {
-    LaunchScope ls((cudaStream_t)stream, "tc_pack_weights", 0.0, 8.0 * CO * CI * 9);
-    tc_pack_weights_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, (__nv_bfloat16*)wpack, CO, CI);
-  }
-  return (int)cudaGetLastError();
-}
-
-extern "C" int nconv_b200_conv3x3_tc(const nconv_b200_tc_desc* d, void* stream) {
+extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   if (!d || !d->a || !d->wpack || !d->y) return NCONV_ERR_BAD_ARG;
   if (d->B <= 0 || d->H <= 0 || d->W <= 0 || d->CA <= 0 || d->CB < 0) return NCONV_ERR_BAD_ARG;
-  if (d->CA % 16 || d->CB % 16 || (d->CB > 0 && !d->b)) return NCONV_ERR_UNSUPPORTED;
+  if (d->mode < 0 || d->mode > 2) return NCONV_ERR_BAD_ARG;
+  const int mode = d->mode;
+  const int lead = tc_lead(mode, d->CA);
+  if ((!lead && d->CA % 16) || d->CB % 16 || (d->CB > 0 && !d->b)) return NCONV_ERR_UNSUPPORTED;
   if (!(d->CO == 32 || d->CO == 64)) return NCONV_ERR_UNSUPPORTED;
-  const TcPlan p = tc_plan(d->H, d->W, d->CO);
+  if (mode == TC_S2 && ((d->H | d->W) & 1)) return NCONV_ERR_UNSUPPORTED;
+  if (d->yq && (mode == TC_T ? 0 : ((mode == TC_S2 ? (d->H / 2) | (d->W / 2) : (d->H | d->W)) & 1))) return NCONV_ERR_UNSUPPORTED;
+  const bool has_1x1 = (mode == TC_S2) && d->has_1x1;
+  const int AH = (mode == TC_S2) ? d->H / 2 : d->H, AW = (mode == TC_S2) ? d->W / 2 : d->W;
+  const int ngrp = (mode == TC_T) ? 4 : (has_1x1 ? 2 : 1);
+  const int ntw = tc_ntaps_w(mode, has_1x1);
+  const TcPlan p = tc_plan(mode, AH, AW, d->CO, ngrp, ntw);
   if (!p.ok) return NCONV_ERR_UNSUPPORTED;
   TcArgs a = {};
   a.src[0] = (const __nv_bfloat16*)d->a; a.src[1] = (const __nv_bfloat16*)d->b;
-  a.c8[0] = d->CA / 8; a.c8[1] = d->CB / 8;
-  a.pairs[0] = d->CA / 16; a.pairs[1] = d->CB / 16;
+  a.c8[0] = lead ? 1 : d->CA / 8; a.c8[1] = d->CB / 8;
+  a.pairs[0] = lead ? 1 : d->CA / 16; a.pairs[1] = d->CB / 16;
+  if (mode == TC_S2) {
+    const P8QGeom q = P8QGeom::make(d->B, 8, d->H, d->W);
+    a.slab_elems = q.slab_elems(); a.grp_elems = q.phase_elems(); a.src_pitch = q.Wq1; a.src_rows = q.Hq1;
+  } else {
+    a.slab_elems = (size_t)(d->H + 2) * (d->W + 2) * 8; a.grp_elems = 0; a.src_pitch = d->W + 2; a.src_rows = d->H + 2;
+  }
   a.wpack = (const __nv_bfloat16*)d->wpack; a.scale = d->scale; a.shift = d->shift;
-  a.out = (__nv_bfloat16*)d->y;
-  a.B = d->B; a.H = d->H; a.W = d->W; a.Hp = d->H + 2; a.Wp = d->W + 2;
-  a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.T = p.T; a.rows_alloc = p.rows_alloc;
+  a.out = (__nv_bfloat16*)d->y; a.outq = (__nv_bfloat16*)d->yq;
+  a.B = d->B; a.AH = AH; a.AW = AW;
+  a.OH = (mode == TC_T) ? 2 * d->H : AH; a.OW = (mode == TC_T) ? 2 * d->W : AW;
+  a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.T = p.T; a.rows_alloc = p.rows_alloc; a.rows_ld = p.rows_ld;
+  a.G = p.G; a.ngrp = ngrp; a.ntaps_w = ntw;
   a.tiles_x = p.tiles_x; a.tiles_y = p.tiles_y; a.ntiles = p.tiles_x * p.tiles_y * d->B;
-  a.relu = d->relu;
+  a.relu = d->relu; a.mode = mode;
+  tc_build_taps(a, mode, has_1x1);
   cudaStream_t st = (cudaStream_t)stream;
   return d->CO == 64 ? launch_tc<64>(a, p, st) : launch_tc<32>(a, p, st);
 }

@@ -42,8 +42,9 @@ class TcDesc(Structure):
     """nconv_b200_tc_desc"""
     _fields_ = [
         ("a", c_void_p), ("b", c_void_p), ("wpack", c_void_p), ("scale", c_void_p), ("shift", c_void_p),
-        ("y", c_void_p),
+        ("y", c_void_p), ("yq", c_void_p),
         ("B", c_int), ("CA", c_int), ("CB", c_int), ("CO", c_int), ("H", c_int), ("W", c_int), ("relu", c_int),
+        ("mode", c_int), ("has_1x1", c_int),
     ]
 
 
@@ -78,9 +79,12 @@ SIGNATURES = {
     "nconv_b200_p8_pack": (c_int, [c_void_p, c_void_p] + [c_int] * 4 + [c_void_p]),
     "nconv_b200_p8_unpack": (c_int, [c_void_p, c_void_p] + [c_int] * 4 + [c_void_p]),
     "nconv_b200_p8_zero_ring": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p]),
-    "nconv_b200_tc_wpack_bytes": (c_size_t, [c_int, c_int]),
-    "nconv_b200_tc_pack_weights": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
-    "nconv_b200_conv3x3_tc": (c_int, [POINTER(TcDesc), c_void_p]),
+    "nconv_b200_p8q_bytes": (c_size_t, [c_int] * 4),
+    "nconv_b200_p8q_zero_ring": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p]),
+    "nconv_b200_p8q_pack": (c_int, [c_void_p, c_void_p] + [c_int] * 4 + [c_void_p]),
+    "nconv_b200_tc_wpack_bytes": (c_size_t, [c_int] * 5),
+    "nconv_b200_tc_pack_weights": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "nconv_b200_conv_tc": (c_int, [POINTER(TcDesc), c_void_p]),
 }
 
 _lib = None

@@ -384,30 +384,48 @@ _define("bn_fold(Tensor gamma, Tensor beta, Tensor mean, Tensor var, Tensor? con
 # --------------------------------------------------------------------------------------
 # tensor-core path: P8 activations + tcgen05 bf16x3 3x3 convolution
 # --------------------------------------------------------------------------------------
+TC_S1, TC_S2, TC_T = 0, 1, 2
+
+
 class P8:
     """A [B,C,H,W] activation held in the P8 device layout (csrc/p8.cuh).  `buf` is a uint8 CUDA
-    tensor of nconv_b200_p8_bytes(); kernels read and write it through raw pointers."""
-    __slots__ = ("buf", "B", "C", "H", "W")
+    tensor of nconv_b200_p8_bytes(); `qbuf` (optional) is the P8Q phase-split copy that stride-2
+    consumers read.  Kernels access both through raw pointers."""
+    __slots__ = ("buf", "qbuf", "B", "C", "H", "W")
 
-    def __init__(self, buf, B, C, H, W):
-        self.buf, self.B, self.C, self.H, self.W = buf, B, C, H, W
+    def __init__(self, buf, B, C, H, W, qbuf=None):
+        self.buf, self.qbuf, self.B, self.C, self.H, self.W = buf, qbuf, B, C, H, W
 
     @staticmethod
-    def empty(B, C, H, W, device, zero_ring=True):
+    def empty(B, C, H, W, device, zero_ring=True, with_q=False):
         n = int(_C.nconv_b200_p8_bytes(B, C, H, W))
         t = P8(torch.empty(n, device=device, dtype=torch.uint8), B, C, H, W)
+        if with_q:
+            nq = int(_C.nconv_b200_p8q_bytes(B, C, H, W))
+            if nq == 0:
+                raise ValueError("P8Q needs even H and W")
+            t.qbuf = torch.empty(nq, device=device, dtype=torch.uint8)
         if zero_ring:
-            with torch.cuda.device(device):
-                check(_C.nconv_b200_p8_zero_ring(_p(t.buf), B, C, H, W, _stream(t.buf)), "p8_zero_ring")
+            t.zero_ring()
         return t
 
+    def zero_ring(self):
+        with torch.cuda.device(self.buf.device):
+            check(_C.nconv_b200_p8_zero_ring(_p(self.buf), self.B, self.C, self.H, self.W, _stream(self.buf)),
+                  "p8_zero_ring")
+            if self.qbuf is not None:
+                check(_C.nconv_b200_p8q_zero_ring(_p(self.qbuf), self.B, self.C, self.H, self.W, _stream(self.buf)),
+                      "p8q_zero_ring")
+
     @staticmethod
-    def pack(x):
+    def pack(x, with_q=False):
         x = _prep(x, "x")
         B, C, H, W = x.shape
-        t = P8.empty(B, C, H, W, x.device, zero_ring=False)
+        t = P8.empty(B, C, H, W, x.device, zero_ring=False, with_q=with_q)
         with torch.cuda.device(x.device):
             check(_C.nconv_b200_p8_pack(_p(x), _p(t.buf), B, C, H, W, _stream(x)), "p8_pack")
+            if with_q:
+                check(_C.nconv_b200_p8q_pack(_p(x), _p(t.qbuf), B, C, H, W, _stream(x)), "p8q_pack")
         return t
 
     def unpack(self):
@@ -417,28 +435,40 @@ class P8:
         return x
 
 
-def tc_pack_weights(weight):
-    weight = _prep(weight, "weight")
-    CO, CI, kh, kw = weight.shape
-    if (kh, kw) != (3, 3) or CI % 16:
-        raise ValueError("tc_pack_weights: weight must be [CO, CI%16==0, 3, 3]")
-    wp = torch.empty(int(_C.nconv_b200_tc_wpack_bytes(CO, CI)), device=weight.device, dtype=torch.uint8)
+def tc_pack_weights(mode: int, weight, CA: int, CB: int = 0, w1=None):
+    """Pack conv weights for conv_tc: S1/S2 [CO,CA+CB,3,3] (+ w1 [CO,CA+CB,1,1]); T [CA+CB,CO,4,4]."""
+    weight = _prep(weight, "weight"); w1 = _prep_opt(w1, "w1")
+    CO = weight.shape[1] if mode == TC_T else weight.shape[0]
+    CI = weight.shape[0] if mode == TC_T else weight.shape[1]
+    if CI != CA + CB or tuple(weight.shape[2:]) != ((4, 4) if mode == TC_T else (3, 3)):
+        raise ValueError("tc_pack_weights: weight shape mismatch")
+    n = int(_C.nconv_b200_tc_wpack_bytes(mode, CO, CA, CB, int(w1 is not None)))
+    wp = torch.empty(n, device=weight.device, dtype=torch.uint8)
     with torch.cuda.device(weight.device):
-        check(_C.nconv_b200_tc_pack_weights(_p(weight), _p(wp), CO, CI, _stream(weight)), "tc_pack_weights")
+        check(_C.nconv_b200_tc_pack_weights(mode, _p(weight), _p(w1), _p(wp), CO, CA, CB, _stream(weight)),
+              "tc_pack_weights")
     return wp
 
 
-def conv3x3_tc(a: "P8", b, wpack, CO: int, scale, shift, relu: bool, out=None) -> "P8":
-    """y = act(scale*conv3x3(cat[a,b]) + shift) on the tcgen05 path; a, b, y are P8."""
+def conv_tc(mode: int, a: "P8", b, wpack, CO: int, scale, shift, relu: bool, has_1x1=False, out=None,
+            with_q=False) -> "P8":
+    """y = act(scale*conv(cat[a,b]) + shift) (+ 1x1/s2 residual) on the tcgen05 path; a, b, y are P8."""
     CB = 0 if b is None else b.C
     if b is not None and (b.B, b.H, b.W) != (a.B, a.H, a.W):
-        raise ValueError("conv3x3_tc: source shape mismatch")
+        raise ValueError("conv_tc: source shape mismatch")
     scale = _prep_opt(scale, "scale"); shift = _prep_opt(shift, "shift")
-    y = out if out is not None else P8.empty(a.B, CO, a.H, a.W, a.buf.device)
-    d = TcDesc(_p(a.buf), None if b is None else _p(b.buf), _p(wpack), _p(scale), _p(shift), _p(y.buf),
-               a.B, a.C, CB, CO, a.H, a.W, int(relu))
+    OH, OW = {TC_S1: (a.H, a.W), TC_S2: (a.H // 2, a.W // 2), TC_T: (2 * a.H, 2 * a.W)}[mode]
+    y = out if out is not None else P8.empty(a.B, CO, OH, OW, a.buf.device, with_q=with_q)
+    if mode == TC_S2:
+        if a.qbuf is None or (b is not None and b.qbuf is None):
+            raise ValueError("conv_tc: stride-2 sources need their P8Q copy")
+        pa, pb = _p(a.qbuf), None if b is None else _p(b.qbuf)
+    else:
+        pa, pb = _p(a.buf), None if b is None else _p(b.buf)
+    d = TcDesc(pa, pb, _p(wpack), _p(scale), _p(shift), _p(y.buf), _p(y.qbuf), a.B, a.C, CB, CO, a.H, a.W,
+               int(relu), mode, int(has_1x1))
     with torch.cuda.device(a.buf.device):
-        check(_C.nconv_b200_conv3x3_tc(byref(d), _stream(a.buf)), "conv3x3_tc")
+        check(_C.nconv_b200_conv_tc(byref(d), _stream(a.buf)), "conv_tc")
     return y
 
 

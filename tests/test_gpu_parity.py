@@ -349,6 +349,19 @@ def test_p8_roundtrip(shape):
     assert O.max_rel_err(y, x, floor=1e-6) <= 2.0 ** -16
 
 
+def _ring_intact(y):
+    """kernels write interior pixels only: the zero ring of a P8 output must survive"""
+    B, C, H, W = y.B, y.C, y.H, y.W
+    raw = y.buf[: 2 * ((C + 7) // 8) * B * (H + 2) * (W + 2) * 16].view(torch.bfloat16)
+    raw = raw.view(B, (C + 7) // 8, 2, H + 2, W + 2, 8).float()
+    return (float(raw[:, :, :, 0].abs().max()) == 0 and float(raw[:, :, :, -1].abs().max()) == 0 and
+            float(raw[:, :, :, :, 0].abs().max()) == 0 and float(raw[:, :, :, :, -1].abs().max()) == 0)
+
+
+# bf16x3: fp32-class accuracy, stated as 2e-5 of the output scale (an fp32 conv is itself ~1e-6)
+TC_TOL = 2e-5
+
+
 @pytest.mark.parametrize("cfg", [
     # CA, CB, CO, B, H, W, relu, affine
     (32, 0, 32, 2, 24, 80, True, True),
@@ -359,7 +372,7 @@ def test_p8_roundtrip(shape):
     (32, 0, 32, 1, 5, 7, True, True),            # smaller than one tile
 ])
 def test_conv3x3_tc_vs_fp64(cfg):
-    from nconv_b200.ops import P8, tc_pack_weights, conv3x3_tc
+    from nconv_b200.ops import P8, tc_pack_weights, conv_tc, TC_S1
     CA, CB, CO, B, H, W, relu, affine = cfg
     g = torch.Generator().manual_seed(sum(cfg[:6]))
     a = torch.randn(B, CA, H, W, generator=g) * 3
@@ -376,14 +389,81 @@ def test_conv3x3_tc_vs_fp64(cfg):
         ref = ref.relu()
     pa = P8.pack(a.to(dev()))
     pb = P8.pack(b.to(dev())) if b is not None else None
-    wp = tc_pack_weights(w.to(dev()))
-    y = conv3x3_tc(pa, pb, wp, CO, None if scale is None else scale.to(dev()), shift.to(dev()), relu)
+    wp = tc_pack_weights(TC_S1, w.to(dev()), CA, CB)
+    y = conv_tc(TC_S1, pa, pb, wp, CO, None if scale is None else scale.to(dev()), shift.to(dev()), relu)
     out = y.unpack()
     torch.cuda.synchronize()
-    # bf16x3: fp32-class accuracy, stated as 2e-5 of the output scale (fp32 conv itself is ~1e-6)
-    assert grad_err(out, ref) <= 2e-5
-    # the zero ring of the output must be intact (kernels write interior pixels only)
-    raw = y.buf[: 2 * ((CO + 7) // 8) * B * (H + 2) * (W + 2) * 16].view(torch.bfloat16)
-    raw = raw.view(B, CO // 8, 2, H + 2, W + 2, 8).float()
-    assert float(raw[:, :, :, 0].abs().max()) == 0 and float(raw[:, :, :, -1].abs().max()) == 0
-    assert float(raw[:, :, :, :, 0].abs().max()) == 0 and float(raw[:, :, :, :, -1].abs().max()) == 0
+    assert grad_err(out, ref) <= TC_TOL
+    assert _ring_intact(y)
+
+
+@pytest.mark.parametrize("cfg", [
+    # CI, CO, B, H, W, with 1x1 residual
+    (32, 64, 2, 48, 64, True),
+    (64, 64, 1, 30, 44, True),
+    (64, 64, 1, 120, 160, False),
+    (32, 32, 1, 6, 10, True),
+])
+def test_conv3x3_s2_tc_vs_fp64(cfg):
+    """RGBEncoder (step2.py:134-154): ReLU(BN(conv3x3_s2(x)+b)) + conv1x1_s2(x); also checks the P8Q
+    copy the kernel writes for the next stride-2 layer."""
+    from nconv_b200.ops import P8, tc_pack_weights, conv_tc, TC_S2
+    CI, CO, B, H, W, res = cfg
+    g = torch.Generator().manual_seed(sum(cfg[:5]))
+    x = torch.randn(B, CI, H, W, generator=g) * 3
+    w = torch.randn(CO, CI, 3, 3, generator=g) / (3 * CI ** 0.5)
+    w1 = torch.randn(CO, CI, 1, 1, generator=g) / CI ** 0.5 if res else None
+    scale = torch.rand(CO, generator=g) + 0.5
+    shift = torch.randn(CO, generator=g)
+    ref = F.conv2d(x.double(), w.double(), stride=2, padding=1) * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)
+    ref = ref.relu()
+    if res:
+        ref = ref + F.conv2d(x.double(), w1.double(), stride=2)
+    px = P8.pack(x.to(dev()), with_q=True)
+    wp = tc_pack_weights(TC_S2, w.to(dev()), CI, 0, w1=None if w1 is None else w1.to(dev()))
+    with_q = (H // 2) % 2 == 0 and (W // 2) % 2 == 0
+    y = conv_tc(TC_S2, px, None, wp, CO, scale.to(dev()), shift.to(dev()), True, has_1x1=res, with_q=with_q)
+    out = y.unpack()
+    assert grad_err(out, ref) <= TC_TOL
+    assert _ring_intact(y)
+    if with_q:
+        # the P8Q copy must hold the same values: feed it to a second stride-2 conv
+        w2 = torch.randn(CO, CO, 3, 3, generator=g) / (3 * CO ** 0.5) if CO in (32, 64) else None
+        wp2 = tc_pack_weights(TC_S2, w2.to(dev()), CO, 0)
+        y2 = conv_tc(TC_S2, y, None, wp2, CO, None, None, False)
+        ref2 = F.conv2d(ref, w2.double(), stride=2, padding=1)
+        assert grad_err(y2.unpack(), ref2) <= 2 * TC_TOL
+
+
+@pytest.mark.parametrize("cfg", [
+    # lone depth channel?, CF, CO, B, H, W
+    (True, 64, 64, 2, 15, 20),
+    (True, 32, 32, 1, 24, 40),
+    (False, 64, 64, 1, 9, 13),
+    (True, 64, 64, 1, 60, 80),
+])
+def test_convT4x4s2_tc_vs_fp64(cfg):
+    """Basic2dTrans (step2.py:197-214) on cat[depth(1), features(C)] (UpCat :174)."""
+    from nconv_b200.ops import P8, tc_pack_weights, conv_tc, TC_T
+    lone, CF, CO, B, H, W = cfg
+    g = torch.Generator().manual_seed(sum(cfg[1:]))
+    d = torch.randn(B, 1, H, W, generator=g) * 5 if lone else None
+    f = torch.randn(B, CF, H, W, generator=g) * 3
+    CI = CF + (1 if lone else 0)
+    w = torch.randn(CI, CO, 4, 4, generator=g) / (2 * CI ** 0.5)
+    scale = torch.rand(CO, generator=g) + 0.5
+    shift = torch.randn(CO, generator=g)
+    x = torch.cat((d, f), 1) if lone else f
+    ref = F.conv_transpose2d(x.double(), w.double(), stride=2, padding=1)
+    ref = (ref * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)).relu()
+    pf = P8.pack(f.to(dev()))
+    if lone:
+        pd = P8.pack(d.to(dev()))
+        wp = tc_pack_weights(TC_T, w.to(dev()), 1, CF)
+        y = conv_tc(TC_T, pd, pf, wp, CO, scale.to(dev()), shift.to(dev()), True)
+    else:
+        wp = tc_pack_weights(TC_T, w.to(dev()), CF, 0)
+        y = conv_tc(TC_T, pf, None, wp, CO, scale.to(dev()), shift.to(dev()), True)
+    assert (y.H, y.W) == (2 * H, 2 * W)
+    assert grad_err(y.unpack(), ref) <= TC_TOL
+    assert _ring_intact(y)
