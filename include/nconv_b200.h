@@ -198,6 +198,19 @@ typedef struct {
 } nconv_b200_tc_desc;
 int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream);
 
+/* HBM-bound edges of the tensor-core stack (CUDA cores, converting fp32 NCHW <-> P8 on the fly).
+ * conv_small_p8: y = act(scale*conv3x3(x)+shift) (+ conv1x1(x) when w1 != NULL) for x fp32
+ *   [B,CI,H,W] with (CI,CO) in {(3,32),(1,32),(1,64)} -> P8 y (+ optional P8Q copy yq):
+ *   rgb_encoder0 (step2.py:134-154) and depth_conv (:221).
+ * head_p8: y = residual + conv3x3_{C->1}(f) (Conv3x3 :156, :255-257, :274-276) for f P8
+ *   [B,C in {32,64},H,W] -> fp32 y [B,1,H,W] and, optionally, y8: the same plane as a
+ *   lone-channel P8 (input of the next level's ConvTranspose). */
+int nconv_b200_conv_small_p8(const float* x, const float* w, const float* w1, const float* scale,
+                             const float* shift, void* y, void* yq, int B, int CI, int CO, int H, int W,
+                             int relu, void* stream);
+int nconv_b200_head_p8(const void* f, const float* w, const float* residual, float* y, void* y8, int B,
+                       int C, int H, int W, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

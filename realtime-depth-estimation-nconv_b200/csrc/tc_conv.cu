@@ -44,6 +44,46 @@ constexpr int TC_MAX_TAPS = 17;
 
 enum { TC_S1 = 0, TC_S2 = 1, TC_T = 2 };
 
+// Compile-time tap tables (tap index -> staged-tile offset in 16 B units, weight block, accumulator
+// group, first-into-group).  `plane16` = one staged plane in 16 B units; plane group g starts at
+// g*4*plane16.
+template <int MODE> struct TapTable;
+template <> struct TapTable<TC_S1> {            // tap = u*3+v reads staged (r+u, c+v)
+  static constexpr int NTAPS = 9;
+  __host__ __device__ static constexpr uint32_t a_off16(int i, int P, uint32_t) { return (uint32_t)((i / 3) * P + (i % 3)); }
+  __host__ __device__ static constexpr uint32_t w_idx(int i) { return (uint32_t)i; }
+  __host__ __device__ static constexpr uint32_t dgrp(int) { return 0; }
+  __host__ __device__ static constexpr bool first(int i) { return i == 0; }
+};
+template <> struct TapTable<TC_S2> {
+  // input row 2y+u-1: u=0 -> odd phase, phase row y-1 (staged row r); u=1 -> even phase, row y
+  // (staged r+1); u=2 -> odd phase, row y (staged r+1).  Same along x.  Tap 9 = the 1x1/s2 branch.
+  static constexpr int NTAPS = 10;
+  __host__ __device__ static constexpr uint32_t a_off16(int i, int P, uint32_t plane16) {
+    if (i == 9) return (uint32_t)(P + 1);                               // x[2y, 2x]: phase (0,0)
+    const int u = i / 3, v = i % 3;
+    const int py = (u == 1) ? 0 : 1, rs = (u == 0) ? 0 : 1, px = (v == 1) ? 0 : 1, cs = (v == 0) ? 0 : 1;
+    return (uint32_t)(py * 2 + px) * 4 * plane16 + (uint32_t)(rs * P + cs);
+  }
+  __host__ __device__ static constexpr uint32_t w_idx(int i) { return (uint32_t)i; }
+  __host__ __device__ static constexpr uint32_t dgrp(int i) { return i == 9 ? 1 : 0; }
+  __host__ __device__ static constexpr bool first(int i) { return i == 0 || i == 9; }
+};
+template <> struct TapTable<TC_T> {
+  // out[2a+py, 2b+px] += in[a+py-t, b+px-s] * W[.., kh=(1-py)+2t, kw=(1-px)+2s];  tap = kh*4+kw
+  static constexpr int NTAPS = 16;
+  __host__ __device__ static constexpr int py(int i) { return 1 - ((i / 4) & 1); }
+  __host__ __device__ static constexpr int px(int i) { return 1 - ((i % 4) & 1); }
+  __host__ __device__ static constexpr uint32_t a_off16(int i, int P, uint32_t) {
+    const int dy = py(i) - ((i / 4) >> 1), dx = px(i) - ((i % 4) >> 1);
+    return (uint32_t)((1 + dy) * P + (1 + dx));
+  }
+  __host__ __device__ static constexpr uint32_t w_idx(int i) { return (uint32_t)i; }
+  __host__ __device__ static constexpr uint32_t dgrp(int i) { return (uint32_t)(py(i) * 2 + px(i)); }
+  // first tap of each phase in kh-major order: kh in {0,1} x kw in {0,1}
+  __host__ __device__ static constexpr bool first(int i) { return (i / 4) < 2 && (i % 4) < 2; }
+};
+
 struct TcTap {
   uint32_t a_off;   // byte offset of the tap's hi A tile inside a stage (plane group base + shift*16)
   uint16_t w_idx;   // weight tap block inside the stage's packed weights
@@ -70,12 +110,11 @@ struct TcArgs {
   TcTap taps[TC_MAX_TAPS];
 };
 
-template <int N>
+template <int N, int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_full[TC_STAGES], s_empty[TC_STAGES], s_tfull[2], s_tempty[2];
   __shared__ uint32_t s_tmem_base;
-  __shared__ TcTap s_taps[TC_MAX_TAPS];
   __shared__ float s_scale[N], s_shift[N];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -87,7 +126,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   const uint32_t smem_base = smem_u32(smem);
   const int nk = a.pairs[0] + a.pairs[1];
 
-  if (threadIdx.x < a.ntaps) s_taps[threadIdx.x] = a.taps[threadIdx.x];
   if (threadIdx.x < N) {
     s_scale[threadIdx.x] = a.scale ? __ldg(a.scale + threadIdx.x) : 1.f;
     s_shift[threadIdx.x] = a.shift ? __ldg(a.shift + threadIdx.x) : 0.f;
@@ -152,19 +190,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         mbar_wait(smem_u32(&s_full[stage]), phase);
         tc_fence_after();
         if (lane == 0) {
-          const uint32_t sa = smem_base + stage * stage_bytes;
-          const uint32_t sb = sa + a_stage_bytes;
+          // Descriptor words are built from kernel parameters and compile-time tap tables only, so
+          // they stay in uniform registers (UTCHMMA takes its descriptors from the uniform file).
+          constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);       // SBO = 128 B, descriptor version 1
+          const uint32_t sa16 = (smem_base + stage * stage_bytes) >> 4;
+          const uint32_t sb16 = sa16 + (a_stage_bytes >> 4);
+          const uint32_t a_lbo = (a_plane_bytes >> 4) << 16, alo_off = (2 * a_plane_bytes) >> 4;
+          constexpr uint32_t B_LBO = (uint32_t)(N * 16 >> 4) << 16, BLO_OFF = (2 * N * 16) >> 4;
           for (int t = 0; t < a.T; ++t) {
-            for (int i = 0; i < a.ntaps; ++i) {
-              const TcTap tp = s_taps[i];
-              const uint32_t d = tmem_base + buf * 256 + (tp.dgrp * a.T + t) * N;
-              const uint32_t aaddr = sa + tp.a_off + (uint32_t)t * 128 * 16;
-              const uint64_t a_hi = umma_desc(aaddr, a_plane_bytes, 128);
-              const uint64_t a_lo = umma_desc(aaddr + 2 * a_plane_bytes, a_plane_bytes, 128);
-              const uint32_t baddr = sb + tp.w_idx * B_TAP_BYTES;
-              const uint64_t b_hi = umma_desc(baddr, N * 16, 128);
-              const uint64_t b_lo = umma_desc(baddr + 2 * N * 16, N * 16, 128);
-              umma_bf16(d, a_hi, b_hi, IDESC, (k > 0 || !tp.first) ? 1u : 0u);
+            const uint32_t dbase = tmem_base + buf * 256 + t * N;
+            const uint32_t at16 = sa16 + (uint32_t)t * 128;
+#pragma unroll
+            for (int i = 0; i < TapTable<MODE>::NTAPS; ++i) {
+              if (i >= a.ntaps) break;                                   // S2 without the 1x1 branch
+              const uint32_t ao = TapTable<MODE>::a_off16(i, a.P, a_plane_bytes >> 4);
+              const uint32_t d = dbase + TapTable<MODE>::dgrp(i) * a.T * N;
+              const uint64_t a_hi = ((uint64_t)DESC_HI << 32) | ((at16 + ao) | a_lbo);
+              const uint64_t a_lo = ((uint64_t)DESC_HI << 32) | ((at16 + ao + alo_off) | a_lbo);
+              const uint32_t bo = sb16 + TapTable<MODE>::w_idx(i) * (B_TAP_BYTES >> 4);
+              const uint64_t b_hi = ((uint64_t)DESC_HI << 32) | (bo | B_LBO);
+              const uint64_t b_lo = ((uint64_t)DESC_HI << 32) | ((bo + BLO_OFF) | B_LBO);
+              umma_bf16(d, a_hi, b_hi, IDESC, (k > 0 || !TapTable<MODE>::first(i)) ? 1u : 0u);
               umma_bf16(d, a_lo, b_hi, IDESC, 1u);
               umma_bf16(d, a_hi, b_lo, IDESC, 1u);
             }
@@ -182,7 +228,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
     uint32_t it = 0;
     const size_t oplane = (size_t)(a.OH + 2) * (a.OW + 2) * 8;
     const P8QGeom qg = P8QGeom::make(a.B, N, a.OH, a.OW);
-    const int nphase = (a.mode == TC_T) ? 4 : 1;
+    constexpr int nphase = (MODE == TC_T) ? 4 : 1;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
       const int tx = tile % a.tiles_x, ty = (tile / a.tiles_x) % a.tiles_y, n = tile / (a.tiles_x * a.tiles_y);
@@ -194,15 +240,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         const int ay = ty * a.R + r, ax = tx * a.Wt + c;
         const bool valid = (r < a.R) && (c < a.Wt) && (ay < a.AH) && (ax < a.AW);
         for (int ph = 0; ph < nphase; ++ph) {
-          const int oy = (a.mode == TC_T) ? 2 * ay + (ph >> 1) : ay;
-          const int ox = (a.mode == TC_T) ? 2 * ax + (ph & 1) : ax;
+          const int oy = (MODE == TC_T) ? 2 * ay + (ph >> 1) : ay;
+          const int ox = (MODE == TC_T) ? 2 * ax + (ph & 1) : ax;
           __nv_bfloat16* obase = a.out + ((size_t)n * (N / 8) * 2) * oplane + ((size_t)(oy + 1) * (a.OW + 2) + (ox + 1)) * 8;
           const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256;
 #pragma unroll
           for (int cb = 0; cb < N / 32; ++cb) {
             uint32_t v[32], w[32];
             tmem_ld32(tcol + (ph * a.T + t) * N + cb * 32, v);
-            if (a.ngrp == 2) tmem_ld32(tcol + (a.T + t) * N + cb * 32, w);      // S2 residual branch
+            if (MODE == TC_S2 && a.ngrp == 2) tmem_ld32(tcol + (a.T + t) * N + cb * 32, w);      // S2 residual branch
             tmem_ld_wait();
             if (valid) {
 #pragma unroll
@@ -213,7 +259,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
                   const int o = cb * 32 + ch * 8 + e;
                   float x = fmaf(__uint_as_float(v[ch * 8 + e]), s_scale[o], s_shift[o]);
                   if (a.relu) x = fmaxf(x, 0.f);
-                  if (a.ngrp == 2) x += __uint_as_float(w[ch * 8 + e]);
+                  if (MODE == TC_S2 && a.ngrp == 2) x += __uint_as_float(w[ch * 8 + e]);
                   f[e] = x;
                 }
                 uint4 hi, lo;
@@ -317,9 +363,9 @@ static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw) {
   return best;
 }
 
-template <int N>
+template <int N, int MODE>
 static int launch_tc(const TcArgs& a, const TcPlan& p, cudaStream_t st) {
-  auto kern = conv_tc_kernel<N>;
+  auto kern = conv_tc_kernel<N, MODE>;
   static bool attr_done[NCONV_MAX_DEVICES] = {};
   static int sm_count[NCONV_MAX_DEVICES] = {};
   int dev = 0, sms = 0;
@@ -452,5 +498,7 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   a.relu = d->relu; a.mode = mode;
   tc_build_taps(a, mode, has_1x1);
   cudaStream_t st = (cudaStream_t)stream;
-  return d->CO == 64 ? launch_tc<64>(a, p, st) : launch_tc<32>(a, p, st);
+  if (mode == TC_S1) return d->CO == 64 ? launch_tc<64, TC_S1>(a, p, st) : launch_tc<32, TC_S1>(a, p, st);
+  if (mode == TC_S2) return d->CO == 64 ? launch_tc<64, TC_S2>(a, p, st) : launch_tc<32, TC_S2>(a, p, st);
+  return d->CO == 64 ? launch_tc<64, TC_T>(a, p, st) : launch_tc<32, TC_T>(a, p, st);
 }

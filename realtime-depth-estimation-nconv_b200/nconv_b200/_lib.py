@@ -85,6 +85,8 @@ SIGNATURES = {
     "nconv_b200_tc_wpack_bytes": (c_size_t, [c_int] * 5),
     "nconv_b200_tc_pack_weights": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "nconv_b200_conv_tc": (c_int, [POINTER(TcDesc), c_void_p]),
+    "nconv_b200_conv_small_p8": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_void_p]),
+    "nconv_b200_head_p8": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
 }
 
 _lib = None

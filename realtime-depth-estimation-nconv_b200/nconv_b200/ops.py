@@ -472,6 +472,29 @@ def conv_tc(mode: int, a: "P8", b, wpack, CO: int, scale, shift, relu: bool, has
     return y
 
 
+def conv_small_p8(x, weight, w1, scale, shift, relu: bool, out=None, with_q=False) -> "P8":
+    """fp32 NCHW (1 or 3 channels) -> P8: act(scale*conv3x3(x)+shift) (+ conv1x1(x))."""
+    x = _prep(x, "x"); weight = _prep(weight, "weight"); w1 = _prep_opt(w1, "w1")
+    scale = _prep_opt(scale, "scale"); shift = _prep_opt(shift, "shift")
+    B, CI, H, W = x.shape
+    CO = weight.shape[0]
+    y = out if out is not None else P8.empty(B, CO, H, W, x.device, with_q=with_q)
+    with torch.cuda.device(x.device):
+        check(_C.nconv_b200_conv_small_p8(_p(x), _p(weight), _p(w1), _p(scale), _p(shift), _p(y.buf), _p(y.qbuf),
+                                          B, CI, CO, H, W, int(relu), _stream(x)), "conv_small_p8")
+    return y
+
+
+def head_p8(f: "P8", weight, residual, out8=None):
+    """residual + conv3x3_{C->1}(f): returns (fp32 [B,1,H,W], lone-channel P8 or None)."""
+    weight = _prep(weight, "weight"); residual = _prep_opt(residual, "residual")
+    y = torch.empty((f.B, 1, f.H, f.W), device=f.buf.device, dtype=torch.float32)
+    with torch.cuda.device(y.device):
+        check(_C.nconv_b200_head_p8(_p(f.buf), _p(weight), _p(residual), _p(y), None if out8 is None else _p(out8.buf),
+                                    f.B, f.C, f.H, f.W, _stream(y)), "head_p8")
+    return y, out8
+
+
 def launch_count() -> int:
     """Kernels enqueued by libnconv_b200.so in this process so far."""
     return _lib.launch_count()

@@ -467,3 +467,43 @@ def test_convT4x4s2_tc_vs_fp64(cfg):
     assert (y.H, y.W) == (2 * H, 2 * W)
     assert grad_err(y.unpack(), ref) <= TC_TOL
     assert _ring_intact(y)
+
+
+@pytest.mark.parametrize("cfg", [(3, 32, 2, 20, 36, True), (1, 64, 1, 15, 20, False), (1, 32, 2, 24, 130, False),
+                                 (3, 32, 1, 48, 300, True)])
+def test_conv_small_p8(cfg):
+    from nconv_b200.ops import P8, conv_small_p8, tc_pack_weights, conv_tc, TC_S2
+    CI, CO, B, H, W, res = cfg
+    g = torch.Generator().manual_seed(sum(cfg[:5]))
+    x = torch.rand(B, CI, H, W, generator=g) * 255
+    w = torch.randn(CO, CI, 3, 3, generator=g) * 0.05
+    w1 = torch.randn(CO, CI, 1, 1, generator=g) * 0.05 if res else None
+    scale = torch.rand(CO, generator=g) + 0.5
+    shift = torch.randn(CO, generator=g)
+    ref = (F.conv2d(x.double(), w.double(), padding=1) * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)).relu()
+    if res:
+        ref = ref + F.conv2d(x.double(), w1.double())
+    y = conv_small_p8(x.to(dev()), w.to(dev()), None if w1 is None else w1.to(dev()), scale.to(dev()), shift.to(dev()),
+                      True, with_q=(H % 2 == 0 and W % 2 == 0))
+    assert grad_err(y.unpack(), ref) <= 1e-5
+    assert _ring_intact(y)
+    if y.qbuf is not None and CO == 32:
+        w2 = torch.randn(64, 32, 3, 3, generator=g) * 0.05
+        y2 = conv_tc(TC_S2, y, None, tc_pack_weights(TC_S2, w2.to(dev()), 32, 0), 64, None, None, False)
+        assert grad_err(y2.unpack(), F.conv2d(ref, w2.double(), stride=2, padding=1)) <= 2 * TC_TOL
+
+
+@pytest.mark.parametrize("cfg", [(64, 2, 15, 20), (32, 1, 24, 130)])
+def test_head_p8(cfg):
+    from nconv_b200.ops import P8, head_p8
+    C, B, H, W = cfg
+    g = torch.Generator().manual_seed(sum(cfg))
+    f = torch.randn(B, C, H, W, generator=g)
+    d = torch.rand(B, 1, H, W, generator=g) * 10
+    w = torch.randn(1, C, 3, 3, generator=g) * 0.1
+    ref = d.double() + F.conv2d(f.double(), w.double(), padding=1)
+    out8 = P8.empty(B, 1, H, W, dev())
+    y, y8 = head_p8(P8.pack(f.to(dev())), w.to(dev()), d.to(dev()), out8=out8)
+    assert grad_err(y, ref) <= 1e-5
+    assert grad_err(y8.unpack(), ref) <= 1e-5
+    assert _ring_intact(y8)

@@ -6,7 +6,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 for p in (ROOT, os.path.join(ROOT, "realtime-depth-estimation-nconv_b200")):
     sys.path.insert(0, p)
 import torch
-from nconv_b200.ops import P8, tc_pack_weights, conv3x3_tc
+from nconv_b200.ops import P8, tc_pack_weights, conv_tc, TC_S1
 
 dev = torch.device("cuda:0")
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
@@ -16,17 +16,17 @@ SHAPES = [(64, 0, 32, 480, 640), (32, 0, 32, 480, 640), (32, 32, 32, 480, 640), 
 for CA, CB, CO, H, W in SHAPES:
     a = P8.pack(torch.randn(B, CA, H, W, device=dev))
     b = P8.pack(torch.randn(B, CB, H, W, device=dev)) if CB else None
-    wp = tc_pack_weights(torch.randn(CO, CA + CB, 3, 3, device=dev) * 0.05)
+    wp = tc_pack_weights(TC_S1, torch.randn(CO, CA + CB, 3, 3, device=dev) * 0.05, CA, CB)
     shift = torch.zeros(CO, device=dev)
     y = P8.empty(B, CO, H, W, dev)
     for _ in range(3):
-        conv3x3_tc(a, b, wp, CO, None, shift, True, out=y)
+        conv_tc(TC_S1, a, b, wp, CO, None, shift, True, out=y)
     torch.cuda.synchronize()
     n = 10
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(n):
-        conv3x3_tc(a, b, wp, CO, None, shift, True, out=y)
+        conv_tc(TC_S1, a, b, wp, CO, None, shift, True, out=y)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / n
     px = B * H * W
