@@ -10,10 +10,11 @@ from nconv_b200.ops import P8, tc_pack_weights, conv_tc, TC_S1
 
 dev = torch.device("cuda:0")
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+ONLY = int(sys.argv[2]) if len(sys.argv) > 2 else None     # single shape (for ncu captures)
 SHAPES = [(64, 0, 32, 480, 640), (32, 0, 32, 480, 640), (32, 32, 32, 480, 640), (64, 64, 64, 240, 320), (64, 0, 64, 240, 320),
           (64, 0, 32, 240, 320), (32, 0, 32, 240, 320), (64, 64, 64, 120, 160), (64, 0, 64, 120, 160),
           (64, 64, 64, 60, 80), (64, 0, 64, 60, 80)]
-for CA, CB, CO, H, W in SHAPES:
+for CA, CB, CO, H, W in (SHAPES if ONLY is None else SHAPES[ONLY:ONLY + 1]):
     a = P8.pack(torch.randn(B, CA, H, W, device=dev))
     b = P8.pack(torch.randn(B, CB, H, W, device=dev)) if CB else None
     wp = tc_pack_weights(TC_S1, torch.randn(CO, CA + CB, 3, 3, device=dev) * 0.05, CA, CB)
