@@ -59,6 +59,16 @@ __device__ __forceinline__ float softplus_beta10(float x) {
   return bx > 20.0f ? x : log1pf(expf(bx)) / 10.0f;
 }
 
+// Packed fp32 FMA (sm_100 FFMA2): acc.{lo,hi} += w.{lo,hi} * s.  ptxas folds the {s, s} pack into
+// the instruction's scalar-broadcast operand form (`FFMA2 Rd, Rw.F32x2.HI_LO, Rs.F32, Rd`), so no
+// extra register or MOV is spent on it.
+typedef unsigned long long u64;
+__device__ __forceinline__ void ffma2(u64& acc, u64 w, float s) {
+  asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%2, %2};\n\tfma.rn.f32x2 %0, %1, t, %0;\n\t}" : "+l"(acc) : "l"(w), "f"(s));
+}
+__device__ __forceinline__ float lo32f(u64 v) { return __uint_as_float((unsigned)(v & 0xffffffffull)); }
+__device__ __forceinline__ float hi32f(u64 v) { return __uint_as_float((unsigned)(v >> 32)); }
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 }  // namespace nconv

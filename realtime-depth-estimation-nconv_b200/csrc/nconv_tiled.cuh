@@ -142,11 +142,27 @@ nconv_tiled(const TiledArgs a) {
     }
   }
 
-  float accN[CO_T][PX], accD[CO_T][PX];
+  // Accumulators.  With an even CO_T the FMA stream is packed: one FFMA2 (fma.rn.f32x2, sm_100)
+  // updates two adjacent output channels of one pixel — the weight pair (w[o], w[o+1]) comes
+  // straight from a 64-bit half of the broadcast LDS.128 and the activation is the scalar
+  // broadcast operand — so the 2*PX*CO_T FMAs per tap cost PX*CO_T issue slots.  fp32 peak needs
+  // every issue slot with scalar FFMA (measured 72 TFLOP/s), which a loop that also issues LDS and
+  // address arithmetic cannot give; FFMA2 runs at the same flop rate on half the slots.
+  constexpr bool PACK = (CO_T % 2 == 0);
+  constexpr int CO_P = PACK ? CO_T / 2 : 1;
+  float accN[PACK ? 1 : CO_T][PX], accD[PACK ? 1 : CO_T][PX];
+  u64 accN2[CO_P][PX], accD2[CO_P][PX];
+  if constexpr (PACK) {
 #pragma unroll
-  for (int o = 0; o < CO_T; ++o)
+    for (int o = 0; o < CO_P; ++o)
 #pragma unroll
-    for (int p = 0; p < PX; ++p) { accN[o][p] = 0.f; accD[o][p] = 0.f; }
+      for (int p = 0; p < PX; ++p) { accN2[o][p] = 0ull; accD2[o][p] = 0ull; }
+  } else {
+#pragma unroll
+    for (int o = 0; o < CO_T; ++o)
+#pragma unroll
+      for (int p = 0; p < PX; ++p) { accN[o][p] = 0.f; accD[o][p] = 0.f; }
+  }
 
   const int gx0a = ox0 - PAD - OFF;   // global col of staged col 0 (multiple of 4)
   const int gy0 = oy0 - PAD;
@@ -255,22 +271,53 @@ nconv_tiled(const TiledArgs a) {
         }
 #pragma unroll
         for (int v = 0; v < K; ++v) {
-          float wv[CO_T];
+          if constexpr (PACK) {
+            u64 w2[CO_P];
+            if constexpr (CO_T % 4 == 0) {
 #pragma unroll
-          for (int o = 0; o < CO_T; o += WV) VecLoad<WV>::ld(wv + o, wrow + (u * K + v) * CO_T + o);
+              for (int o = 0; o < CO_P; o += 2) {
+                const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(wrow + (u * K + v) * CO_T + 2 * o);
+                w2[o] = t.x; w2[o + 1] = t.y;
+              }
+            } else {
 #pragma unroll
-          for (int o = 0; o < CO_T; ++o)
-#pragma unroll
-            for (int p = 0; p < PX; ++p) {
-              accN[o][p] = fmaf(wv[o], xr[OFF + p + v], accN[o][p]);
-              accD[o][p] = fmaf(wv[o], cr[OFF + p + v], accD[o][p]);
+              for (int o = 0; o < CO_P; ++o) w2[o] = *reinterpret_cast<const u64*>(wrow + (u * K + v) * CO_T + 2 * o);
             }
+#pragma unroll
+            for (int o = 0; o < CO_P; ++o)
+#pragma unroll
+              for (int p = 0; p < PX; ++p) {
+                ffma2(accN2[o][p], w2[o], xr[OFF + p + v]);
+                ffma2(accD2[o][p], w2[o], cr[OFF + p + v]);
+              }
+          } else {
+            float wv[CO_T];
+#pragma unroll
+            for (int o = 0; o < CO_T; o += WV) VecLoad<WV>::ld(wv + o, wrow + (u * K + v) * CO_T + o);
+#pragma unroll
+            for (int o = 0; o < CO_T; ++o)
+#pragma unroll
+              for (int p = 0; p < PX; ++p) {
+                accN[o][p] = fmaf(wv[o], xr[OFF + p + v], accN[o][p]);
+                accD[o][p] = fmaf(wv[o], cr[OFF + p + v], accD[o][p]);
+              }
+          }
         }
       }
     }
   }
 
   // ---- epilogue
+  float aN[CO_T][PX], aD[CO_T][PX];
+#pragma unroll
+  for (int o = 0; o < CO_T; ++o)
+#pragma unroll
+    for (int p = 0; p < PX; ++p) {
+      if constexpr (PACK) {
+        aN[o][p] = (o & 1) ? hi32f(accN2[o >> 1][p]) : lo32f(accN2[o >> 1][p]);
+        aD[o][p] = (o & 1) ? hi32f(accD2[o >> 1][p]) : lo32f(accD2[o >> 1][p]);
+      } else { aN[o][p] = accN[o][p]; aD[o][p] = accD[o][p]; }
+    }
   const int oy = oy0 + ty, ox = ox0 + PX * tx;
   if (BWD) {
     if (oy >= a.HO) return;
@@ -288,8 +335,8 @@ nconv_tiled(const TiledArgs a) {
       float gxv[PX], gcv[PX];
 #pragma unroll
       for (int p = 0; p < PX; ++p) {
-        gxv[p] = accN[o][p] * cv[p];
-        gcv[p] = fmaf(accN[o][p], xv[p], accD[o][p]);
+        gxv[p] = aN[o][p] * cv[p];
+        gcv[p] = fmaf(aN[o][p], xv[p], aD[o][p]);
       }
       if (vec) {
         if (a.y) *reinterpret_cast<float4*>(a.y + base) = make_float4(gxv[0], gxv[1], gxv[2], gxv[3]);
@@ -316,8 +363,8 @@ nconv_tiled(const TiledArgs a) {
         float n7 = 0.f, d7 = 0.f;
 #pragma unroll
         for (int o = 0; o < CO_T; ++o) {
-          float D = accD[o][p];
-          float x6 = accN[o][p] / (D + a.eps) + s_bias[o];
+          float D = aD[o][p];
+          float x6 = aN[o][p] / (D + a.eps) + s_bias[o];
           float c6 = D / s_sum[o];
           float w7 = __ldg(a.w7 + o);
           n7 = fmaf(w7, x6 * c6, n7);
@@ -344,8 +391,8 @@ nconv_tiled(const TiledArgs a) {
     const float bo = s_bias[o], so = s_sum[o];
 #pragma unroll
     for (int p = 0; p < PX; ++p) {
-      float D = accD[o][p];
-      yv[o][p] = accN[o][p] / (D + a.eps) + bo;
+      float D = aD[o][p];
+      yv[o][p] = aN[o][p] / (D + a.eps) + bo;
       cv[o][p] = D / so;
     }
   }
