@@ -1,6 +1,8 @@
 // NConv2d forward launchers (C ABI) — /root/reference/models/step1.py:116-149 and the fused
 // DNET stages (step1.py:51-94).  The kernel itself is nconv_tiled.cuh.
 #include "nconv_tiled.cuh"
+#include "nconv_stream.cuh"
+#include <cstdlib>
 
 namespace nconv {
 
@@ -84,6 +86,22 @@ extern "C" int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* 
     if (d->CA == 8 && d->CB == 8 && d->CO == 8)
       return launch_tiled<8, 8, 8, 8, 3, 1, NCONV_B200_F_TAIL>(a, st);
     return NCONV_ERR_UNSUPPORTED;
+  }
+  // HBM-bound small-channel shapes (BASELINE.json config 2): streaming kernel, needs 128-bit rows.
+  // NCONV_B200_NO_STREAM=1 forces the tiled kernel (A/B measurements only).
+  static const bool no_stream = getenv("NCONV_B200_NO_STREAM") != nullptr;
+  if (!no_stream && a.vec_ok && d->CB == 0 && !pool && 2 * d->pad + 1 == d->K && (d->flags & ~NCONV_B200_F_THRESH) == 0) {
+#define NCONV_STREAM_CASE(ci_, co_, k_, pf_)                                                          \
+    if (d->CA == ci_ && d->CO == co_ && d->K == k_) {                                                \
+      if (thresh) return launch_stream<ci_, co_, k_, pf_, true>(d->xa, nullptr, d->w, d->bias, d->y, d->cout, d->B, \
+                                                                d->H, d->W, d->eps, d->thr, st);     \
+      return launch_stream<ci_, co_, k_, pf_, false>(d->xa, d->ca, d->w, d->bias, d->y, d->cout, d->B, d->H,  \
+                                                     d->W, d->eps, d->thr, st);                      \
+    }
+    NCONV_STREAM_CASE(1, 2, 3, 3)
+    NCONV_STREAM_CASE(2, 2, 3, 3)
+    // (4,4,3), (1,2,5), (2,2,5) measured no faster than the tiled kernel (issue-bound): left on it.
+#undef NCONV_STREAM_CASE
   }
   // DNET shapes (step1.py:38-49)
   NCONV_CASE(1, 0, 8, 8, 5, 2, NCONV_B200_F_THRESH)

@@ -57,6 +57,24 @@ def test_nconv2d_layer_vs_reference_golden(golden, K, idx):
         assert grad_err(t, T(g[p + name])) <= GRAD_TOL, name
 
 
+@pytest.mark.parametrize("cfg", [(1, 2, 3), (2, 2, 3)])
+@pytest.mark.parametrize("shape", [(2, 37, 132), (1, 9, 128), (3, 50, 300), (1, 480, 640)])
+def test_nconv2d_stream_kernel_vs_oracle(K, cfg, shape):
+    """The streaming kernel (csrc/nconv_stream.cuh: config-2 small-channel shapes, W % 4 == 0) against the
+    CPU oracle: partial strips, segments shorter than RS, image borders, exact-zero confidence."""
+    ci, co, k = cfg
+    B, H, W = shape
+    g = torch.Generator().manual_seed(B * 1000 + H + ci * 7 + k)
+    x = torch.rand(B, ci, H, W, generator=g) * 10
+    c = torch.rand(B, ci, H, W, generator=g) * (torch.rand(B, ci, H, W, generator=g) < 0.5)
+    w = O.softplus_beta10(torch.rand(co, ci, k, k, generator=g))
+    b = torch.full((co,), 0.01)
+    y_ref, c_ref = O.nconv2d(x, c, w, b, (k // 2, k // 2))
+    y, cout = K.nconv2d(x.to(dev()), c.to(dev()), w.to(dev()), b.to(dev()), k // 2, k // 2, 1e-7)
+    assert O.max_rel_err(y, y_ref) <= REL_TOL
+    assert O.max_rel_err(cout, c_ref) <= REL_TOL
+
+
 def test_nconv2d_module_hook_semantics(K):
     """KA4: training forward overwrites the stored weight with softplus(w, beta=10) in place;
     eval leaves it alone; the gradient is straight-through (w.r.t. the transformed weight)."""
