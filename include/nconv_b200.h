@@ -141,6 +141,51 @@ int nconv_b200_convT4x4s2_fwd(const float* a, const float* b, const float* w, co
                               const float* shift, float* y, int B, int CA, int CB, int CO, int H,
                               int W, int relu, void* stream);
 
+/* ---- training mode of the RGB-guided stack (train_step2.py:60-66 runs SETP2_BP_TRAIN under
+ * model.train(): BatchNorm2d with batch statistics, autograd through every conv of step2.py) ---- */
+
+/* scratch for the per-channel fp64 reductions below */
+size_t nconv_b200_train_ws_bytes(int C);
+
+/* nn.BatchNorm2d training forward (step2.py:141,188,212) fused with ReLU and the residual that
+ * RGBEncoder adds after the activation (:151-152): y = act(gamma*(x-mean_B)/sqrt(var_B+eps)+beta)
+ * (+residual); running_mean/var updated with `momentum` (unbiased variance) unless NULL;
+ * scale/shift/save_mean/save_rstd: [C] outputs kept for backward. */
+int nconv_b200_bn_train_fwd(const float* x, const float* gamma, const float* beta, float* running_mean,
+                            float* running_var, const float* residual, float* y, float* scale,
+                            float* shift, float* save_mean, float* save_rstd, void* ws, int B, int C,
+                            int H, int W, float eps, float momentum, int relu, void* stream);
+
+/* backward of the above: gz (grad of the BatchNorm input z), ggamma, gbeta from gy (grad of the
+ * activation output), z and the saved scale/shift/mean/rstd. */
+int nconv_b200_bn_train_bwd(const float* gy, const float* z, const float* scale, const float* shift,
+                            const float* mean, const float* rstd, const float* gamma, float* gz,
+                            float* ggamma, float* gbeta, void* ws, int B, int C, int H, int W, int relu,
+                            void* stream);
+
+/* backward of ReLU(conv + bias) (ConvBlock, step2.py:290-297): g = gy*[y>0] (g may be NULL),
+ * gbias[c] = sum g; relu=0 gives the plain per-channel sum of gy. */
+int nconv_b200_relu_bias_bwd(const float* gy, const float* y, float* g, float* gbias, void* ws, int B,
+                             int C, int H, int W, int relu, void* stream);
+
+/* weight gradient gw[CO][CI][K][K] = sum_{b,oy,ox} g[b,co,oy,ox]*x[b,ci,oy*S-P+u,ox*S-P+v] of
+ * Conv2d (K,S,P) in {(1,1,0),(1,2,0),(3,1,1),(3,2,1)}; (4,2,1) with g and x swapped is
+ * ConvTranspose2d(4,2,1)'s [CI][CO][4][4] gradient.  ws: split-K partials. */
+size_t nconv_b200_conv_wgrad_ws_bytes(int CI, int CO, int K);
+int nconv_b200_conv_wgrad(const float* g, const float* x, float* gw, void* ws, size_t ws_bytes, int B,
+                          int CI, int CO, int H, int W, int K, int S, int P, void* stream);
+
+/* data gradient of a stride-2 Conv2d (transposed=0, w [CO][CI][K][K]) or of ConvTranspose2d(4,2,1)
+ * (transposed=1, w [CI][CO][4][4]); gx: [B,CI,H,W]. */
+size_t nconv_b200_conv_dgrad_ws_bytes(int CI, int CO, int K);
+int nconv_b200_conv_dgrad_gather(const float* g, const float* w, float* gx, void* ws, int B, int CI,
+                                 int CO, int H, int W, int K, int S, int P, int transposed,
+                                 void* stream);
+
+/* wf[CI][CO][K][K] = flipped, transposed w[CO][CI][K][K]: nconv_b200_conv2d_fwd(g, wf) is the data
+ * gradient of a stride-1 "same" convolution. */
+int nconv_b200_wflip(const float* w, float* wf, int CO, int CI, int K, void* stream);
+
 /* F.interpolate(mode='bilinear', align_corners=True) to (HO,WO) — step2.py:252,271 */
 int nconv_b200_bilinear_ac_fwd(const float* x, float* y, int planes, int H, int W, int HO, int WO,
                                void* stream);

@@ -184,6 +184,77 @@ def gen_setp2(r1, r2):
     np.savez_compressed(os.path.join(OUT, "setp2_export.npz"), **out)
 
 
+SETP2_TRAIN_HW = (480, 640)     # the reference's step 1 crops [1:481,1:641]: SETP2 only runs at this size
+SUBSAMPLE_ABOVE, SUBSAMPLE_STRIDE = 20000, 13
+
+
+def subsample(a: np.ndarray) -> np.ndarray:
+    """Full tensor when small, every 13th element of the flattened tensor otherwise (keeps the
+    fixture small; the test applies the same rule to the CUDA result)."""
+    f = a.reshape(-1)
+    return f if f.size <= SUBSAMPLE_ABOVE else f[::SUBSAMPLE_STRIDE]
+
+
+def _setp2_train_run(r1, r2, double, tmpdir):
+    """One training-mode forward/backward of the reference SETP2_BP_TRAIN (train_step2.py:60-64):
+    frozen step 1 (hook still fires), BatchNorm with batch statistics, autograd through the whole
+    stack; fixed linear loss sum_k <d_k, G_k> over the 4 scales of both streams."""
+    H, W = SETP2_TRAIN_HW
+    torch.manual_seed(3)
+    s1 = r1.SETP1_NCONV()
+    os.makedirs(os.path.join(tmpdir, "checkpoints"), exist_ok=True)
+    torch.save({"state_dict": {"module." + k: v for k, v in s1.state_dict().items()}},
+               os.path.join(tmpdir, "checkpoints", "golden_step1.pth.tar"))
+    cwd = os.getcwd()
+    os.chdir(tmpdir)
+    try:
+        torch.manual_seed(5)
+        m = r2.SETP2_BP_TRAIN("golden_step1")
+    finally:
+        os.chdir(cwd)
+    m.train()
+    rgb0, d0, rgb1, d1 = setp2_inputs(1, seed=9, H=H, W=W)
+    g = torch.Generator().manual_seed(77)
+    Gs = [torch.randn(2, 1, H // f, W // f, generator=g) for f in (8, 4, 2, 1)]
+    saved = torch.Tensor.float
+    if double:
+        m = m.double(); rgb0, d0, rgb1, d1 = (t.double() for t in (rgb0, d0, rgb1, d1)); Gs = [t.double() for t in Gs]
+        torch.Tensor.float = lambda t: t.double()
+    try:
+        with ref_shim.two_arg_step1():
+            a, b = m(rgb0, d0, rgb1, d1)
+        depths = [torch.cat((x, y), 0) for x, y in zip(a, b)]
+        sum((d * G).sum() for d, G in zip(depths, Gs)).backward()
+    finally:
+        torch.Tensor.float = saved
+    return m, depths
+
+
+def gen_setp2_train(r1, r2):
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        m, depths = _setp2_train_run(r1, r2, False, td)
+        m64, depths64 = _setp2_train_run(r1, r2, True, td)
+    out = {"hw": np.array(SETP2_TRAIN_HW)}
+    for i, d in enumerate(depths):
+        out["d%d" % i] = subsample(_np(d))
+        out["d64_%d" % i] = subsample(_np(depths64[i]).astype(np.float64))
+    p64 = dict(m64.named_parameters())
+    names = []
+    for k, p in m.named_parameters():
+        if p.grad is None:
+            continue
+        names.append(k)
+        out["g_" + k] = subsample(_np(p.grad))
+        out["g64_" + k] = subsample(_np(p64[k].grad))
+        out["gnorm_" + k] = np.array(float(p.grad.double().norm()))
+    out["grad_names"] = np.array(names)
+    for k, v in m.state_dict().items():
+        if ("running_" in k or "num_batches" in k) and not k.startswith("step1.") and "rgb_encoder4" not in k:
+            out["bn_" + k] = _np(v)
+    np.savez_compressed(os.path.join(OUT, "setp2_train.npz"), **out)
+
+
 def main():
     assert ref_shim.reference_available(), "needs /root/reference"
     os.makedirs(OUT, exist_ok=True)
@@ -198,6 +269,8 @@ def main():
         gen_setp1_train(r1)
     if not only or "setp2" in only:
         gen_setp2(r1, r2)
+    if not only or "setp2train" in only:
+        gen_setp2_train(r1, r2)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

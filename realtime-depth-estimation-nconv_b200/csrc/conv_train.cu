@@ -1,0 +1,655 @@
+// Training-mode kernels of the RGB-guided stack (SETP2_BP_TRAIN, /root/reference/models/step2.py:22-77
+// run under train_step2.py:60-66, i.e. model.train(): BatchNorm2d normalises with BATCH statistics and
+// autograd differentiates every Conv2d / ConvTranspose2d / BatchNorm2d / ReLU of the stack).  fp32 NCHW.
+//
+//   bn_train_stats / bn_train_finalize / affine_act   BatchNorm2d training forward (+ReLU, + residual)
+//   bn_bwd_reduce / bn_bwd_apply                      BatchNorm2d (+ReLU) backward
+//   relu_bias_bwd                                     ConvBlock's ReLU(conv + bias) backward: masks the
+//                                                     gradient and reduces the bias gradient
+//   channel_sum                                       bias gradient of a plain convolution
+//   conv_wgrad<K,S>                                   weight gradient (also ConvTranspose2d's, roles swapped)
+//   conv_gather<MODE,K,S>                             data gradient of the stride-2 convolutions
+//                                                     (transposed gather) and of ConvTranspose2d(4,2,1)
+//                                                     (a strided 4x4 convolution of the gradient)
+//   wflip                                             W[co][ci][u][v] -> W'[ci][co][K-1-u][K-1-v]: the data
+//                                                     gradient of a stride-1 "same" convolution is the
+//                                                     forward kernel (conv_simt.cu) run on W'
+//
+// Per-channel reductions accumulate in double (per-thread fp32 partials over <= 64 values, combined in
+// fp64 through shared memory and one atomicAdd(double) per CTA), so BatchNorm statistics of the
+// un-normalised RGB activations (mean >> std) do not lose digits and results do not depend on the grid.
+#include "common.cuh"
+#include "nconv_b200.h"
+#include "launch_count.h"
+#include <cstdio>
+
+namespace nconv {
+
+constexpr int RED_THREADS = 256;
+
+__device__ __forceinline__ double block_sum_double(double v, double* sh) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+  __syncthreads();
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (warp == 0) {
+    t = (lane < RED_THREADS / 32) ? sh[lane] : 0.0;
+#pragma unroll
+    for (int d = 4; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+  }
+  return t;   // valid in thread 0
+}
+
+// ---- BatchNorm training forward ---------------------------------------------------------------------
+// acc[c][0] += sum(x - pivot[c]),  acc[c][1] += sum((x - pivot[c])^2); pivot = x[0, c, 0, 0] keeps the
+// one-pass variance well conditioned.  grid (chunks, C, B).
+__global__ void __launch_bounds__(RED_THREADS) bn_stats_kernel(const float* __restrict__ x, double* __restrict__ acc,
+                                                               int C, int HW) {
+  __shared__ double sh[RED_THREADS / 32];
+  const int c = blockIdx.y, b = blockIdx.z;
+  const float pivot = __ldg(x + (size_t)c * HW);
+  const float* p = x + ((size_t)b * C + c) * HW;
+  double s1 = 0.0, s2 = 0.0;
+  const int per = (HW + gridDim.x - 1) / gridDim.x;
+  const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  for (int i0 = lo + threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
+    float f1 = 0.f, f2 = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < 32; ++k) {
+      const int i = i0 + k * RED_THREADS;
+      if (i < hi) { const float d = __ldg(p + i) - pivot; f1 += d; f2 = fmaf(d, d, f2); }
+    }
+    s1 += f1; s2 += f2;
+  }
+  s1 = block_sum_double(s1, sh);
+  s2 = block_sum_double(s2, sh);
+  if (threadIdx.x == 0) { atomicAdd(acc + 2 * c, s1); atomicAdd(acc + 2 * c + 1, s2); }
+}
+
+// mean/var from the sums; scale/shift for the apply pass; save mean and rstd for backward; update the
+// running statistics exactly as nn.BatchNorm2d does (momentum, unbiased variance).
+__global__ void bn_finalize_kernel(const double* __restrict__ acc, const float* __restrict__ x, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* __restrict__ running_mean,
+                                   float* __restrict__ running_var, float* __restrict__ scale, float* __restrict__ shift,
+                                   float* __restrict__ save_mean, float* __restrict__ save_rstd, int C, int HW, double n,
+                                   float eps, float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double pivot = (double)__ldg(x + (size_t)c * HW);
+  const double m1 = acc[2 * c] / n, m2 = acc[2 * c + 1] / n;
+  const double mean = pivot + m1;
+  double var = m2 - m1 * m1;
+  if (var < 0.0) var = 0.0;
+  const float rstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+  scale[c] = g * rstd;
+  shift[c] = bt - (float)mean * g * rstd;
+  save_mean[c] = (float)mean;
+  save_rstd[c] = rstd;
+  if (running_mean) {
+    const double unbiased = n > 1.0 ? var * n / (n - 1.0) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+  }
+}
+
+// y = act(x * scale[c] + shift[c]) (+ residual); in place allowed (y == x).
+__global__ void __launch_bounds__(256) affine_act_kernel(const float* __restrict__ x, const float* __restrict__ scale,
+                                                         const float* __restrict__ shift, const float* __restrict__ residual,
+                                                         float* __restrict__ y, int C, int HW, long long total, int relu) {
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += 256ll * gridDim.x) {
+    const int c = (int)((i / HW) % C);
+    float v = fmaf(x[i], __ldg(scale + c), __ldg(shift + c));
+    if (relu) v = fmaxf(v, 0.f);
+    if (residual) v += __ldg(residual + i);
+    y[i] = v;
+  }
+}
+
+// ---- BatchNorm (+ReLU) backward ---------------------------------------------------------------------
+// z: the BatchNorm input saved by forward.  g = gy * [z*scale+shift > 0] (ReLU mask, if relu).
+// acc[c][0] += sum g, acc[c][1] += sum g * xhat.
+__global__ void __launch_bounds__(RED_THREADS) bn_bwd_reduce_kernel(const float* __restrict__ gy, const float* __restrict__ z,
+                                                                    const float* __restrict__ scale, const float* __restrict__ shift,
+                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                    double* __restrict__ acc, int C, int HW, int relu) {
+  __shared__ double sh[RED_THREADS / 32];
+  const int c = blockIdx.y, b = blockIdx.z;
+  const float sc = scale[c], sf = shift[c], mu = mean[c], rs = rstd[c];
+  const size_t base = ((size_t)b * C + c) * HW;
+  double s1 = 0.0, s2 = 0.0;
+  const int per = (HW + gridDim.x - 1) / gridDim.x;
+  const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  for (int i0 = lo + threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
+    float f1 = 0.f, f2 = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < 32; ++k) {
+      const int i = i0 + k * RED_THREADS;
+      if (i < hi) {
+        const float zv = __ldg(z + base + i);
+        float g = __ldg(gy + base + i);
+        if (relu && !(fmaf(zv, sc, sf) > 0.f)) g = 0.f;
+        f1 += g; f2 = fmaf(g, (zv - mu) * rs, f2);
+      }
+    }
+    s1 += f1; s2 += f2;
+  }
+  s1 = block_sum_double(s1, sh);
+  s2 = block_sum_double(s2, sh);
+  if (threadIdx.x == 0) { atomicAdd(acc + 2 * c, s1); atomicAdd(acc + 2 * c + 1, s2); }
+}
+
+// gz = gamma*rstd * (g - sum_g/n - xhat * sum_gxhat/n); also emits ggamma = sum_gxhat, gbeta = sum_g once.
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ gy, const float* __restrict__ z,
+                                                           const float* __restrict__ scale, const float* __restrict__ shift,
+                                                           const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                           const float* __restrict__ gamma, const double* __restrict__ acc,
+                                                           float* __restrict__ gz, float* __restrict__ ggamma,
+                                                           float* __restrict__ gbeta, int C, int HW, long long total, double n,
+                                                           int relu) {
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C; c += 256) {
+      if (gbeta) gbeta[c] = (float)acc[2 * c];
+      if (ggamma) ggamma[c] = (float)acc[2 * c + 1];
+    }
+  }
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += 256ll * gridDim.x) {
+    const int c = (int)((i / HW) % C);
+    const float sc = scale[c], sf = shift[c], mu = mean[c], rs = rstd[c];
+    const float zv = z[i];
+    float g = gy[i];
+    if (relu && !(fmaf(zv, sc, sf) > 0.f)) g = 0.f;
+    const float xh = (zv - mu) * rs;
+    const float m1 = (float)(acc[2 * c] / n), m2 = (float)(acc[2 * c + 1] / n);
+    const float gm = gamma ? gamma[c] : 1.f;
+    gz[i] = gm * rs * (g - m1 - xh * m2);
+  }
+}
+
+// ---- ReLU(conv + bias) backward: g = gy * [y > 0]; gbias[c] = sum g --------------------------------
+__global__ void __launch_bounds__(RED_THREADS) relu_bias_bwd_kernel(const float* __restrict__ gy, const float* __restrict__ y,
+                                                                    float* __restrict__ g, double* __restrict__ acc, int C,
+                                                                    int HW, int relu) {
+  __shared__ double sh[RED_THREADS / 32];
+  const int c = blockIdx.y, b = blockIdx.z;
+  const size_t base = ((size_t)b * C + c) * HW;
+  double s1 = 0.0;
+  const int per = (HW + gridDim.x - 1) / gridDim.x;
+  const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  for (int i0 = lo + threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
+    float f1 = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < 32; ++k) {
+      const int i = i0 + k * RED_THREADS;
+      if (i < hi) {
+        float v = __ldg(gy + base + i);
+        if (relu && !(__ldg(y + base + i) > 0.f)) v = 0.f;
+        if (g) g[base + i] = v;
+        f1 += v;
+      }
+    }
+    s1 += f1;
+  }
+  s1 = block_sum_double(s1, sh);
+  if (threadIdx.x == 0) atomicAdd(acc + c, s1);
+}
+
+__global__ void double_to_float_kernel(const double* __restrict__ a, float* __restrict__ o, int n, int stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) o[i] = (float)a[(size_t)i * stride];
+}
+
+static inline int red_chunks(int HW, int C, int B) {
+  // enough CTAs to fill the machine, each with >= 8K elements
+  int want = (148 * 8 + C * B - 1) / (C * B);
+  int maxc = (HW + 8191) / 8192;
+  int ch = want < maxc ? want : maxc;
+  return ch < 1 ? 1 : ch;
+}
+
+}  // namespace nconv
+
+using namespace nconv;
+
+extern "C" size_t nconv_b200_train_ws_bytes(int C) { return (size_t)2 * C * sizeof(double); }
+
+// BatchNorm2d training forward (+ReLU, + residual added after the activation, RGBEncoder :151-152).
+// ws: nconv_b200_train_ws_bytes(C) of scratch.  scale/shift/save_mean/save_rstd: [C] outputs.
+extern "C" int nconv_b200_bn_train_fwd(const float* x, const float* gamma, const float* beta, float* running_mean,
+                                       float* running_var, const float* residual, float* y, float* scale, float* shift,
+                                       float* save_mean, float* save_rstd, void* ws, int B, int C, int H, int W,
+                                       float eps, float momentum, int relu, void* stream) {
+  if (!x || !y || !scale || !shift || !save_mean || !save_rstd || !ws) return NCONV_ERR_BAD_ARG;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HW = H * W;
+  const long long total = (long long)B * C * HW;
+  NCONV_RETURN_IF_ERR(cudaMemsetAsync(ws, 0, nconv_b200_train_ws_bytes(C), st));
+  {
+    LaunchScope ls(st, "bn_train_stats", 3.0 * total, 4.0 * total);
+    bn_stats_kernel<<<dim3(red_chunks(HW, C, B), C, B), RED_THREADS, 0, st>>>(x, (double*)ws, C, HW);
+  }
+  {
+    LaunchScope ls(st, "bn_train_finalize", 0.0, 0.0);
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>((const double*)ws, x, gamma, beta, running_mean, running_var, scale,
+                                                        shift, save_mean, save_rstd, C, HW, (double)B * HW, eps, momentum);
+  }
+  {
+    LaunchScope ls(st, "bn_train_apply", 2.0 * total, 4.0 * total * (residual ? 3.0 : 2.0));
+    const int blocks = (int)((total + 256 * 8 - 1) / (256 * 8) < 148 * 16 ? (total + 256 * 8 - 1) / (256 * 8) : 148 * 16);
+    affine_act_kernel<<<blocks < 1 ? 1 : blocks, 256, 0, st>>>(x, scale, shift, residual, y, C, HW, total, relu);
+  }
+  return (int)cudaGetLastError();
+}
+
+// BatchNorm2d (+ReLU) backward.  z = the BatchNorm input of forward; scale/shift/mean/rstd as saved.
+extern "C" int nconv_b200_bn_train_bwd(const float* gy, const float* z, const float* scale, const float* shift,
+                                       const float* mean, const float* rstd, const float* gamma, float* gz, float* ggamma,
+                                       float* gbeta, void* ws, int B, int C, int H, int W, int relu, void* stream) {
+  if (!gy || !z || !scale || !shift || !mean || !rstd || !gz || !ws) return NCONV_ERR_BAD_ARG;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HW = H * W;
+  const long long total = (long long)B * C * HW;
+  NCONV_RETURN_IF_ERR(cudaMemsetAsync(ws, 0, nconv_b200_train_ws_bytes(C), st));
+  {
+    LaunchScope ls(st, "bn_bwd_reduce", 5.0 * total, 8.0 * total);
+    bn_bwd_reduce_kernel<<<dim3(red_chunks(HW, C, B), C, B), RED_THREADS, 0, st>>>(gy, z, scale, shift, mean, rstd,
+                                                                                   (double*)ws, C, HW, relu);
+  }
+  {
+    LaunchScope ls(st, "bn_bwd_apply", 8.0 * total, 12.0 * total);
+    long long blocks = (total + 256 * 8 - 1) / (256 * 8);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    bn_bwd_apply_kernel<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(gy, z, scale, shift, mean, rstd, gamma,
+                                                                        (const double*)ws, gz, ggamma, gbeta, C, HW, total,
+                                                                        (double)B * HW, relu);
+  }
+  return (int)cudaGetLastError();
+}
+
+// g = gy * [y > 0] (if relu; g may be null when only the channel sums are wanted), gbias[c] = sum g.
+extern "C" int nconv_b200_relu_bias_bwd(const float* gy, const float* y, float* g, float* gbias, void* ws, int B, int C,
+                                        int H, int W, int relu, void* stream) {
+  if (!gy || !ws || (relu && !y)) return NCONV_ERR_BAD_ARG;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HW = H * W;
+  const long long total = (long long)B * C * HW;
+  NCONV_RETURN_IF_ERR(cudaMemsetAsync(ws, 0, nconv_b200_train_ws_bytes(C), st));
+  {
+    LaunchScope ls(st, "relu_bias_bwd", 2.0 * total, 4.0 * total * (g ? 3.0 : (relu ? 2.0 : 1.0)));
+    relu_bias_bwd_kernel<<<dim3(red_chunks(HW, C, B), C, B), RED_THREADS, 0, st>>>(gy, y, g, (double*)ws, C, HW, relu);
+  }
+  if (gbias) {
+    LaunchScope ls(st, "channel_sum_out", 0.0, 0.0);
+    double_to_float_kernel<<<(C + 127) / 128, 128, 0, st>>>((const double*)ws, gbias, C, 1);
+  }
+  return (int)cudaGetLastError();
+}
+
+// =====================================================================================================
+// Weight gradient:  gW[co][ci][u][v] = sum_{b,oy,ox} g[b,co,oy,ox] * x[b,ci, oy*S-P+u, ox*S-P+v]
+// (Conv2d K in {1,3}, S in {1,2}; ConvTranspose2d(4,2,1) is the same sum with the roles of input and
+// output gradient swapped, K=4 S=2 P=1.)
+//
+// A GEMM C[co][(ci,u,v)] = G[co][px] * X[px][(ci,u,v)] with the pixel axis as the contraction.  A CTA
+// owns a CO_B x 8(ci) x K*K block of C and a strided subset of pixel chunks (split-K); a chunk is 64
+// output pixels of one row: G tile [CO_B][64] and the x halo rows [8][K][(64-1)*S+K] go through shared
+// memory, a thread accumulates 4(co) x 1(ci) x K*K taps in registers over its 64/NSUB pixels with the
+// x window sliding in registers (S new columns per pixel), then the NSUB pixel sub-ranges are summed
+// through shared memory and the CTA writes its partial block; wgrad_reduce sums the split-K partials
+// in a fixed order (deterministic).
+// =====================================================================================================
+namespace nconv {
+
+constexpr int WG_CH = 64;        // output pixels per chunk
+constexpr int WG_CIB = 8;        // input channels per CTA
+
+struct WgradArgs {
+  const float* g; const float* x; float* part;
+  int B, CI, CO, H, W, HO, WO, nsplit, chunks_x;
+  long long chunks;
+};
+
+template <int K, int S, int P, int TMG>
+__global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
+  constexpr int CO_B = 4 * TMG, NSUB = 256 / (TMG * WG_CIB), PXT = WG_CH / NSUB;
+  constexpr int XC = (WG_CH - 1) * S + K;                   // staged x columns
+  constexpr int XCP = XC | 1;                               // odd row pitch: the 8 channels of a warp hit 8 distinct banks
+  constexpr int GP = WG_CH + 1;
+  constexpr int PER = 4 * K * K;
+  constexpr int TILE = CO_B * GP + WG_CIB * K * XCP, RED = TMG * WG_CIB * PER;
+  static_assert(NSUB >= 1 && PXT * NSUB == WG_CH, "bad wgrad tiling");
+  __shared__ float s_all[TILE > RED ? TILE : RED];
+  float* s_g = s_all;
+  float* s_x = s_all + CO_B * GP;
+
+  const int tid = threadIdx.x;
+  const int ci_l = tid % WG_CIB, tm = (tid / WG_CIB) % TMG, sub = tid / (WG_CIB * TMG);
+  const int ci0 = blockIdx.y * WG_CIB, co0 = blockIdx.z * CO_B;
+
+  float acc[4][K * K];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int t = 0; t < K * K; ++t) acc[j][t] = 0.f;
+
+  for (long long ch = blockIdx.x; ch < a.chunks; ch += a.nsplit) {
+    const int cx = (int)(ch % a.chunks_x);
+    const long long r = ch / a.chunks_x;
+    const int oy = (int)(r % a.HO), b = (int)(r / a.HO);
+    const int ox0 = cx * WG_CH;
+    __syncthreads();
+    for (int idx = tid; idx < CO_B * WG_CH; idx += 256) {
+      const int px = idx % WG_CH, co = idx / WG_CH;
+      float v = 0.f;
+      if (co0 + co < a.CO && ox0 + px < a.WO) v = __ldg(a.g + (((size_t)b * a.CO + co0 + co) * a.HO + oy) * a.WO + ox0 + px);
+      s_g[co * GP + px] = v;
+    }
+    for (int idx = tid; idx < WG_CIB * K * XC; idx += 256) {
+      const int xc = idx % XC, u = (idx / XC) % K, cc = idx / (XC * K);
+      const int iy = oy * S - P + u, ix = ox0 * S - P + xc;
+      float v = 0.f;
+      if (ci0 + cc < a.CI && iy >= 0 && iy < a.H && ix >= 0 && ix < a.W)
+        v = __ldg(a.x + (((size_t)b * a.CI + ci0 + cc) * a.H + iy) * a.W + ix);
+      s_x[(cc * K + u) * XCP + xc] = v;
+    }
+    __syncthreads();
+    const float* gx = s_g + (4 * tm) * GP + sub * PXT;
+    const float* xx = s_x + ci_l * K * XCP + sub * PXT * S;
+    float win[K][K];
+#pragma unroll
+    for (int u = 0; u < K; ++u)
+#pragma unroll
+      for (int v = 0; v < K - S; ++v) win[u][v + S] = xx[u * XCP + v];      // pre-shifted: first step shifts left by S
+#pragma unroll
+    for (int p = 0; p < PXT; ++p) {
+#pragma unroll
+      for (int u = 0; u < K; ++u) {
+#pragma unroll
+        for (int v = 0; v < K - S; ++v) win[u][v] = win[u][v + S];
+#pragma unroll
+        for (int v = (K - S > 0 ? K - S : 0); v < K; ++v) win[u][v] = xx[u * XCP + p * S + v];
+      }
+      float gv[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) gv[j] = gx[j * GP + p];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int u = 0; u < K; ++u)
+#pragma unroll
+          for (int v = 0; v < K; ++v) acc[j][u * K + v] = fmaf(gv[j], win[u][v], acc[j][u * K + v]);
+    }
+  }
+
+  // ---- sum the NSUB pixel sub-ranges, write the CTA's partial block
+  __syncthreads();
+  float* s_red = s_all;    // one sub-range at a time: TMG*8 * 4*K*K floats
+  for (int s = NSUB - 1; s >= 1; --s) {
+    if (sub == s) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int t = 0; t < K * K; ++t) s_red[(j * K * K + t) * (TMG * WG_CIB) + tm * WG_CIB + ci_l] = acc[j][t];
+    }
+    __syncthreads();
+    if (sub == 0) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int t = 0; t < K * K; ++t) acc[j][t] += s_red[(j * K * K + t) * (TMG * WG_CIB) + tm * WG_CIB + ci_l];
+    }
+    __syncthreads();
+  }
+  if (sub == 0 && ci0 + ci_l < a.CI) {
+    float* out = a.part + (size_t)blockIdx.x * a.CO * a.CI * K * K;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int co = co0 + 4 * tm + j;
+      if (co < a.CO) {
+#pragma unroll
+        for (int t = 0; t < K * K; ++t) out[((size_t)co * a.CI + ci0 + ci_l) * K * K + t] = acc[j][t];
+      }
+    }
+  }
+}
+
+__global__ void wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ gw, int n, int nsplit) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s = 0.0;
+  for (int k = 0; k < nsplit; ++k) s += (double)part[(size_t)k * n + i];
+  gw[i] = (float)s;
+}
+
+static inline int wgrad_nsplit(long long chunks, int ciblocks, int coblocks) {
+  long long want = (148 * 4 + (long long)ciblocks * coblocks - 1) / ((long long)ciblocks * coblocks);
+  if (want > chunks) want = chunks;
+  if (want > 512) want = 512;
+  return (int)(want < 1 ? 1 : want);
+}
+
+template <int K, int S, int P>
+static int launch_wgrad(const float* g, const float* x, float* gw, void* ws, size_t ws_bytes, int B, int CI, int CO, int H,
+                        int W, int HO, int WO, cudaStream_t st) {
+  WgradArgs a;
+  a.g = g; a.x = x; a.part = (float*)ws; a.B = B; a.CI = CI; a.CO = CO; a.H = H; a.W = W; a.HO = HO; a.WO = WO;
+  a.chunks_x = ceil_div(WO, WG_CH);
+  a.chunks = (long long)B * HO * a.chunks_x;
+  const bool small_co = CO <= 32;
+  const int co_b = small_co ? 32 : 64;
+  const int ciblocks = ceil_div(CI, WG_CIB), coblocks = ceil_div(CO, co_b);
+  a.nsplit = wgrad_nsplit(a.chunks, ciblocks, coblocks);
+  const size_t n = (size_t)CO * CI * K * K;
+  if (ws_bytes < n * a.nsplit * sizeof(float)) return NCONV_ERR_WORKSPACE;
+  char label[64];
+  snprintf(label, sizeof(label), "conv_wgrad k%d s%d %d->%d @%dx%d", K, S, CI, CO, H, W);
+  {
+    LaunchScope ls(st, label, 2.0 * CI * CO * K * K * (double)B * HO * WO,
+                   4.0 * ((double)B * CI * H * W + (double)B * CO * HO * WO));
+    dim3 grid(a.nsplit, ciblocks, coblocks);
+    if (small_co) conv_wgrad_kernel<K, S, P, 8><<<grid, 256, 0, st>>>(a);
+    else conv_wgrad_kernel<K, S, P, 16><<<grid, 256, 0, st>>>(a);
+  }
+  {
+    LaunchScope ls(st, "wgrad_reduce", (double)n * a.nsplit, 4.0 * n * (a.nsplit + 1));
+    wgrad_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const float*)ws, gw, (int)n, a.nsplit);
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace nconv
+
+// Workspace for nconv_b200_conv_wgrad (split-K partials).
+extern "C" size_t nconv_b200_conv_wgrad_ws_bytes(int CI, int CO, int K) { return (size_t)512 * CO * CI * K * K * sizeof(float); }
+
+// gw [CO][CI][K][K] = sum g[b,co,oy,ox] * x[b,ci,oy*S-P+u,ox*S-P+v];  g: [B,CO,HO,WO], x: [B,CI,H,W].
+// (K,S,P) in {(1,1,0),(1,2,0),(3,1,1),(3,2,1),(4,2,1)}.
+extern "C" int nconv_b200_conv_wgrad(const float* g, const float* x, float* gw, void* ws, size_t ws_bytes, int B, int CI,
+                                     int CO, int H, int W, int K, int S, int P, void* stream) {
+  if (!g || !x || !gw || !ws || B <= 0 || CI <= 0 || CO <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  const int HO = (H + 2 * P - K) / S + 1, WO = (W + 2 * P - K) / S + 1;
+  if (HO <= 0 || WO <= 0) return NCONV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (K == 3 && S == 1 && P == 1) return nconv::launch_wgrad<3, 1, 1>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
+  if (K == 3 && S == 2 && P == 1) return nconv::launch_wgrad<3, 2, 1>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
+  if (K == 1 && S == 1 && P == 0) return nconv::launch_wgrad<1, 1, 0>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
+  if (K == 1 && S == 2 && P == 0) return nconv::launch_wgrad<1, 2, 0>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
+  if (K == 4 && S == 2 && P == 1) return nconv::launch_wgrad<4, 2, 1>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
+  return NCONV_ERR_UNSUPPORTED;
+}
+
+// =====================================================================================================
+// Gather convolutions for the data gradients that are not a stride-1 "same" convolution:
+//   MODE 0 (transposed gather): dgrad of Conv2d(K, stride S, pad P):
+//       out[b,oc,iy,ix] = sum_{rc,u,v} g[b,rc,(iy+P-u)/S,(ix+P-v)/S] * W[rc][oc][u][v]   (when divisible, in range)
+//     one CTA works on ONE output phase (iy%S, ix%S), so the set of contributing taps is uniform and
+//     the gradient reads are unit-stride;
+//   MODE 1 (strided gather): dgrad of ConvTranspose2d(K=4, S=2, P=1), a strided convolution of g:
+//       out[b,oc,iy,ix] = sum_{rc,kh,kw} g[b,rc,iy*S-P+kh,ix*S-P+kw] * Wt[oc][rc][kh][kw]
+// rc = channels of g (the layer's outputs), oc = channels of the result (the layer's inputs).
+// Weights are re-packed once per call to wt[tap][rc][oc] (gather_pack_kernel); a thread owns 4 pixels x
+// 8 oc, reduction channels go through shared memory 8 at a time, g is read through L1.
+// =====================================================================================================
+namespace nconv {
+
+struct GatherArgs {
+  const float* g; const float* wt; float* out;
+  int B, RC, OC, GH, GW, OH, OW, K, S, P;
+};
+
+// conv weight W[co][ci][K][K] (transposed=0) or ConvTranspose weight Wt[ci][co][K][K] (transposed=1)
+// -> wt[tap][rc=co][oc=ci]
+__global__ void gather_pack_kernel(const float* __restrict__ w, float* __restrict__ wt, int CO, int CI, int KK, int transposed) {
+  const int total = KK * CO * CI;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int ci = idx % CI, co = (idx / CI) % CO, tap = idx / (CI * CO);
+    wt[idx] = transposed ? __ldg(w + ((size_t)ci * CO + co) * KK + tap) : __ldg(w + ((size_t)co * CI + ci) * KK + tap);
+  }
+}
+
+__host__ __device__ __forceinline__ int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+
+template <int MODE>
+__global__ void __launch_bounds__(256) conv_gather_kernel(const GatherArgs a) {
+  __shared__ __align__(16) float s_w[16 * 8 * 8];      // [tap][rc 8][oc 8]
+  const int K = a.K, S = a.S, P = a.P, KK = K * K;
+  const int phases = (MODE == 0) ? S * S : 1;
+  const int nob = (a.OC + 7) / 8;
+  const int z = blockIdx.z;
+  const int ph = z % phases, ob = (z / phases) % nob, b = z / (phases * nob);
+  const int py = ph / S, px = ph % S;
+  const int PH = (MODE == 0) ? (a.OH - py + S - 1) / S : a.OH;
+  const int PW = (MODE == 0) ? (a.OW - px + S - 1) / S : a.OW;
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int q4 = 4 * (blockIdx.x * 32 + lane), j = blockIdx.y * 8 + wrp;
+  const bool active = (j < PH) && (q4 < PW);
+
+  float acc[8][4];
+#pragma unroll
+  for (int o = 0; o < 8; ++o)
+#pragma unroll
+    for (int p = 0; p < 4; ++p) acc[o][p] = 0.f;
+
+  for (int rc0 = 0; rc0 < a.RC; rc0 += 8) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < KK * 64; idx += 256) {
+      const int o = idx & 7, r = (idx >> 3) & 7, tap = idx >> 6;
+      float v = 0.f;
+      if (rc0 + r < a.RC && ob * 8 + o < a.OC) v = __ldg(a.wt + ((size_t)tap * a.RC + rc0 + r) * a.OC + ob * 8 + o);
+      s_w[idx] = v;
+    }
+    __syncthreads();
+    if (!active) continue;
+    const int nr = min(8, a.RC - rc0);
+    for (int r = 0; r < nr; ++r) {
+      const float* gp = a.g + ((size_t)b * a.RC + rc0 + r) * a.GH * a.GW;
+      for (int u = 0; u < K; ++u) {
+        int gy;
+        if (MODE == 0) {
+          const int t = py + P - u;
+          if (((t % S) + S) % S != 0) continue;
+          gy = j + floordiv(t, S);
+        } else {
+          gy = j * S - P + u;
+        }
+        if (gy < 0 || gy >= a.GH) continue;
+        const float* grow = gp + (size_t)gy * a.GW;
+        for (int v = 0; v < K; ++v) {
+          int gx0, step;
+          if (MODE == 0) {
+            const int t = px + P - v;
+            if (((t % S) + S) % S != 0) continue;
+            gx0 = q4 + floordiv(t, S); step = 1;
+          } else {
+            gx0 = q4 * S - P + v; step = S;
+          }
+          float gv[4];
+#pragma unroll
+          for (int p = 0; p < 4; ++p) {
+            const int gx = gx0 + p * step;
+            gv[p] = (gx >= 0 && gx < a.GW) ? __ldg(grow + gx) : 0.f;
+          }
+          const float4 w0 = *reinterpret_cast<const float4*>(s_w + ((u * K + v) * 8 + r) * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(s_w + ((u * K + v) * 8 + r) * 8 + 4);
+          const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+          for (int o = 0; o < 8; ++o)
+#pragma unroll
+            for (int p = 0; p < 4; ++p) acc[o][p] = fmaf(wv[o], gv[p], acc[o][p]);
+        }
+      }
+    }
+  }
+  if (!active) return;
+  const int iy = (MODE == 0) ? j * S + py : j;
+#pragma unroll
+  for (int o = 0; o < 8; ++o) {
+    const int oc = ob * 8 + o;
+    if (oc >= a.OC) break;
+    float* orow = a.out + (((size_t)b * a.OC + oc) * a.OH + iy) * a.OW;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      if (q4 + p < PW) orow[(MODE == 0) ? (q4 + p) * S + px : q4 + p] = acc[o][p];
+    }
+  }
+}
+
+// W[co][ci][u][v] -> W'[ci][co][K-1-u][K-1-v]
+__global__ void wflip_kernel(const float* __restrict__ w, float* __restrict__ wf, int CO, int CI, int K) {
+  const int KK = K * K, total = CO * CI * KK;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int tap = idx % KK, co = (idx / KK) % CO, ci = idx / (KK * CO);
+    wf[idx] = __ldg(w + ((size_t)co * CI + ci) * KK + (KK - 1 - tap));
+  }
+}
+
+}  // namespace nconv
+
+extern "C" size_t nconv_b200_conv_dgrad_ws_bytes(int CI, int CO, int K) { return (size_t)CI * CO * K * K * sizeof(float); }
+
+// Data gradient of Conv2d(K, S, P=K/2) for S = 2 (transposed = 0; w = [CO][CI][K][K]; g = [B,CO,HO,WO];
+// gx = [B,CI,H,W]) and of ConvTranspose2d(4,2,1) (transposed = 1; w = [CI][CO][4][4]; g = [B,CO,2H,2W];
+// gx = [B,CI,H,W]).  ws: nconv_b200_conv_dgrad_ws_bytes(CI, CO, K).
+extern "C" int nconv_b200_conv_dgrad_gather(const float* g, const float* w, float* gx, void* ws, int B, int CI, int CO,
+                                            int H, int W, int K, int S, int P, int transposed, void* stream) {
+  if (!g || !w || !gx || !ws || B <= 0 || CI <= 0 || CO <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  if (K < 1 || K > 4 || S < 1 || S > 2) return NCONV_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int KK = K * K;
+  {
+    LaunchScope ls(st, "gather_pack", 0.0, 8.0 * CI * CO * KK);
+    gather_pack_kernel<<<(CI * CO * KK + 255) / 256, 256, 0, st>>>(w, (float*)ws, CO, CI, KK, transposed);
+  }
+  GatherArgs a;
+  a.g = g; a.wt = (const float*)ws; a.out = gx; a.B = B; a.RC = CO; a.OC = CI; a.OH = H; a.OW = W; a.K = K; a.S = S; a.P = P;
+  if (transposed) { a.GH = 2 * H; a.GW = 2 * W; }
+  else { a.GH = (H + 2 * P - K) / S + 1; a.GW = (W + 2 * P - K) / S + 1; }
+  const int phases = transposed ? 1 : S * S;
+  const int PH = transposed ? H : (H + S - 1) / S, PW = transposed ? W : (W + S - 1) / S;
+  dim3 grid(nconv::ceil_div(nconv::ceil_div(PW, 4), 32), nconv::ceil_div(PH, 8), B * ((CI + 7) / 8) * phases);
+  char label[64];
+  snprintf(label, sizeof(label), "conv_dgrad_gather%s k%d s%d %d<-%d @%dx%d", transposed ? "T" : "", K, S, CI, CO, H, W);
+  {
+    const double taps = transposed ? (double)KK : (double)KK / (S * S);
+    LaunchScope ls(st, label, 2.0 * CI * CO * taps * (double)B * H * W,
+                   4.0 * ((double)B * CO * a.GH * a.GW + (double)B * CI * H * W));
+    if (transposed) conv_gather_kernel<1><<<grid, 256, 0, st>>>(a);
+    else conv_gather_kernel<0><<<grid, 256, 0, st>>>(a);
+  }
+  return (int)cudaGetLastError();
+}
+
+// wf [CI][CO][K][K] = spatially flipped, channel-transposed w [CO][CI][K][K]: conv2d_fwd(g, wf) is the data
+// gradient of a stride-1 "same" convolution.
+extern "C" int nconv_b200_wflip(const float* w, float* wf, int CO, int CI, int K, void* stream) {
+  if (!w || !wf || CO <= 0 || CI <= 0 || K <= 0) return NCONV_ERR_BAD_ARG;
+  LaunchScope ls((cudaStream_t)stream, "wflip", 0.0, 8.0 * CO * CI * K * K);
+  wflip_kernel<<<(CO * CI * K * K + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, wf, CO, CI, K);
+  return (int)cudaGetLastError();
+}

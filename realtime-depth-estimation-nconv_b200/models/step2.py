@@ -15,9 +15,11 @@ EnforcePos/GenKernel) are never instantiated by the reference and are not reprod
 Generalisations (identical to the reference for its batch-1-per-stream use):
 outputs are split `[:B]/[B:]` instead of `[0:1]/[1:2]`.
 
-Scope note: the CUDA path implements inference semantics (BatchNorm with running statistics).
-Training-mode BatchNorm + conv backward for this stack is the next row; calling
-forward with BN modules in training mode raises instead of silently falling back.
+Training (train_step2.py:60-66 keeps the model in train()): BatchNorm2d layers in training mode
+normalise with batch statistics and update their running buffers; whenever autograd is recording and
+a parameter or input needs a gradient, every conv / transposed conv / BatchNorm / ReLU runs through
+the analytic forward+backward kernels of csrc/conv_train.cu (`ops.conv_train`, `convT_train`,
+`bn_train`).  Concatenations on that path are materialised (`torch.cat`, as in the reference).
 """
 from __future__ import annotations
 
@@ -33,11 +35,18 @@ from models.step1 import SETP1_NCONV
 _K = torch.ops.nconv_b200
 
 
+def _recording(x, *params) -> bool:
+    """Autograd is recording and something on this layer's path needs a gradient."""
+    return torch.is_grad_enabled() and (x.requires_grad or any(p is not None and p.requires_grad for p in params))
+
+
+def _cat(x, x2):
+    return x if x2 is None else torch.cat((x, x2), dim=1)
+
+
 def _fold(bn: nn.BatchNorm2d, conv_bias):
     if bn.training:
-        raise NotImplementedError(
-            "SETP2 CUDA path: BatchNorm in training mode (batch statistics) is not implemented yet; "
-            "call .eval() (there is no PyTorch fallback on purpose)")
+        raise RuntimeError("internal: eval-mode BatchNorm fold requested for a BatchNorm in training mode")
     return _K.bn_fold(bn.weight, bn.bias, bn.running_mean, bn.running_var, conv_bias, float(bn.eps))
 
 
@@ -271,9 +280,16 @@ class RGBEncoder(nn.Module):
 
     def forward(self, x):
         conv, bn = self.encoder[0], self.encoder[1]
+        w1 = self.downsample[0].weight
+        if bn.training:
+            z = _ops.conv_train(x, conv.weight, conv.bias, None, self.stride, False)
+            r = _ops.conv_train(x, w1, None, None, self.stride, False)
+            return _ops.bn_train(z, bn, residual=r, relu=True)
+        if _recording(x, conv.weight, w1):
+            raise NotImplementedError("RGBEncoder: gradients through an eval-mode BatchNorm are not implemented")
         scale, shift = _fold(bn, conv.bias)
         t = _K.conv2d(x, None, conv.weight, scale, shift, None, self.stride, True)
-        return _K.conv2d(x, None, self.downsample[0].weight, None, None, t, self.stride, False)
+        return _K.conv2d(x, None, w1, None, None, t, self.stride, False)
 
 
 class Basic2d(nn.Module):
@@ -295,11 +311,20 @@ class Basic2d(nn.Module):
 
     def forward(self, x, x2=None):
         conv = self.conv.conv
-        if hasattr(self.conv, 'bn'):
+        has_bn = hasattr(self.conv, 'bn')
+        stride = int(conv.stride[0])
+        if has_bn and self.conv.bn.training:
+            z = _ops.conv_train(_cat(x, x2), conv.weight, conv.bias, None, stride, False)
+            return _ops.bn_train(z, self.conv.bn, relu=self._relu)
+        if _recording(x, conv.weight, conv.bias) or (x2 is not None and x2.requires_grad and torch.is_grad_enabled()):
+            if has_bn:
+                raise NotImplementedError("Basic2d: gradients through an eval-mode BatchNorm are not implemented")
+            return _ops.conv_train(_cat(x, x2), conv.weight, conv.bias, None, stride, self._relu)
+        if has_bn:
             scale, shift = _fold(self.conv.bn, conv.bias)
         else:
             scale, shift = None, conv.bias
-        return _K.conv2d(x, x2, conv.weight, scale, shift, None, int(conv.stride[0]), self._relu)
+        return _K.conv2d(x, x2, conv.weight, scale, shift, None, stride, self._relu)
 
 
 class Basic2dTrans(nn.Module):
@@ -320,7 +345,14 @@ class Basic2dTrans(nn.Module):
             raise NotImplementedError("Basic2dTrans: only ReLU")
 
     def forward(self, x, x2=None):
-        if isinstance(self.bn, nn.BatchNorm2d):
+        is_bn = isinstance(self.bn, nn.BatchNorm2d)
+        if is_bn and self.bn.training:
+            if self.conv.bias is not None:
+                raise NotImplementedError("Basic2dTrans: bias together with a norm layer is not a layer of this stack")
+            return _ops.bn_train(_ops.convT_train(_cat(x, x2), self.conv.weight), self.bn, relu=True)
+        if _recording(x, self.conv.weight) or (x2 is not None and x2.requires_grad and torch.is_grad_enabled()):
+            raise NotImplementedError("Basic2dTrans: gradients need the BatchNorm in training mode")
+        if is_bn:
             scale, shift = _fold(self.bn, self.conv.bias)
         else:
             scale, shift = None, self.conv.bias
@@ -352,7 +384,10 @@ class ConvBlock(nn.Module):
         self.relu = nn.ReLU()
 
     def forward(self, x, x2=None):
-        return _K.conv2d(x, x2, self.conv.weight, None, self.conv.bias, None, int(self.conv.stride[0]), True)
+        stride = int(self.conv.stride[0])
+        if _recording(x, self.conv.weight, self.conv.bias) or (x2 is not None and x2.requires_grad and torch.is_grad_enabled()):
+            return _ops.conv_train(_cat(x, x2), self.conv.weight, self.conv.bias, None, stride, True)
+        return _K.conv2d(x, x2, self.conv.weight, None, self.conv.bias, None, stride, True)
 
 
 class NewFusionBlock(nn.Module):
@@ -390,7 +425,7 @@ class FusionResolutionBlock(nn.Module):
         fout = self.upcat(rgb, fusion_festure, depth_last_step)
         depth = _resize(depth, self.downsample_factor)
         fout = self.fuse(fout, depth)
-        dout = _K.conv2d(fout, None, self.conv.weight, None, None, depth, 1, False)   # depth + res
+        dout = _head(fout, self.conv.weight, depth)                                   # depth + res
         return fout, dout
 
 
@@ -406,8 +441,15 @@ class FusionResolution0(nn.Module):
     def forward(self, rgb, depth):
         depth = _resize(depth, self.downsample_factor)
         fout = self.fuse(rgb, depth)
-        dout = _K.conv2d(fout, None, self.conv.weight, None, None, depth, 1, False)
+        dout = _head(fout, self.conv.weight, depth)
         return fout, dout
+
+
+def _head(fout, weight, depth):
+    """depth + conv3x3_{C->1, no bias}(fout)  (step2.py:255-257, 274-276)."""
+    if _recording(fout, weight):
+        return _ops.conv_train(fout, weight, None, depth, 1, False)
+    return _K.conv2d(fout, None, weight, None, None, depth, 1, False)
 
 
 def _resize(depth, factor):

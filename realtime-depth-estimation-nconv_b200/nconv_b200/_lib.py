@@ -57,6 +57,15 @@ SIGNATURES = {
     "nconv_b200_profile_count": (c_int, []),
     "nconv_b200_profile_get": (c_int, [c_int, ctypes.c_char_p, c_int, POINTER(c_float), POINTER(ctypes.c_double),
                                        POINTER(ctypes.c_double)]),
+    "nconv_b200_train_ws_bytes": (c_size_t, [c_int]),
+    "nconv_b200_bn_train_fwd": (c_int, [c_void_p] * 12 + [c_int] * 4 + [c_float, c_float, c_int, c_void_p]),
+    "nconv_b200_bn_train_bwd": (c_int, [c_void_p] * 11 + [c_int] * 5 + [c_void_p]),
+    "nconv_b200_relu_bias_bwd": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
+    "nconv_b200_conv_wgrad_ws_bytes": (c_size_t, [c_int] * 3),
+    "nconv_b200_conv_wgrad": (c_int, [c_void_p] * 4 + [c_size_t] + [c_int] * 8 + [c_void_p]),
+    "nconv_b200_conv_dgrad_ws_bytes": (c_size_t, [c_int] * 3),
+    "nconv_b200_conv_dgrad_gather": (c_int, [c_void_p] * 4 + [c_int] * 9 + [c_void_p]),
+    "nconv_b200_wflip": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
     "nconv_b200_nconv2d_fwd": (c_int, [c_void_p] * 6 + [c_int] * 9 + [c_float, c_void_p]),
     "nconv_b200_nconv2d_fwd_fused": (c_int, [POINTER(FwdDesc), c_void_p]),
     "nconv_b200_nconv2d_bwd_workspace_bytes": (c_size_t, [c_int] * 9),

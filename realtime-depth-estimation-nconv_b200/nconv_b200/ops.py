@@ -498,3 +498,191 @@ def head_p8(f: "P8", weight, residual, out8=None):
 def launch_count() -> int:
     """Kernels enqueued by libnconv_b200.so in this process so far."""
     return _lib.launch_count()
+
+
+# --------------------------------------------------------------------------------------
+# training mode of the RGB-guided stack: conv / convT / BatchNorm forward+backward
+# (csrc/conv_train.cu; the reference differentiates step2.py with autograd under model.train())
+# --------------------------------------------------------------------------------------
+_SCRATCH = {}
+
+
+def _scratch(dev, nbytes: int):
+    """Grow-only per-device scratch (fp64 channel sums, split-K partials, re-packed weights).  Kernels
+    using it are ordered on the current stream, so one buffer per purpose and device is enough."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    t = _SCRATCH.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(max(int(nbytes), 1 << 20), device=dev, dtype=torch.uint8)
+        _SCRATCH[key] = t
+    return t
+
+
+def _conv_fwd_raw(x, weight, shift, residual, stride: int, relu: bool):
+    B, CI, H, W = x.shape
+    CO, _, K, _ = weight.shape
+    HO, WO = _conv_out(H, K, stride), _conv_out(W, K, stride)
+    y = torch.empty((B, CO, HO, WO), device=x.device, dtype=torch.float32)
+    d = ConvDesc(_p(x), None, _p(weight), None, _p(shift), _p(residual), _p(y), B, CI, 0, CO, H, W, K, stride, int(relu))
+    with torch.cuda.device(x.device):
+        check(_C.nconv_b200_conv2d_fwd(byref(d), _stream(x)), "conv2d_fwd")
+    return y
+
+
+def _relu_bias_bwd(gy, y, relu: bool, want_g: bool, want_bias: bool):
+    B, C, H, W = gy.shape
+    g = torch.empty_like(gy) if want_g else None
+    gb = torch.empty(C, device=gy.device, dtype=torch.float32) if want_bias else None
+    ws = _scratch(gy.device, int(_C.nconv_b200_train_ws_bytes(C)))
+    with torch.cuda.device(gy.device):
+        check(_C.nconv_b200_relu_bias_bwd(_p(gy), _p(y) if relu else None, _p(g), _p(gb), _p(ws), B, C, H, W, int(relu),
+                                          _stream(gy)), "relu_bias_bwd")
+    return g, gb
+
+
+def _conv_wgrad(g, x, K: int, S: int, P: int):
+    """gw[CO][CI][K][K] for g [B,CO,HO,WO], x [B,CI,H,W]."""
+    B, CI, H, W = x.shape
+    CO = g.shape[1]
+    gw = torch.empty((CO, CI, K, K), device=x.device, dtype=torch.float32)
+    n = int(_C.nconv_b200_conv_wgrad_ws_bytes(CI, CO, K))
+    ws = _scratch(x.device, n)
+    with torch.cuda.device(x.device):
+        check(_C.nconv_b200_conv_wgrad(_p(g), _p(x), _p(gw), _p(ws), n, B, CI, CO, H, W, K, S, P, _stream(x)), "conv_wgrad")
+    return gw
+
+
+class _ConvTrain(torch.autograd.Function):
+    """y = [ReLU](conv_{K,stride,pad=K//2}(x, w) + bias) (+ residual) with the analytic backward."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, stride, relu):
+        x = _prep(x, "x"); weight = _prep(weight, "weight"); bias = _prep_opt(bias, "bias")
+        residual = _prep_opt(residual, "residual")
+        if relu and residual is not None:
+            raise ValueError("conv_train: ReLU with a residual is not a layer of this stack")
+        y = _conv_fwd_raw(x, weight, bias, residual, stride, relu)
+        ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.cfg = (stride, relu, bias is not None, residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight, y = ctx.saved_tensors
+        stride, relu, has_bias, has_res = ctx.cfg
+        need_x, need_w, need_b, need_r = ctx.needs_input_grad[:4]
+        gy = _prep(gy, "gy")
+        CO, CI, K, _ = weight.shape
+        g, gb = gy, None
+        if relu or (has_bias and need_b):
+            g2, gb = _relu_bias_bwd(gy, y, relu, want_g=relu, want_bias=has_bias and need_b)
+            if relu:
+                g = g2
+        gw = _conv_wgrad(g, x, K, stride, K // 2) if need_w else None
+        gx = None
+        if need_x:
+            dev = x.device
+            if stride == 1:
+                wf = torch.empty((CI, CO, K, K), device=dev, dtype=torch.float32)
+                with torch.cuda.device(dev):
+                    check(_C.nconv_b200_wflip(_p(weight), _p(wf), CO, CI, K, _stream(x)), "wflip")
+                gx = _conv_fwd_raw(g, wf, None, None, 1, False)
+            else:
+                gx = torch.empty_like(x)
+                ws = _scratch(dev, int(_C.nconv_b200_conv_dgrad_ws_bytes(CI, CO, K)))
+                with torch.cuda.device(dev):
+                    check(_C.nconv_b200_conv_dgrad_gather(_p(g), _p(weight), _p(gx), _p(ws), x.shape[0], CI, CO,
+                                                          x.shape[2], x.shape[3], K, stride, K // 2, 0, _stream(x)),
+                          "conv_dgrad_gather")
+        return gx, gw, gb, (gy if (has_res and need_r) else None), None, None
+
+
+def conv_train(x, weight, bias=None, residual=None, stride=1, relu=False):
+    return _ConvTrain.apply(x, weight, bias, residual, stride, relu)
+
+
+class _ConvTTrain(torch.autograd.Function):
+    """ConvTranspose2d(k=4, s=2, p=1, bias=False) (Basic2dTrans, step2.py:205) with the analytic backward."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        x = _prep(x, "x"); weight = _prep(weight, "weight")
+        B, CI, H, W = x.shape
+        CO = weight.shape[1]
+        y = torch.empty((B, CO, 2 * H, 2 * W), device=x.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_convT4x4s2_fwd(_p(x), None, _p(weight), None, None, _p(y), B, CI, 0, CO, H, W, 0,
+                                               _stream(x)), "convT4x4s2_fwd")
+        ctx.save_for_backward(x, weight)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        gy = _prep(gy, "gy")
+        B, CI, H, W = x.shape
+        CO = weight.shape[1]
+        gw = gx = None
+        if ctx.needs_input_grad[1]:
+            # roles swapped: "input" = gy [B,CO,2H,2W], "output gradient" = x [B,CI,H,W]  ->  [CI][CO][4][4]
+            gw = _conv_wgrad(x, gy, 4, 2, 1)
+        if ctx.needs_input_grad[0]:
+            gx = torch.empty_like(x)
+            ws = _scratch(x.device, int(_C.nconv_b200_conv_dgrad_ws_bytes(CI, CO, 4)))
+            with torch.cuda.device(x.device):
+                check(_C.nconv_b200_conv_dgrad_gather(_p(gy), _p(weight), _p(gx), _p(ws), B, CI, CO, H, W, 4, 2, 1, 1,
+                                                      _stream(x)), "conv_dgrad_gatherT")
+        return gx, gw
+
+
+def convT_train(x, weight):
+    return _ConvTTrain.apply(x, weight)
+
+
+class _BnTrain(torch.autograd.Function):
+    """nn.BatchNorm2d in training mode (+ReLU, + residual added after the activation)."""
+
+    @staticmethod
+    def forward(ctx, z, gamma, beta, running_mean, running_var, residual, eps, momentum, relu):
+        z = _prep(z, "z"); residual = _prep_opt(residual, "residual")
+        B, C, H, W = z.shape
+        dev = z.device
+        y = torch.empty_like(z)
+        stats = torch.empty((4, C), device=dev, dtype=torch.float32)     # scale, shift, mean, rstd
+        ws = _scratch(dev, int(_C.nconv_b200_train_ws_bytes(C)))
+        with torch.cuda.device(dev):
+            check(_C.nconv_b200_bn_train_fwd(_p(z), _p(gamma), _p(beta), _p(running_mean), _p(running_var), _p(residual),
+                                             _p(y), _p(stats[0]), _p(stats[1]), _p(stats[2]), _p(stats[3]), _p(ws),
+                                             B, C, H, W, eps, momentum, int(relu), _stream(z)), "bn_train_fwd")
+        ctx.save_for_backward(z, gamma, stats)
+        ctx.cfg = (relu, residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        z, gamma, stats = ctx.saved_tensors
+        relu, has_res = ctx.cfg
+        gy = _prep(gy, "gy")
+        B, C, H, W = z.shape
+        gz = torch.empty_like(z)
+        gg = torch.empty(C, device=z.device, dtype=torch.float32)
+        gb = torch.empty(C, device=z.device, dtype=torch.float32)
+        ws = _scratch(z.device, int(_C.nconv_b200_train_ws_bytes(C)))
+        with torch.cuda.device(z.device):
+            check(_C.nconv_b200_bn_train_bwd(_p(gy), _p(z), _p(stats[0]), _p(stats[1]), _p(stats[2]), _p(stats[3]),
+                                             _p(gamma), _p(gz), _p(gg), _p(gb), _p(ws), B, C, H, W, int(relu),
+                                             _stream(z)), "bn_train_bwd")
+        return (gz, gg if ctx.needs_input_grad[1] else None, gb if ctx.needs_input_grad[2] else None, None, None,
+                gy if (has_res and ctx.needs_input_grad[5]) else None, None, None, None)
+
+
+def bn_train(z, bn: "torch.nn.BatchNorm2d", residual=None, relu=True):
+    """BatchNorm2d with batch statistics; updates bn.running_* and num_batches_tracked like nn.BatchNorm2d."""
+    if bn.momentum is None:
+        raise NotImplementedError("bn_train: cumulative moving average (momentum=None) is not used by this stack")
+    rm = bn.running_mean if bn.track_running_stats else None
+    rv = bn.running_var if bn.track_running_stats else None
+    y = _BnTrain.apply(z, bn.weight, bn.bias, rm, rv, residual, float(bn.eps), float(bn.momentum), relu)
+    if bn.track_running_stats and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+    return y

@@ -346,12 +346,101 @@ def test_setp2_export_vs_reference_golden(golden):
     assert torch.all(o0[:, :, :45] == 0) and torch.all(o0[:, :, -45:] == 0) and torch.all(o0[..., :20] == 0)
 
 
-def test_setp2_train_mode_bn_raises():
-    """No silent fallback: batch-statistics BatchNorm is not implemented on the CUDA path yet."""
-    from models.step2 import RGBEncoder
-    enc = RGBEncoder(3, 32, 1).to(dev()).train()
-    with pytest.raises(NotImplementedError):
-        enc(torch.rand(1, 3, 8, 8, device=dev()))
+def _rel(a, ref):
+    return float((a.detach().double().cpu() - ref.double()).abs().max() / ref.double().abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("cfg", [
+    # CI, CO, K, stride, relu, bias, B, H, W
+    (16, 32, 3, 1, True, True, 2, 20, 36), (64, 64, 3, 1, True, True, 1, 15, 20), (128, 64, 3, 1, False, False, 1, 12, 70),
+    (32, 64, 3, 2, False, True, 2, 16, 24), (32, 64, 1, 2, False, False, 2, 16, 24), (3, 32, 3, 1, False, True, 2, 9, 13),
+    (3, 32, 1, 1, False, False, 2, 9, 13), (32, 1, 3, 1, False, False, 2, 24, 130), (1, 64, 3, 1, True, True, 1, 15, 20),
+])
+def test_conv_train_forward_backward_vs_fp64(cfg):
+    """ops.conv_train (forward kernel + wgrad + dgrad + ReLU/bias backward, csrc/conv_train.cu) against
+    torch autograd in fp64 — the layers of step2.py:130-158, 183-191, 290-297."""
+    from nconv_b200 import ops
+    CI, CO, K, stride, relu, bias, B, H, W = cfg
+    g = torch.Generator().manual_seed(CI * 100 + CO + K)
+    x = (torch.rand(B, CI, H, W, generator=g) * 4 - 1)
+    w = (torch.rand(CO, CI, K, K, generator=g) - 0.5) * 0.2
+    bb = (torch.rand(CO, generator=g) - 0.5) if bias else None
+    xr, wr = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    br = bb.double().requires_grad_(True) if bias else None
+    yr = F.conv2d(xr, wr, br, stride=stride, padding=K // 2)
+    if relu:
+        yr = F.relu(yr)
+    G = torch.randn(yr.shape, generator=g)
+    (yr * G.double()).sum().backward()
+    xd, wd = x.to(dev()).requires_grad_(True), w.to(dev()).requires_grad_(True)
+    bd = bb.to(dev()).requires_grad_(True) if bias else None
+    y = ops.conv_train(xd, wd, bd, None, stride, relu)
+    (y * G.to(dev())).sum().backward()
+    assert _rel(y, yr) <= 1e-5
+    assert _rel(wd.grad, wr.grad) <= 2e-5
+    assert _rel(xd.grad, xr.grad) <= 2e-5
+    if bias:
+        assert _rel(bd.grad, br.grad) <= 2e-5
+
+
+@pytest.mark.parametrize("cfg", [(65, 64, 2, 15, 20), (33, 32, 1, 9, 13), (9, 16, 2, 5, 6)])
+def test_convT_train_forward_backward_vs_fp64(cfg):
+    from nconv_b200 import ops
+    CI, CO, B, H, W = cfg
+    g = torch.Generator().manual_seed(CI + CO)
+    x = torch.rand(B, CI, H, W, generator=g) * 2 - 0.5
+    w = (torch.rand(CI, CO, 4, 4, generator=g) - 0.5) * 0.2
+    xr, wr = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    yr = F.conv_transpose2d(xr, wr, None, stride=2, padding=1)
+    G = torch.randn(yr.shape, generator=g)
+    (yr * G.double()).sum().backward()
+    xd, wd = x.to(dev()).requires_grad_(True), w.to(dev()).requires_grad_(True)
+    y = ops.convT_train(xd, wd)
+    (y * G.to(dev())).sum().backward()
+    assert _rel(y, yr) <= 1e-5
+    assert _rel(wd.grad, wr.grad) <= 2e-5
+    assert _rel(xd.grad, xr.grad) <= 2e-5
+
+
+@pytest.mark.parametrize("cfg", [(2, 32, 20, 36, True, True), (3, 64, 15, 20, True, False), (2, 8, 5, 7, False, False)])
+def test_bn_train_forward_backward_vs_fp64(cfg):
+    """ops.bn_train against nn.BatchNorm2d (training mode) in fp64, with un-normalised inputs
+    (mean >> std, like the raw-RGB activations), ReLU, the post-activation residual of RGBEncoder,
+    and the running-statistics update."""
+    from nconv_b200 import ops
+    B, C, H, W, relu, res = cfg
+    g = torch.Generator().manual_seed(B * C + H)
+    z = torch.randn(B, C, H, W, generator=g) * 3 + 100
+    r = torch.randn(B, C, H, W, generator=g) if res else None
+    bn = torch.nn.BatchNorm2d(C)
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(C, generator=g) + 0.5); bn.bias.copy_(torch.rand(C, generator=g) - 0.5)
+        bn.running_mean.copy_(torch.randn(C, generator=g)); bn.running_var.copy_(torch.rand(C, generator=g) + 0.5)
+    import copy
+    bnr = copy.deepcopy(bn).double().train()
+    zr = z.double().requires_grad_(True)
+    rr = r.double().requires_grad_(True) if res else None
+    yr = bnr(zr)
+    if relu:
+        yr = F.relu(yr)
+    if res:
+        yr = yr + rr
+    G = torch.randn(yr.shape, generator=g)
+    (yr * G.double()).sum().backward()
+    bnd = copy.deepcopy(bn).to(dev()).train()
+    zd = z.to(dev()).requires_grad_(True)
+    rd = r.to(dev()).requires_grad_(True) if res else None
+    y = ops.bn_train(zd, bnd, residual=rd, relu=relu)
+    (y * G.to(dev())).sum().backward()
+    assert _rel(y, yr) <= 2e-5
+    assert _rel(zd.grad, zr.grad) <= 1e-4
+    assert _rel(bnd.weight.grad, bnr.weight.grad) <= 2e-5
+    assert _rel(bnd.bias.grad, bnr.bias.grad) <= 2e-5
+    assert _rel(bnd.running_mean, bnr.running_mean) <= 1e-6
+    assert _rel(bnd.running_var, bnr.running_var) <= 1e-5
+    assert int(bnd.num_batches_tracked) == 1
+    if res:
+        assert torch.equal(rd.grad.cpu(), G)
 
 
 # ---------------------------------------------------------------------------------------------
