@@ -332,11 +332,14 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
   const int ci_l = tid % WG_CIB, tm = (tid / WG_CIB) % TMG, sub = tid / (WG_CIB * TMG);
   const int ci0 = blockIdx.y * WG_CIB, co0 = blockIdx.z * CO_B;
 
-  float acc[4][K * K];
+  // Two-level accumulation: `acc` sums one chunk (PXT products), `tot` sums the chunks.  The rounding
+  // error then grows with sqrt(PXT) + sqrt(chunks per CTA) instead of sqrt(all pixels of the CTA): these
+  // sums run over up to 10^5 products of un-normalised activations with heavy cancellation.
+  float acc[4][K * K], tot[4][K * K];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int t = 0; t < K * K; ++t) acc[j][t] = 0.f;
+    for (int t = 0; t < K * K; ++t) { acc[j][t] = 0.f; tot[j][t] = 0.f; }
 
   for (long long ch = blockIdx.x; ch < a.chunks; ch += a.nsplit) {
     const int cx = (int)(ch % a.chunks_x);
@@ -385,7 +388,15 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
 #pragma unroll
           for (int v = 0; v < K; ++v) acc[j][u * K + v] = fmaf(gv[j], win[u][v], acc[j][u * K + v]);
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int t = 0; t < K * K; ++t) { tot[j][t] += acc[j][t]; acc[j][t] = 0.f; }
   }
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int t = 0; t < K * K; ++t) acc[j][t] = tot[j][t];
 
   // ---- sum the NSUB pixel sub-ranges, write the CTA's partial block
   __syncthreads();
