@@ -34,6 +34,7 @@
 #include "p8.cuh"
 #include "tc_ptx.cuh"
 #include <cstdio>
+#include <cstdlib>
 
 namespace nconv {
 
@@ -98,7 +99,7 @@ struct TcArgs {
   size_t slab_elems;            // elements per (n, chunk, part) slab of a source
   size_t grp_elems;             // elements per plane group inside a slab (P8Q phase plane)
   int src_pitch, src_rows;      // source plane geometry (pixels per row, rows)
-  const __nv_bfloat16* wpack;   // [kstage][wtap][part][j][CO][8]
+  const __nv_bfloat16* wpack;   // [kstage][wtap][j][part][CO][8]
   const float* scale;           // [CO] or null
   const float* shift;           // [CO] or null
   __nv_bfloat16* out;           // P8 [B][CO/8][2][OH+2][OW+2][8]
@@ -110,8 +111,14 @@ struct TcArgs {
   TcTap taps[TC_MAX_TAPS];
 };
 
-template <int N, int MODE>
+// STACK (Co = 32, S1): the packed weights of a tap are [j][hi|lo][N][8], so ONE B descriptor with 2N rows
+// is [W_hi ; W_lo]: A_hi x [W_hi|W_lo] gives hi*hi and hi*lo in one N=2N MMA (two column halves of the
+// accumulator, summed by the epilogue) and A_lo x W_hi is the second MMA.  An M128xK16 MMA reads its 4 KB A
+// tile from shared memory in ~32 cycles whatever N is, so at N=32 the three MMAs of a slice were bound by
+// three A reads (96 cycles); stacked they are two (64 cycles).
+template <int N, int MODE, bool STACK>
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcArgs a) {
+  constexpr int NACC = STACK ? 2 * N : N;                                   // accumulator columns per (group, M-tile)
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_full[TC_STAGES], s_empty[TC_STAGES], s_tfull[2], s_tempty[2];
   __shared__ uint32_t s_tmem_base;
@@ -120,7 +127,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t a_plane_bytes = (uint32_t)a.rows_alloc * a.P * 16;       // one (group, part, j) plane
   const uint32_t a_stage_bytes = (uint32_t)a.G * 4 * a_plane_bytes;
-  constexpr uint32_t B_TAP_BYTES = 2 * 2 * N * 16;                        // [part][j][N][16 B]
+  constexpr uint32_t B_TAP_BYTES = 2 * 2 * N * 16;                        // [j][part][N][16 B]
   const uint32_t b_stage_bytes = (uint32_t)a.ntaps_w * B_TAP_BYTES;
   const uint32_t stage_bytes = a_stage_bytes + b_stage_bytes;
   const uint32_t smem_base = smem_u32(smem);
@@ -181,6 +188,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
+    constexpr uint32_t IDESC2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((2 * N) >> 3) << 17) | ((128u >> 4) << 24);
     uint32_t stage = 0, phase = 0, it = 0;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
@@ -196,23 +204,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           const uint32_t sa16 = (smem_base + stage * stage_bytes) >> 4;
           const uint32_t sb16 = sa16 + (a_stage_bytes >> 4);
           const uint32_t a_lbo = (a_plane_bytes >> 4) << 16, alo_off = (2 * a_plane_bytes) >> 4;
-          constexpr uint32_t B_LBO = (uint32_t)(N * 16 >> 4) << 16, BLO_OFF = (2 * N * 16) >> 4;
+          constexpr uint32_t B_LBO = (uint32_t)(2 * N * 16 >> 4) << 16, BLO_OFF = (N * 16) >> 4;   // [j][hi|lo][N][16 B]
           for (int t = 0; t < a.T; ++t) {
-            const uint32_t dbase = tmem_base + buf * 256 + t * N;
+            const uint32_t dbase = tmem_base + buf * 256 + t * NACC;
             const uint32_t at16 = sa16 + (uint32_t)t * 128;
 #pragma unroll
             for (int i = 0; i < TapTable<MODE>::NTAPS; ++i) {
               if (i >= a.ntaps) break;                                   // S2 without the 1x1 branch
               const uint32_t ao = TapTable<MODE>::a_off16(i, a.P, a_plane_bytes >> 4);
-              const uint32_t d = dbase + TapTable<MODE>::dgrp(i) * a.T * N;
+              const uint32_t d = dbase + TapTable<MODE>::dgrp(i) * a.T * NACC;
               const uint64_t a_hi = ((uint64_t)DESC_HI << 32) | ((at16 + ao) | a_lbo);
               const uint64_t a_lo = ((uint64_t)DESC_HI << 32) | ((at16 + ao + alo_off) | a_lbo);
               const uint32_t bo = sb16 + TapTable<MODE>::w_idx(i) * (B_TAP_BYTES >> 4);
               const uint64_t b_hi = ((uint64_t)DESC_HI << 32) | (bo | B_LBO);
               const uint64_t b_lo = ((uint64_t)DESC_HI << 32) | ((bo + BLO_OFF) | B_LBO);
-              umma_bf16(d, a_hi, b_hi, IDESC, (k > 0 || !TapTable<MODE>::first(i)) ? 1u : 0u);
-              umma_bf16(d, a_lo, b_hi, IDESC, 1u);
-              umma_bf16(d, a_hi, b_lo, IDESC, 1u);
+              const uint32_t acc = (k > 0 || !TapTable<MODE>::first(i)) ? 1u : 0u;
+              if (STACK) {
+                umma_bf16(d, a_hi, b_hi, IDESC2, acc);          // [hi*hi | hi*lo] : b_hi's 2N rows = [W_hi ; W_lo]
+                umma_bf16(d, a_lo, b_hi, IDESC, 1u);            // + lo*hi into the first half
+              } else {
+                umma_bf16(d, a_hi, b_hi, IDESC, acc);
+                umma_bf16(d, a_lo, b_hi, IDESC, 1u);
+                umma_bf16(d, a_hi, b_lo, IDESC, 1u);
+              }
             }
           }
           umma_commit(smem_u32(&s_empty[stage]));                       // frees the smem slot when the MMAs retire
@@ -247,9 +261,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
           for (int cb = 0; cb < N / 32; ++cb) {
             uint32_t v[32], w[32];
-            tmem_ld32(tcol + (ph * a.T + t) * N + cb * 32, v);
-            if (MODE == TC_S2 && a.ngrp == 2) tmem_ld32(tcol + (a.T + t) * N + cb * 32, w);      // S2 residual branch
+            tmem_ld32(tcol + (ph * a.T + t) * NACC + cb * 32, v);
+            if (MODE == TC_S2 && a.ngrp == 2) tmem_ld32(tcol + (a.T + t) * NACC + cb * 32, w);   // S2 residual branch
+            if (STACK) tmem_ld32(tcol + (ph * a.T + t) * NACC + N + cb * 32, w);                   // the hi*lo half
             tmem_ld_wait();
+            if (STACK) {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
+            }
             if (valid) {
 #pragma unroll
               for (int ch = 0; ch < 4; ++ch) {
@@ -295,7 +314,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
 
 namespace nconv {
 
-// ---- weight packing -> [kstage][wtap][part][j][CO][8] split bf16 -----------------------------------
+// ---- weight packing -> [kstage][wtap][j][part][CO][8] split bf16 -----------------------------------
 //   S1: w [CO][CI][3][3]                     9 taps
 //   S2: w [CO][CI][3][3] (+ w1 [CO][CI] 1x1) 9 (+1) taps
 //   T : w [CI][CO][4][4]                     16 taps; `lead` leading input channels (the depth channel of
@@ -322,9 +341,9 @@ __global__ void tc_pack_weights_kernel(const float* __restrict__ w, const float*
     }
     __nv_bfloat16 hi, lo;
     split_bf16(v, hi, lo);
-    const size_t base = ((size_t)(ks * ntw + wt) * 2) * 2 * CO * 8;     // [part][j][CO][8]
-    wp[base + ((size_t)(0 * 2 + j) * CO + co) * 8 + e] = hi;
-    wp[base + ((size_t)(1 * 2 + j) * CO + co) * 8 + e] = lo;
+    const size_t base = ((size_t)(ks * ntw + wt) * 2) * 2 * CO * 8;     // [j][part][CO][8]
+    wp[base + ((size_t)(j * 2 + 0) * CO + co) * 8 + e] = hi;
+    wp[base + ((size_t)(j * 2 + 1) * CO + co) * 8 + e] = lo;
   }
 }
 
@@ -335,10 +354,10 @@ static inline int tc_ntaps_w(int mode, bool has_1x1) { return mode == TC_T ? 16 
 // ---- tile geometry ---------------------------------------------------------------------------------
 struct TcPlan { int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, tiles_x, tiles_y; size_t smem; bool ok; };
 
-static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw) {
+static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw, bool stack) {
   TcPlan best = {}; best.ok = false;
   double best_cost = 1e300;
-  const int tmax = 256 / (N * ngrp);                   // accumulator columns per TMEM buffer
+  const int tmax = 256 / (N * (stack ? 2 : 1) * ngrp);  // M-tiles per TMEM buffer (256 columns each)
   const int hc = (mode == TC_S2) ? 1 : 2, hr = hc;     // halo columns / rows of the staged tile
   const int G = (mode == TC_S2) ? 4 : 1;
   for (int Wt = 8; Wt <= 250 && Wt <= AW + 7; ++Wt) {
@@ -363,9 +382,9 @@ static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw) {
   return best;
 }
 
-template <int N, int MODE>
+template <int N, int MODE, bool STACK = false>
 static int launch_tc(const TcArgs& a, const TcPlan& p, cudaStream_t st) {
-  auto kern = conv_tc_kernel<N, MODE>;
+  auto kern = conv_tc_kernel<N, MODE, STACK>;
   static bool attr_done[NCONV_MAX_DEVICES] = {};
   static int sm_count[NCONV_MAX_DEVICES] = {};
   int dev = 0, sms = 0;
@@ -476,7 +495,9 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   const int AH = (mode == TC_S2) ? d->H / 2 : d->H, AW = (mode == TC_S2) ? d->W / 2 : d->W;
   const int ngrp = (mode == TC_T) ? 4 : (has_1x1 ? 2 : 1);
   const int ntw = tc_ntaps_w(mode, has_1x1);
-  const TcPlan p = tc_plan(mode, AH, AW, d->CO, ngrp, ntw);
+  static const bool no_stack = getenv("NCONV_B200_NO_STACK") != nullptr;      // A/B measurements only
+  const bool stack = (mode == TC_S1) && d->CO == 32 && !no_stack;
+  const TcPlan p = tc_plan(mode, AH, AW, d->CO, ngrp, ntw, stack);
   if (!p.ok) return NCONV_ERR_UNSUPPORTED;
   TcArgs a = {};
   a.src[0] = (const __nv_bfloat16*)d->a; a.src[1] = (const __nv_bfloat16*)d->b;
@@ -498,7 +519,10 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   a.relu = d->relu; a.mode = mode;
   tc_build_taps(a, mode, has_1x1);
   cudaStream_t st = (cudaStream_t)stream;
-  if (mode == TC_S1) return d->CO == 64 ? launch_tc<64, TC_S1>(a, p, st) : launch_tc<32, TC_S1>(a, p, st);
+  if (mode == TC_S1) {
+    if (d->CO == 64) return launch_tc<64, TC_S1>(a, p, st);
+    return stack ? launch_tc<32, TC_S1, true>(a, p, st) : launch_tc<32, TC_S1>(a, p, st);
+  }
   if (mode == TC_S2) return d->CO == 64 ? launch_tc<64, TC_S2>(a, p, st) : launch_tc<32, TC_S2>(a, p, st);
   return d->CO == 64 ? launch_tc<64, TC_T>(a, p, st) : launch_tc<32, TC_T>(a, p, st);
 }
