@@ -38,8 +38,8 @@
 
 namespace nconv {
 
-constexpr int TC_THREADS = 192;
-constexpr int TC_STAGES = 2;
+constexpr int TC_THREADS = 224;      // warp 0, 6: producers; warp 1: MMA issuer; warps 2-5: epilogue
+constexpr int TC_MAX_STAGES = 3;
 constexpr int TC_SMEM_MAX = 227 * 1024 - 1024;   // dynamic part; static barriers etc. take the rest
 constexpr int TC_MAX_TAPS = 17;
 
@@ -107,7 +107,8 @@ struct TcArgs {
   int B, AH, AW, OH, OW;        // anchor grid and output size
   int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, ntaps, ntaps_w;
   int tiles_x, tiles_y, ntiles;
-  int relu, mode;
+  int relu, mode, stages;
+  int dbg;                      // NCONV_B200_TC_DEBUG bits (timing experiments only): 1 no stores, 2 no MMAs, 4 no loads
   TcTap taps[TC_MAX_TAPS];
 };
 
@@ -120,7 +121,7 @@ template <int N, int MODE, bool STACK>
 __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcArgs a) {
   constexpr int NACC = STACK ? 2 * N : N;                                   // accumulator columns per (group, M-tile)
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ __align__(8) uint64_t s_full[TC_STAGES], s_empty[TC_STAGES], s_tfull[2], s_tempty[2];
+  __shared__ __align__(8) uint64_t s_full[TC_MAX_STAGES], s_empty[TC_MAX_STAGES], s_tfull[2], s_tempty[2];
   __shared__ uint32_t s_tmem_base;
   __shared__ float s_scale[N], s_shift[N];
 
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
     s_shift[threadIdx.x] = a.shift ? __ldg(a.shift + threadIdx.x) : 0.f;
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < TC_STAGES; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
+    for (int s = 0; s < TC_MAX_STAGES; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -151,8 +152,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
 
-  if (warp == 0) {
-    // ===================== producer =====================
+  if (warp == 0 || warp == 6) {
+    // ===================== producers =====================
+    // A bulk copy takes its operands from uniform registers, so a warp issues its lanes' copies one at a
+    // time (~60 cycles each); with ~45 row copies per K-stage one warp could not keep ahead of the MMAs
+    // (ncu: the issuer sat on the `full` barrier).  Two warps split the rows; warp 0 also posts the
+    // expected byte count and the weight copy (the transaction count may go negative in between).
+    const int pw = (warp == 0) ? 0 : 1;
     uint32_t stage = 0, phase = 0;
     const uint32_t row_bytes = (uint32_t)a.P * 16;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
@@ -168,12 +174,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         mbar_wait(smem_u32(&s_empty[stage]), phase ^ 1);
         const uint32_t full = smem_u32(&s_full[stage]);
         const uint32_t sa = smem_base + stage * stage_bytes;
-        if (lane == 0) {
+        if (a.dbg & 4) { if (pw == 0 && lane == 0) mbar_arrive(full); __syncwarp(); if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; } continue; }
+        if (pw == 0 && lane == 0) {
           mbar_arrive_expect_tx(full, (uint32_t)ncopy * row_bytes + b_stage_bytes);
           bulk_g2s(sa + a_stage_bytes, a.wpack + (size_t)k * (b_stage_bytes / 2), b_stage_bytes, full);
         }
         __syncwarp();
-        for (int i = lane; i < ncopy; i += 32) {
+        for (int i = lane + 32 * pw; i < ncopy; i += 64) {
           const int pl = i / nrow, r = i - pl * nrow;          // pl = (g*2 + part)*2 + j
           const int j = pl & 1, part = (pl >> 1) & 1, g = pl >> 2;
           const int chunk = lone ? 0 : c0 + j;
@@ -182,7 +189,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           bulk_g2s(sa + pl * a_plane_bytes + r * row_bytes, gp, row_bytes, full);
         }
         __syncwarp();
-        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -219,6 +226,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
               const uint64_t b_hi = ((uint64_t)DESC_HI << 32) | (bo | B_LBO);
               const uint64_t b_lo = ((uint64_t)DESC_HI << 32) | ((bo + BLO_OFF) | B_LBO);
               const uint32_t acc = (k > 0 || !TapTable<MODE>::first(i)) ? 1u : 0u;
+              if (a.dbg & 2) continue;
               if (STACK) {
                 umma_bf16(d, a_hi, b_hi, IDESC2, acc);          // [hi*hi | hi*lo] : b_hi's 2N rows = [W_hi ; W_lo]
                 umma_bf16(d, a_lo, b_hi, IDESC, 1u);            // + lo*hi into the first half
@@ -233,7 +241,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           if (k == nk - 1) umma_commit(smem_u32(&s_tfull[buf]));       // accumulators of this tile complete
         }
         __syncwarp();
-        if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -269,7 +277,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
               for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
             }
-            if (valid) {
+            if (valid && !(a.dbg & 1)) {
 #pragma unroll
               for (int ch = 0; ch < 4; ++ch) {
                 float f[8];
@@ -352,9 +360,9 @@ static inline int tc_nstage(int mode, int CA, int CB) { return tc_lead(mode, CA)
 static inline int tc_ntaps_w(int mode, bool has_1x1) { return mode == TC_T ? 16 : (mode == TC_S2 && has_1x1 ? 10 : 9); }
 
 // ---- tile geometry ---------------------------------------------------------------------------------
-struct TcPlan { int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, tiles_x, tiles_y; size_t smem; bool ok; };
+struct TcPlan { int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, tiles_x, tiles_y; size_t smem; bool ok; int stages; double cost; };
 
-static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw, bool stack) {
+static TcPlan tc_plan_stages(int mode, int AH, int AW, int N, int ngrp, int ntw, bool stack, int stages) {
   TcPlan best = {}; best.ok = false;
   double best_cost = 1e300;
   const int tmax = 256 / (N * (stack ? 2 : 1) * ngrp);  // M-tiles per TMEM buffer (256 columns each)
@@ -368,18 +376,28 @@ static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw, bool s
       if (T > tmax) break;
       const int maxshift = hr * P + hc;
       const int rows_alloc = (T * 128 + maxshift + P) / P;
-      const size_t smem = (size_t)TC_STAGES * ((size_t)G * 4 * rows_alloc * P * 16 + (size_t)ntw * 2 * 2 * N * 16);
+      const size_t smem = (size_t)stages * ((size_t)G * 4 * rows_alloc * P * 16 + (size_t)ntw * 2 * 2 * N * 16);
       if (smem > (size_t)TC_SMEM_MAX) continue;
       const int tx = (AW + Wt - 1) / Wt, ty = (AH + R - 1) / R;
       // MMA rows issued per tile (x taps, constant) plus a load term for re-read halo rows and weights
       const double cost = (double)tx * ty * (T * 128.0 + 0.25 * G * (R + hr) * P + 0.02 * ntw * N);
       if (cost < best_cost) {
         best_cost = cost;
-        best = {R, Wt, P, T, rows_alloc, R + hr, G, ngrp, tx, ty, smem, true};
+        best = {R, Wt, P, T, rows_alloc, R + hr, G, ngrp, tx, ty, smem, true, stages, cost};
       }
     }
   }
   return best;
+}
+
+// A 3-deep ring lets the loads run two K-stages ahead of the MMAs; take it unless it forces a much worse tile.
+static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw, bool stack) {
+  static const char* force = getenv("NCONV_B200_TC_STAGES");          // A/B measurements only
+  const TcPlan p2 = tc_plan_stages(mode, AH, AW, N, ngrp, ntw, stack, 2);
+  const TcPlan p3 = tc_plan_stages(mode, AH, AW, N, ngrp, ntw, stack, 3);
+  if (force) return atoi(force) == 3 && p3.ok ? p3 : p2;
+  if (p3.ok && (!p2.ok || p3.cost <= 1.12 * p2.cost)) return p3;
+  return p2;
 }
 
 template <int N, int MODE, bool STACK = false>
@@ -516,7 +534,8 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.T = p.T; a.rows_alloc = p.rows_alloc; a.rows_ld = p.rows_ld;
   a.G = p.G; a.ngrp = ngrp; a.ntaps_w = ntw;
   a.tiles_x = p.tiles_x; a.tiles_y = p.tiles_y; a.ntiles = p.tiles_x * p.tiles_y * d->B;
-  a.relu = d->relu; a.mode = mode;
+  a.relu = d->relu; a.mode = mode; a.stages = p.stages;
+  { static const char* dbg = getenv("NCONV_B200_TC_DEBUG"); a.dbg = dbg ? atoi(dbg) : 0; }
   tc_build_taps(a, mode, has_1x1);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == TC_S1) {
