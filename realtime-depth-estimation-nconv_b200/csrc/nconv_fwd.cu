@@ -76,6 +76,8 @@ extern "C" int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* 
   a.a_first = d->a_first; a.eps = d->eps; a.thr = d->thr;
   a.map_h = NearestMap::make(d->CB > 0 ? d->HB : d->H, d->H);
   a.map_w = NearestMap::make(d->CB > 0 ? d->WB : d->W, d->W);
+  a.up2_vec = d->CB > 0 && d->W == 2 * d->WB && d->H == 2 * d->HB && (d->WB % 2 == 0) && (d->W % 4 == 0) &&
+              ((reinterpret_cast<uintptr_t>(d->xb) | reinterpret_cast<uintptr_t>(d->cb)) & 7u) == 0;
   a.vec_ok = (d->W % 4 == 0) && (a.WO % 4 == 0) && aligned16(d->xa) &&
              (thresh || aligned16(d->ca)) &&
              (tail ? aligned16(d->out_tail) : (aligned16(d->y) && aligned16(d->cout)));
