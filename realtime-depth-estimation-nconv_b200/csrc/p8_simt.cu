@@ -45,11 +45,11 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
 
   const int n = blockIdx.z, y = blockIdx.y;
   const int xb = blockIdx.x * (SM_THREADS * PXT) + tid;
-  float acc[PXT][CO];
+  u64 acc2[PXT][CO / 2];          // packed pairs of output channels (FFMA2: weight pair x broadcast input)
 #pragma unroll
   for (int p = 0; p < PXT; ++p)
 #pragma unroll
-    for (int o = 0; o < CO; ++o) acc[p][o] = 0.f;
+    for (int o = 0; o < CO / 2; ++o) acc2[p][o] = 0ull;
   float centre[PXT][CI];
 
 #pragma unroll
@@ -75,13 +75,11 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
         const float* wr = s_w + (ci * 9 + u * 3 + v) * CO;
 #pragma unroll
         for (int o = 0; o < CO; o += 4) {
-          const float4 w4 = *reinterpret_cast<const float4*>(wr + o);
+          const ulonglong2 w4 = *reinterpret_cast<const ulonglong2*>(wr + o);
 #pragma unroll
           for (int p = 0; p < PXT; ++p) {
-            acc[p][o] = fmaf(w4.x, in[p][v], acc[p][o]);
-            acc[p][o + 1] = fmaf(w4.y, in[p][v], acc[p][o + 1]);
-            acc[p][o + 2] = fmaf(w4.z, in[p][v], acc[p][o + 2]);
-            acc[p][o + 3] = fmaf(w4.w, in[p][v], acc[p][o + 3]);
+            ffma2(acc2[p][o / 2], w4.x, in[p][v]);
+            ffma2(acc2[p][o / 2 + 1], w4.y, in[p][v]);
           }
         }
       }
@@ -100,7 +98,7 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const int o = ch * 8 + e;
-        float v = fmaf(acc[p][o], s_scale[o], s_shift[o]);
+        float v = fmaf((o & 1) ? hi32f(acc2[p][o >> 1]) : lo32f(acc2[p][o >> 1]), s_scale[o], s_shift[o]);
         if (a.relu) v = fmaxf(v, 0.f);
         if (a.w1) {
 #pragma unroll
@@ -125,49 +123,73 @@ struct HeadArgs {
   int B, H, W;
 };
 
-// One thread = one output pixel; the P8 ring supplies the zero padding (no bounds tests on loads).
+// 3x3 C->1 head as "1x1 to nine planes, then a shifted sum":  t[tap][p] = sum_c w[c][tap] * f[c][p] is
+// computed ONCE per pixel of the tile + halo (each feature vector is loaded and converted from split bf16
+// once: 8 x 16-byte loads, instead of nine times through L1 as a direct 3x3 gather would), kept in shared
+// memory, and out[y][x] = sum_{u,v} t[3u+v][y+u-1][x+v-1] + residual.  The P8 ring supplies the zero padding.
+// FMAs are packed over tap pairs (FFMA2: weight pair from shared memory, the feature as the broadcast scalar).
+constexpr int HD_TW = 64, HD_TH = 16, HD_PW = HD_TW + 2, HD_PH = HD_TH + 2, HD_THREADS = 256;
+
 template <int C>
-__global__ void __launch_bounds__(128) head_p8_kernel(const HeadArgs a) {
-  __shared__ __align__(16) float s_w[C * 9];    // [chunk][tap][8]
-  for (int i = threadIdx.x; i < C * 9; i += 128) {
-    const int e = i & 7, tap = (i >> 3) % 9, ch = i / 72;
-    s_w[i] = __ldg(a.w + (size_t)(ch * 8 + e) * 9 + tap);
+__global__ void __launch_bounds__(HD_THREADS) head_p8_kernel(const HeadArgs a) {
+  __shared__ __align__(16) float s_w[C * 10];            // [c][tap 0..8, pad]
+  __shared__ float s_t[9][HD_PH][HD_PW + 1];
+  for (int i = threadIdx.x; i < C * 10; i += HD_THREADS) {
+    const int tap = i % 10, c = i / 10;
+    s_w[i] = tap < 9 ? __ldg(a.w + (size_t)c * 9 + tap) : 0.f;
   }
   __syncthreads();
-  const int n = blockIdx.z, y = blockIdx.y, x = blockIdx.x * 128 + threadIdx.x;
-  if (x >= a.W) return;
+  const int n = blockIdx.z, y0 = blockIdx.y * HD_TH, x0 = blockIdx.x * HD_TW;
   const P8Geom g = P8Geom::make(a.B, C, a.H, a.W);
-  float acc0 = 0.f, acc1 = 0.f;
+  // ---- phase 1: nine partial dot products per staged pixel (padded coords: tile pixel (r, c) = image (y0+r-1, x0+c-1))
+  for (int p = threadIdx.x; p < HD_PH * HD_PW; p += HD_THREADS) {
+    const int r = p / HD_PW, c = p - r * HD_PW;
+    const int py = y0 + r, px = x0 + c;                  // padded plane coordinates
+    u64 acc[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
+    if (py < a.H + 2 && px < a.W + 2) {
+      const size_t off = ((size_t)py * g.Wp + px) * 8;
 #pragma unroll 1
-  for (int ch = 0; ch < C / 8; ++ch) {
-    const __nv_bfloat16* ph = a.f + g.plane(n, ch, 0);
-    const __nv_bfloat16* pl = a.f + g.plane(n, ch, 1);
+      for (int ch = 0; ch < C / 8; ++ch) {
+        const uint4 hi = __ldg(reinterpret_cast<const uint4*>(a.f + g.plane(n, ch, 0) + off));
+        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(a.f + g.plane(n, ch, 1) + off));
+        float f[8];
+        join8(hi, lo, f);
 #pragma unroll
-    for (int tap = 0; tap < 9; ++tap) {
-      const int u = tap / 3, v = tap - 3 * u;
-      const size_t off = ((size_t)(y + u) * g.Wp + (x + v)) * 8;     // padded coords: (y+u-1)+1, (x+v-1)+1
-      const uint4 hi = __ldg(reinterpret_cast<const uint4*>(ph + off));
-      const uint4 lo = __ldg(reinterpret_cast<const uint4*>(pl + off));
-      float f[8];
-      join8(hi, lo, f);
-      const float4 w0 = *reinterpret_cast<const float4*>(s_w + (ch * 9 + tap) * 8);
-      const float4 w1 = *reinterpret_cast<const float4*>(s_w + (ch * 9 + tap) * 8 + 4);
-      acc0 = fmaf(w0.x, f[0], acc0); acc1 = fmaf(w0.y, f[1], acc1);
-      acc0 = fmaf(w0.z, f[2], acc0); acc1 = fmaf(w0.w, f[3], acc1);
-      acc0 = fmaf(w1.x, f[4], acc0); acc1 = fmaf(w1.y, f[5], acc1);
-      acc0 = fmaf(w1.z, f[6], acc0); acc1 = fmaf(w1.w, f[7], acc1);
+        for (int e = 0; e < 8; ++e) {
+          const float* wr = s_w + (ch * 8 + e) * 10;
+#pragma unroll
+          for (int q = 0; q < 5; ++q) ffma2(acc[q], *reinterpret_cast<const u64*>(wr + 2 * q), f[e]);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+      s_t[2 * q][r][c] = lo32f(acc[q]);
+      if (2 * q + 1 < 9) s_t[2 * q + 1][r][c] = hi32f(acc[q]);
     }
   }
-  const size_t o = ((size_t)n * a.H + y) * a.W + x;
-  const float v = acc0 + acc1 + (a.residual ? __ldg(a.residual + o) : 0.f);
-  a.y[o] = v;
-  if (a.y8) {
-    const P8Geom g1 = P8Geom::make(a.B, 1, a.H, a.W);
-    float f[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    uint4 hi, lo;
-    split8(f, hi, lo);
-    *reinterpret_cast<uint4*>(a.y8 + g1.plane(n, 0, 0) + g1.pixel(y, x)) = hi;
-    *reinterpret_cast<uint4*>(a.y8 + g1.plane(n, 0, 1) + g1.pixel(y, x)) = lo;
+  __syncthreads();
+  // ---- phase 2: shifted sum + residual; 4 outputs per thread
+  const P8Geom g1 = P8Geom::make(a.B, 1, a.H, a.W);
+  for (int p = threadIdx.x; p < HD_TH * HD_TW; p += HD_THREADS) {
+    const int r = p / HD_TW, c = p - r * HD_TW;
+    const int y = y0 + r, x = x0 + c;
+    if (y >= a.H || x >= a.W) continue;
+    float v = 0.f;
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+#pragma unroll
+      for (int w = 0; w < 3; ++w) v += s_t[u * 3 + w][r + u][c + w];
+    const size_t o = ((size_t)n * a.H + y) * a.W + x;
+    if (a.residual) v += __ldg(a.residual + o);
+    a.y[o] = v;
+    if (a.y8) {
+      float f[8] = {v, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      uint4 hi, lo;
+      split8(f, hi, lo);
+      *reinterpret_cast<uint4*>(a.y8 + g1.plane(n, 0, 0) + g1.pixel(y, x)) = hi;
+      *reinterpret_cast<uint4*>(a.y8 + g1.plane(n, 0, 1) + g1.pixel(y, x)) = lo;
+    }
   }
 }
 
@@ -206,13 +228,13 @@ extern "C" int nconv_b200_head_p8(const void* f, const float* w, const float* re
   if (!f || !w || !y || B <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
   if (C != 32 && C != 64) return NCONV_ERR_UNSUPPORTED;
   HeadArgs a = {(const __nv_bfloat16*)f, w, residual, y, (__nv_bfloat16*)y8, B, H, W};
-  dim3 grid(ceil_div(W, 128), H, B);
+  dim3 grid(ceil_div(W, HD_TW), ceil_div(H, HD_TH), B);
   char label[64];
   snprintf(label, sizeof(label), "head_p8 %d->1 @%dx%d", C, H, W);
   const double px = (double)B * H * W;
   cudaStream_t st = (cudaStream_t)stream;
   LaunchScope ls(st, label, 2.0 * C * 9 * px, 4.0 * (C + 2 + (y8 ? 1 : 0)) * px);
-  if (C == 64) head_p8_kernel<64><<<grid, 128, 0, st>>>(a);
-  else head_p8_kernel<32><<<grid, 128, 0, st>>>(a);
+  if (C == 64) head_p8_kernel<64><<<grid, HD_THREADS, 0, st>>>(a);
+  else head_p8_kernel<32><<<grid, HD_THREADS, 0, st>>>(a);
   return (int)cudaGetLastError();
 }
