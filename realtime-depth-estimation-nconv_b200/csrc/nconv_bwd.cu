@@ -218,26 +218,32 @@ template <int CI, int CO, int K>
 __global__ void nconv_wgrad_final(const float* __restrict__ partial, const float* __restrict__ chan_part,
                                   const float* __restrict__ wsum, float* __restrict__ gw,
                                   float* __restrict__ gb, int ctas_x) {
+  // one warp per output element; lane l sums partials l, l+32, ... in a fixed order, then a
+  // fixed-shape shuffle tree: deterministic for a given ctas_x
   using C = WGradCfg<CI, CO, K>;
   const int total = CO * CI * K * K;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total + CO; idx += gridDim.x * blockDim.x) {
+  const int lane = threadIdx.x & 31;
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
+  for (int idx = wid; idx < total + CO; idx += nw) {
     if (idx < total) {
       int v = idx % K, u = (idx / K) % K, i = (idx / (K * K)) % CI, o = idx / (K * K * CI);
       int oc = o / C::CO_T, ol = o % C::CO_T, ic = i / C::CCH, il = i % C::CCH;
       int chunk = oc * C::NCI + ic;
       int local = ((ol * C::CCH + il) * K + u) * K + v;
       float s = 0.f, T = 0.f;
-      for (int cta = 0; cta < ctas_x; ++cta) {
+      for (int cta = lane; cta < ctas_x; cta += 32) {
         s += __ldg(partial + ((size_t)chunk * ctas_x + cta) * C::OUT_PER_CTA + local);
         T += __ldg(chan_part + (((size_t)oc * ctas_x + cta) * 2 + 1) * 8 + ol);
       }
-      gw[idx] = s - T / __ldg(wsum + o);
+      s = warp_sum(s); T = warp_sum(T);
+      if (lane == 0) gw[idx] = s - T / __ldg(wsum + o);
     } else if (gb) {
       int o = idx - total;
       int oc = o / C::CO_T, ol = o % C::CO_T;
       float s = 0.f;
-      for (int cta = 0; cta < ctas_x; ++cta) s += __ldg(chan_part + (((size_t)oc * ctas_x + cta) * 2 + 0) * 8 + ol);
-      gb[o] = s;
+      for (int cta = lane; cta < ctas_x; cta += 32) s += __ldg(chan_part + (((size_t)oc * ctas_x + cta) * 2 + 0) * 8 + ol);
+      s = warp_sum(s);
+      if (lane == 0) gb[o] = s;
     }
   }
 }
@@ -332,7 +338,7 @@ __global__ void nconv_bwd_weight_generic(const float* __restrict__ gy, const flo
 }
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-constexpr int WG_CTAS_X_MAX = 148;
+constexpr int WG_CTAS_X_MAX = 148 * 6;
 
 template <int CI, int CO, int K, int PAD>
 static int launch_wgrad(WGradArgs a, float* ws_partial, float* gw, float* gb, cudaStream_t st) {
@@ -347,7 +353,15 @@ static int launch_wgrad(WGradArgs a, float* ws_partial, float* gw, float* gb, cu
   }
   const int chunks = C::NCI * C::NCO;
   const int ntiles = a.B * ceil_div(a.HO, WG_TH) * ceil_div(a.WO, WG_TW);
-  int ctas_x = (2 * 148 + chunks - 1) / chunks;
+  static int occ_cache[NCONV_MAX_DEVICES] = {};
+  int occ = dev < NCONV_MAX_DEVICES ? occ_cache[dev] : 0;
+  if (occ == 0) {
+    NCONV_RETURN_IF_ERR(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WG_THREADS, C::BYTES));
+    if (occ < 1) occ = 1;
+    if (occ > 6) occ = 6;
+    if (dev < NCONV_MAX_DEVICES) occ_cache[dev] = occ;
+  }
+  int ctas_x = (occ * 148 + chunks - 1) / chunks;
   if (ctas_x > WG_CTAS_X_MAX) ctas_x = WG_CTAS_X_MAX;
   if (ctas_x > ntiles) ctas_x = ntiles;
   a.partial = ws_partial;
@@ -364,7 +378,7 @@ static int launch_wgrad(WGradArgs a, float* ws_partial, float* gw, float* gb, cu
   const int total = CO * CI * K * K + CO;
   {
     LaunchScope ls(st, "nconv_wgrad_final", 0.0, 4.0 * (double)chunks * ctas_x * C::OUT_PER_CTA);
-    nconv_wgrad_final<CI, CO, K><<<ceil_div(total, 128), 128, 0, st>>>(a.partial, a.chan_part, a.wsum, gw, gb, ctas_x);
+    nconv_wgrad_final<CI, CO, K><<<ceil_div(total, 4), 128, 0, st>>>(a.partial, a.chan_part, a.wsum, gw, gb, ctas_x);
   }
   return (int)cudaGetLastError();
 }
@@ -403,6 +417,7 @@ static int bwd_data_dispatch(const TiledArgs& t, int Ci, int Co, int kh, int ph,
   BWD_DATA_CASE(8, 16, 8, 3, 1)
   BWD_DATA_CASE(8, 16, 8, 3, 0)
   BWD_DATA_CASE(1, 8, 8, 1, 2)
+  BWD_DATA_CASE(8, 1, 1, 5, 2)
   BWD_DATA_CASE(2, 1, 1, 3, 1)
   BWD_DATA_CASE(2, 2, 2, 3, 1)
   BWD_DATA_CASE(4, 4, 4, 3, 1)

@@ -100,6 +100,14 @@ extern "C" int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* 
       return launch_stream<ci_, co_, k_, pf_, false>(d->xa, d->ca, d->w, d->bias, d->y, d->cout, d->B, d->H,  \
                                                      d->W, d->eps, d->thr, st);                      \
     }
+    static const int alt = getenv("NCONV_B200_STREAM_ALT") ? atoi(getenv("NCONV_B200_STREAM_ALT")) : 0;
+    if (alt == 1) {   // experiment switch: deeper prefetch ring / extra shapes on the stream kernel
+      NCONV_STREAM_CASE(1, 2, 3, 6)
+      NCONV_STREAM_CASE(2, 2, 3, 6)
+      NCONV_STREAM_CASE(4, 4, 3, 4)
+      NCONV_STREAM_CASE(1, 2, 5, 5)
+      NCONV_STREAM_CASE(2, 2, 5, 5)
+    }
     NCONV_STREAM_CASE(1, 2, 3, 3)
     NCONV_STREAM_CASE(2, 2, 3, 3)
     // (4,4,3), (1,2,5), (2,2,5) measured no faster than the tiled kernel (issue-bound): left on it.

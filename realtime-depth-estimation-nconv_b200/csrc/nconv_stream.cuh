@@ -61,37 +61,41 @@ __device__ __forceinline__ void fmul2(u64& acc, u64 w, float s) {
   asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%2, %2};\n\tmul.rn.f32x2 %0, %1, t;\n\t}" : "=l"(acc) : "l"(w), "f"(s));
 }
 
-// Per-lane addressing state: everything that does not change along the walk is computed once.
-struct StLane {
-  const float* px; const float* pc;   // own 4 px of (channel 0, first input row); advanced by W per row
-  int hoff;                           // halo offset in floats relative to px (edge lanes)
-  bool inb, hload;                    // own px inside the image / this lane fetches a halo
-};
+// 1/v for v >= eps > 0 (no zero / denormal / infinity handling needed): one MUFU.RCP, 1 ulp.
+__device__ __forceinline__ float rcp_fast(float v) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
 
+// One prefetch: rows outside the image and columns outside the row stay zero (zero padding), so the
+// compute step needs no branch — a padded row simply adds zeros.  Pointers may point outside the
+// tensor when the predicate is false; they are never dereferenced then.
 template <int PAD, bool THRESH>
-__device__ __forceinline__ void st_load(ChanRow<PAD>& r, const StLane& L, size_t off, bool rowok) {
+__device__ __forceinline__ void st_load(ChanRow<PAD>& r, const float* px, const float* pc, int hoff,
+                                        bool own, bool halo) {
   const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
   r.x = z; r.c = z;
 #pragma unroll
   for (int j = 0; j < PAD; ++j) { r.hx[j] = 0.f; r.hc[j] = 0.f; }
-  if (rowok && L.inb) {
-    r.x = __ldg(reinterpret_cast<const float4*>(L.px + off));
-    if (!THRESH) r.c = __ldg(reinterpret_cast<const float4*>(L.pc + off));
+  if (own) {
+    r.x = __ldg(reinterpret_cast<const float4*>(px));
+    if (!THRESH) r.c = __ldg(reinterpret_cast<const float4*>(pc));
   }
-  if (rowok && L.hload) {
+  if (halo) {
     if (PAD == 2) {
-      const float2 hx = __ldg(reinterpret_cast<const float2*>(L.px + off + L.hoff));
+      const float2 hx = __ldg(reinterpret_cast<const float2*>(px + hoff));
       r.hx[0] = hx.x; r.hx[PAD - 1] = hx.y;
-      if (!THRESH) { const float2 hc = __ldg(reinterpret_cast<const float2*>(L.pc + off + L.hoff)); r.hc[0] = hc.x; r.hc[PAD - 1] = hc.y; }
+      if (!THRESH) { const float2 hc = __ldg(reinterpret_cast<const float2*>(pc + hoff)); r.hc[0] = hc.x; r.hc[PAD - 1] = hc.y; }
     } else {
-      r.hx[0] = __ldg(L.px + off + L.hoff);
-      if (!THRESH) r.hc[0] = __ldg(L.pc + off + L.hoff);
+      r.hx[0] = __ldg(px + hoff);
+      if (!THRESH) r.hc[0] = __ldg(pc + hoff);
     }
   }
 }
 
 template <int CI, int CO, int K, int PF, bool THRESH>
-__global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a) {
+__global__ void __launch_bounds__(ST_WARPS * 32, (K == 3 && CI * CO <= 4 && PF <= 3) ? 2 : 1) nconv_stream(const StreamArgs a) {
   constexpr int PAD = K / 2, CO_P = CO / 2, WIN = ST_PX + 2 * PAD;
   constexpr int U = st_lcm(K * CI, PF);          // unroll: accumulator-set, channel and ring indices all static
   static_assert(CO % 2 == 0 && (K == 3 || K == 5), "stream kernel: even CO, K in {3,5}");
@@ -119,8 +123,10 @@ __global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a
 
   const long long unit = (long long)blockIdx.x * ST_WARPS + warp;
   if (unit >= a.units) return;
-  const int seg = (int)(unit % a.nseg);
-  const int strip = (int)((unit / a.nseg) % a.nstrip);
+  // strip index fastest: the warps of a CTA (and neighbouring CTAs) walk adjacent strips of the SAME rows, so
+  // what is in flight at any moment is whole contiguous image rows (DRAM page locality), not 512 B pieces
+  const int strip = (int)(unit % a.nstrip);
+  const int seg = (int)((unit / a.nstrip) % a.nseg);
   const int b = (int)(unit / ((long long)a.nseg * a.nstrip));
   const int oy0 = seg * a.RS, x0 = strip * ST_COLS, col = x0 + ST_PX * lane;
   const int rows = min(a.RS, a.H - oy0);
@@ -128,17 +134,21 @@ __global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a
   const int W = a.W;
   const size_t plane = (size_t)a.H * W;
 
-  StLane L;
-  {
-    // pointer of (channel 0, input row oy0-PAD); rows outside the image are never dereferenced
-    const long long first = ((long long)b * CI * a.H + (oy0 - PAD)) * W + col;
-    L.px = a.x + first; L.pc = THRESH ? a.x + first : a.c + first;
-    L.inb = col < W;
-    const int hcol = (lane == 0) ? x0 - PAD : x0 + ST_COLS;
-    L.hload = (lane == 0 || lane == 31) && hcol >= 0 && hcol < W;
-    L.hoff = (lane == 0) ? -PAD : ST_PX;
-  }
-  const int t_lo = max(0, PAD - oy0), t_hi = min(T, a.H + PAD - oy0);   // input rows inside the image
+  // ---- per-lane state that does not change along the walk
+  const bool inb = col < W;
+  const int hcol = (lane == 0) ? x0 - PAD : x0 + ST_COLS;
+  const bool hlane = (lane == 0 || lane == 31) && hcol >= 0 && hcol < W;
+  const int hoff = (lane == 0) ? -PAD : ST_PX;
+  // input rows inside the image are t in [t_lo, t_hi): one unsigned compare per prefetch
+  const int t_lo = max(0, PAD - oy0);
+  const unsigned t_n = (unsigned)(min(T, a.H + PAD - oy0) - t_lo);
+  // load cursor: (row of the next prefetch, channel 0), own 4 px
+  const long long first = ((long long)b * CI * a.H + (oy0 - PAD)) * W + col;
+  const float* lx = a.x + first;
+  const float* lc = THRESH ? lx : a.c + first;
+  // store cursor: output row 0 of channel 0 (own px); advanced by W per finished row
+  float* yp = a.y + ((size_t)b * CO * a.H + oy0) * W + col;
+  float* cp = a.co + ((size_t)b * CO * a.H + oy0) * W + col;
 
   u64 accN[K][CO_P][ST_PX], accD[K][CO_P][ST_PX];
 #pragma unroll
@@ -152,11 +162,11 @@ __global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a
 #pragma unroll
   for (int i = 0; i < PF; ++i) {
     const int t = i / CI, ci = i % CI;
-    st_load<PAD, THRESH>(ring[i], L, (size_t)t * W + ci * plane, t >= t_lo && t < t_hi);
+    const bool ok = (unsigned)(t - t_lo) < t_n;
+    st_load<PAD, THRESH>(ring[i], lx + ci * plane, lc + ci * plane, hoff, ok && inb, ok && hlane);
+    if (ci == CI - 1) { lx += W; lc += W; }
   }
-
-  float* ypt = a.y + ((size_t)b * CO * a.H + oy0) * W + col;      // output row 0 of channel 0 (own px)
-  float* cpt = a.co + ((size_t)b * CO * a.H + oy0) * W + col;
+  int tl_next = PF / CI;      // row index of the load cursor
 
 #pragma unroll 1
   for (int tb = 0; tb < T; tb += U / CI) {
@@ -165,8 +175,7 @@ __global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a
       const int tl = sl / CI, ci = sl % CI, ph = tl % K;     // static after unrolling (U % (K*CI) == 0)
       const int t = tb + tl;
       if (t < T) {
-        const bool rowok = t >= t_lo && t < t_hi;
-        if (rowok) {
+        {
           // ---- window of this (row, channel): own px, neighbours' px by shuffle, strip-edge halo from the ring
           const ChanRow<PAD>& r = ring[sl % PF];
           float xw[WIN], cw[WIN];
@@ -183,12 +192,12 @@ __global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a
             float hc = r.hc[j];
             if (THRESH) hc = (r.hx[j] > a.thr) ? 1.f : 0.f;
             const float hxc = r.hx[j] * hc;
-            const float lx = __shfl_up_sync(0xffffffffu, xw[ST_PX + j], 1);
-            const float lc = __shfl_up_sync(0xffffffffu, cw[ST_PX + j], 1);
-            const float rx = __shfl_down_sync(0xffffffffu, xw[PAD + j], 1);
-            const float rc = __shfl_down_sync(0xffffffffu, cw[PAD + j], 1);
-            xw[j] = (lane == 0) ? hxc : lx;               cw[j] = (lane == 0) ? hc : lc;
-            xw[PAD + ST_PX + j] = (lane == 31) ? hxc : rx; cw[PAD + ST_PX + j] = (lane == 31) ? hc : rc;
+            const float lxv = __shfl_up_sync(0xffffffffu, xw[ST_PX + j], 1);
+            const float lcv = __shfl_up_sync(0xffffffffu, cw[ST_PX + j], 1);
+            const float rxv = __shfl_down_sync(0xffffffffu, xw[PAD + j], 1);
+            const float rcv = __shfl_down_sync(0xffffffffu, cw[PAD + j], 1);
+            xw[j] = (lane == 0) ? hxc : lxv;               cw[j] = (lane == 0) ? hc : lcv;
+            xw[PAD + ST_PX + j] = (lane == 31) ? hxc : rxv; cw[PAD + ST_PX + j] = (lane == 31) ? hc : rcv;
           }
           const float* wci = s_w + ci * K * K * CO;
 #pragma unroll
@@ -221,38 +230,35 @@ __global__ void __launch_bounds__(ST_WARPS * 32) nconv_stream(const StreamArgs a
                 }
             }
           }
-        } else if (ci == 0) {
-          // input row outside the image: the output row that would start here starts from zero
-#pragma unroll
-          for (int o = 0; o < CO_P; ++o)
-#pragma unroll
-            for (int p = 0; p < ST_PX; ++p) { accN[ph][o][p] = 0ull; accD[ph][o][p] = 0ull; }
         }
-        // ---- refill the ring slot PF steps ahead
+        // ---- refill the ring slot PF steps ahead (cursor arithmetic is static apart from the row test)
         {
-          const int tn = tb + (sl + PF) / CI, cn = (sl + PF) % CI;
-          st_load<PAD, THRESH>(ring[sl % PF], L, (size_t)tn * W + cn * plane, tn >= t_lo && tn < t_hi);
+          const int cn = (sl + PF) % CI;
+          const bool ok = (unsigned)(tl_next - t_lo) < t_n;
+          st_load<PAD, THRESH>(ring[sl % PF], lx + cn * plane, lc + cn * plane, hoff, ok && inb, ok && hlane);
+          if (cn == CI - 1) { lx += W; lc += W; ++tl_next; }
         }
         if (ci == CI - 1) {
           // ---- output row t-(K-1) has now seen all of its K input rows
           const int slot = (ph + 1) % K;
-          const int ro = t - (K - 1);
-          if (ro >= 0 && L.inb) {
+          if (t >= K - 1) {
+            if (inb) {
 #pragma unroll
-            for (int o = 0; o < CO; ++o) {
-              float yv[ST_PX], cvv[ST_PX];
-              const float bo = s_bias[o], rs = s_rs[o];
+              for (int o = 0; o < CO; ++o) {
+                float yv[ST_PX], cvv[ST_PX];
+                const float bo = s_bias[o], rs = s_rs[o];
 #pragma unroll
-              for (int p = 0; p < ST_PX; ++p) {
-                const float N = (o & 1) ? hi32f(accN[slot][o >> 1][p]) : lo32f(accN[slot][o >> 1][p]);
-                const float D = (o & 1) ? hi32f(accD[slot][o >> 1][p]) : lo32f(accD[slot][o >> 1][p]);
-                yv[p] = __fdividef(N, D + a.eps) + bo;
-                cvv[p] = D * rs;
+                for (int p = 0; p < ST_PX; ++p) {
+                  const float N = (o & 1) ? hi32f(accN[slot][o >> 1][p]) : lo32f(accN[slot][o >> 1][p]);
+                  const float D = (o & 1) ? hi32f(accD[slot][o >> 1][p]) : lo32f(accD[slot][o >> 1][p]);
+                  yv[p] = fmaf(N, rcp_fast(D + a.eps), bo);
+                  cvv[p] = D * rs;
+                }
+                __stcs(reinterpret_cast<float4*>(yp + o * plane), make_float4(yv[0], yv[1], yv[2], yv[3]));
+                __stcs(reinterpret_cast<float4*>(cp + o * plane), make_float4(cvv[0], cvv[1], cvv[2], cvv[3]));
               }
-              const size_t off = o * plane + (size_t)ro * W;
-              __stcs(reinterpret_cast<float4*>(ypt + off), make_float4(yv[0], yv[1], yv[2], yv[3]));
-              __stcs(reinterpret_cast<float4*>(cpt + off), make_float4(cvv[0], cvv[1], cvv[2], cvv[3]));
             }
+            yp += W; cp += W;
           }
         }
       }

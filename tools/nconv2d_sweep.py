@@ -43,6 +43,10 @@ def main():
     ap.add_argument("--width", type=int, default=640)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--no-bwd", action="store_true")
+    ap.add_argument("--flush", choices=["write", "read"], default="write")
+    ap.add_argument("--sleep-cycles", type=int, default=400000)
+    ap.add_argument("--breakdown", action="store_true", help="per-kernel times of one cold backward")
+    ap.add_argument("--only", type=str, default="", help="comma list of ci-co-k cases")
     args = ap.parse_args()
     from nconv_b200 import ops  # noqa: F401
     K = torch.ops.nconv_b200
@@ -50,9 +54,21 @@ def main():
     hbm, src = peaks()
     B, H, W = args.batch, args.height, args.width
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush_f = flush.view(torch.float32)
+
+    def do_flush():
+        # "write": L2 is left full of DIRTY lines, whose write-back the timed kernel then pays for;
+        # "read": the written buffer is read back, so the timed kernel starts on a cold, CLEAN L2.
+        flush.fill_(1)
+        if args.flush == "read":
+            flush_f.sum()
     cases = [(ci, co, k, k // 2) for k in (3, 5) for ci, co in SWEEP] + DNET_SHAPES
     rows = []
+    only = set(args.only.split(",")) if args.only else None
+    from nconv_b200 import _lib
     for idx, (ci, co, k, pad) in enumerate(cases):
+        if only and "%d-%d-%d" % (ci, co, k) not in only:
+            continue
         g = torch.Generator(device="cpu"); g.manual_seed(1000 + idx)
         x = (torch.rand(B, ci, H, W, generator=g) * 10).to(dev)
         c = (torch.rand(B, ci, H, W, generator=g) * (torch.rand(B, ci, H, W, generator=g) < 0.5)).to(dev)
@@ -67,7 +83,10 @@ def main():
                 fn()
             ts = []
             for _ in range(args.iters):
-                flush.fill_(1)
+                do_flush()
+                # a device-side spin lets the host finish enqueueing fn()'s launches before the
+                # timed region starts on the GPU (several launches + allocator calls per backward)
+                torch.cuda._sleep(args.sleep_cycles)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(); fn(); e1.record()
                 torch.cuda.synchronize()
@@ -87,12 +106,19 @@ def main():
             bytes_b = 4.0 * B * (4 * co * HO * WO + 4 * ci * H * W)
             row.update({"bwd_ms": ms_b, "bwd_GBs": bytes_b / ms_b / 1e6, "bwd_hbm_frac": bytes_b / ms_b / 1e6 / hbm,
                         "bwd_TFLOPs": 2 * flops_f / ms_b / 1e9})
+            if args.breakdown:
+                do_flush(); torch.cuda.synchronize()
+                _lib.profile_enable(True)
+                K.nconv2d_backward(gy, gc, x, c, w, b, y, co_, pad, pad, 1e-7, True, True, True)
+                torch.cuda.synchronize()
+                row["bwd_kernels"] = [(l, round(ms, 4)) for l, ms, _, _ in _lib.profile_records()]
+                _lib.profile_enable(False)
         rows.append(row)
         print(json.dumps({k_: (round(v, 4) if isinstance(v, float) else v) for k_, v in row.items()}), flush=True)
         del x, c, gy, gc, y, co_
     print(json.dumps({"summary": "nconv2d config-2 sweep", "hbm_peak_GBs": hbm, "peak_source": src,
                       "best_fwd_frac": max(r["fwd_hbm_frac"] for r in rows),
-                      "l2": "256 MB flush write between timed launches"}))
+                      "l2": "256 MB flush (%s) between timed launches" % args.flush}))
 
 
 if __name__ == "__main__":
