@@ -476,10 +476,21 @@ static void tc_build_taps(TcArgs& a, int mode, bool has_1x1) {
 
 }  // namespace nconv
 
+#include "tc_conv_x.cuh"
+
 using namespace nconv;
+
+// Co = 32 stride-1 layers run on the pixels-as-N kernel (tc_conv_x.cuh) with its own weight packing;
+// NCONV_B200_NO_TCX=1 keeps them on conv_tc_kernel (A/B measurements only; read once per process, so
+// packing and launch always agree).
+static bool tcx_on(int mode, int CO) {
+  static const bool off = getenv("NCONV_B200_NO_TCX") != nullptr;
+  return !off && mode == TC_S1 && CO == TCX_CO;
+}
 
 extern "C" size_t nconv_b200_tc_wpack_bytes(int mode, int CO, int CA, int CB, int has_1x1) {
   if (CO <= 0 || CA <= 0 || CB < 0 || mode < 0 || mode > 2) return 0;
+  if (tcx_on(mode, CO)) return (size_t)((CA + CB) / 16) * TCX_WSTAGE_BYTES;
   return (size_t)tc_nstage(mode, CA, CB) * tc_ntaps_w(mode, has_1x1 != 0) * 2 * 2 * CO * 8 * sizeof(__nv_bfloat16);
 }
 
@@ -489,6 +500,14 @@ extern "C" int nconv_b200_tc_pack_weights(int mode, const float* w, const float*
   const int lead = tc_lead(mode, CA);
   if ((!lead && CA % 16) || CB % 16) return NCONV_ERR_UNSUPPORTED;
   if (w1 && mode != TC_S2) return NCONV_ERR_BAD_ARG;
+  if (tcx_on(mode, CO)) {
+    const int nst = (CA + CB) / 16, tot = nst * 3 * 4 * 128 * 8;
+    {
+      LaunchScope ls((cudaStream_t)stream, "tc_pack_weights", 0.0, 8.0 * CO * (CA + CB) * 9);
+      tcx_pack_weights_kernel<<<(tot + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, (__nv_bfloat16*)wpack, CA + CB, nst);
+    }
+    return (int)cudaGetLastError();
+  }
   const int nstage = tc_nstage(mode, CA, CB), ntw = tc_ntaps_w(mode, w1 != nullptr);
   const int total = nstage * ntw * 2 * CO * 8;
   {
@@ -511,6 +530,24 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   if (d->yq && (mode == TC_T ? 0 : ((mode == TC_S2 ? (d->H / 2) | (d->W / 2) : (d->H | d->W)) & 1))) return NCONV_ERR_UNSUPPORTED;
   const bool has_1x1 = (mode == TC_S2) && d->has_1x1;
   const int AH = (mode == TC_S2) ? d->H / 2 : d->H, AW = (mode == TC_S2) ? d->W / 2 : d->W;
+  if (tcx_on(mode, d->CO)) {
+    const int nk = (d->CA + d->CB) / 16;
+    const TcxPlan p = tcx_plan(AH, AW, nk);
+    if (!p.ok) return NCONV_ERR_UNSUPPORTED;
+    TcxArgs a = {};
+    a.src[0] = (const __nv_bfloat16*)d->a; a.src[1] = (const __nv_bfloat16*)d->b;
+    a.c8[0] = d->CA / 8; a.c8[1] = d->CB / 8;
+    a.pairs[0] = d->CA / 16; a.pairs[1] = d->CB / 16;
+    a.slab_elems = (size_t)(d->H + 2) * (d->W + 2) * 8; a.src_pitch = d->W + 2; a.src_rows = d->H + 2;
+    a.wpack = (const __nv_bfloat16*)d->wpack; a.scale = d->scale; a.shift = d->shift;
+    a.out = (__nv_bfloat16*)d->y; a.outq = (__nv_bfloat16*)d->yq;
+    a.B = d->B; a.AH = AH; a.AW = AW;
+    a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.rows_alloc = p.rows_alloc; a.rows_ld = p.rows_ld;
+    a.tiles_x = p.tiles_x; a.tiles_y = p.tiles_y; a.ntiles = p.tiles_x * p.tiles_y * d->B;
+    a.relu = d->relu; a.stages = p.stages;
+    { static const char* dbg = getenv("NCONV_B200_TC_DEBUG"); a.dbg = dbg ? atoi(dbg) : 0; }
+    return launch_tcx(a, p, (cudaStream_t)stream);
+  }
   const int ngrp = (mode == TC_T) ? 4 : (has_1x1 ? 2 : 1);
   const int ntw = tc_ntaps_w(mode, has_1x1);
   static const bool no_stack = getenv("NCONV_B200_NO_STACK") != nullptr;      // A/B measurements only
