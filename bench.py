@@ -199,6 +199,11 @@ def roofline_of(row, peaks, sustained=True):
     tf_peak = peaks["bf16_tflops_sustained" if sustained else "bf16_tflops"]
     tc = row["kernel"].startswith("tc_conv")
     mma_factor = 3.0 if tc else 1.0
+    if tc and row["kernel"].startswith("tc_conv3x3 ") and "->32 " in row["kernel"] and not os.environ.get("NCONV_B200_NO_TCX"):
+        # pixels-as-N kernel (tc_conv_x.cuh): per kernel row and 16 input channels three M128 x N256 x K16 MMAs
+        # produce 3 taps x 32 channels x 254 pixels -> 9*2*128*256*16 issued per 2*32*16*9*254 algorithmic flops
+        # (the zero quarter of the stacked weight rows and the lo*lo product ride along)
+        mma_factor = (128.0 * 256.0) / (32.0 * 254.0)
     t_hbm = row["bytes"] / (peaks["hbm_gbs"] * 1e9)
     t_tc = mma_factor * row["flops"] / (tf_peak * 1e12) if tc else 0.0
     common = {"kernel": row["kernel"], "traffic": None, "peak_source": peaks["source"], "avg_ms": row["avg_ms"],

@@ -33,8 +33,10 @@
 #include "nconv_b200.h"
 #include "p8.cuh"
 #include "tc_ptx.cuh"
+#include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 namespace nconv {
 
@@ -109,6 +111,7 @@ struct TcArgs {
   int tiles_x, tiles_y, ntiles;
   int relu, mode, stages;
   int dbg;                      // NCONV_B200_TC_DEBUG bits (timing experiments only): 1 no stores, 2 no MMAs, 4 no loads
+  int use_tmap;                 // halo planes by TMA tensor copies (one box per staged plane) instead of per-row bulk copies
   TcTap taps[TC_MAX_TAPS];
 };
 
@@ -118,7 +121,8 @@ struct TcArgs {
 // tile from shared memory in ~32 cycles whatever N is, so at N=32 the three MMAs of a slice were bound by
 // three A reads (96 cycles); stacked they are two (64 cycles).
 template <int N, int MODE, bool STACK>
-__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcArgs a) {
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ CUtensorMap tm0,
+                                                                const __grid_constant__ CUtensorMap tm1) {
   constexpr int NACC = STACK ? 2 * N : N;                                   // accumulator columns per (group, M-tile)
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_full[TC_MAX_STAGES], s_empty[TC_MAX_STAGES], s_tfull[2], s_tempty[2];
@@ -175,6 +179,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         const uint32_t full = smem_u32(&s_full[stage]);
         const uint32_t sa = smem_base + stage * stage_bytes;
         if (a.dbg & 4) { if (pw == 0 && lane == 0) mbar_arrive(full); __syncwarp(); if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; } continue; }
+        if (a.use_tmap) {
+          // one tensor copy per staged plane: box [P px as 4P words][rows_ld rows] of plane ((n*C8+chunk)*2+part)*G+g;
+          // out-of-range rows/columns are zero-filled and count towards the transaction bytes
+          if (pw == 0) {
+            if (lane == 0) {
+              mbar_arrive_expect_tx(full, (uint32_t)(a.G * 4 * a.rows_ld) * row_bytes + b_stage_bytes);
+              bulk_g2s(sa + a_stage_bytes, a.wpack + (size_t)k * (b_stage_bytes / 2), b_stage_bytes, full);
+            }
+            __syncwarp();
+            if (lane < a.G * 4) {
+              const int j = lane & 1, part = (lane >> 1) & 1, g = lane >> 2;
+              const int pidx = ((n * a.c8[si] + (lone ? 0 : c0 + j)) * 2 + part) * a.G + g;
+              const CUtensorMap* tm = si == 0 ? &tm0 : &tm1;
+              asm volatile(
+                  "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                  ::"r"(sa + lane * a_plane_bytes), "l"(reinterpret_cast<uint64_t>(tm)), "r"(4 * x0), "r"(y0), "r"(pidx), "r"(full)
+                  : "memory");
+            }
+            __syncwarp();
+          }
+          if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
+          continue;
+        }
         if (pw == 0 && lane == 0) {
           mbar_arrive_expect_tx(full, (uint32_t)ncopy * row_bytes + b_stage_bytes);
           bulk_g2s(sa + a_stage_bytes, a.wpack + (size_t)k * (b_stage_bytes / 2), b_stage_bytes, full);
@@ -375,7 +402,8 @@ static TcPlan tc_plan_stages(int mode, int AH, int AW, int N, int ngrp, int ntw,
       const int T = (flat + 127) / 128;
       if (T > tmax) break;
       const int maxshift = hr * P + hc;
-      const int rows_alloc = (T * 128 + maxshift + P) / P;
+      int rows_alloc = (T * 128 + maxshift + P) / P;
+      while ((rows_alloc * P) % 8) ++rows_alloc;        // 128 B aligned planes (TMA tensor copies)
       const size_t smem = (size_t)stages * ((size_t)G * 4 * rows_alloc * P * 16 + (size_t)ntw * 2 * 2 * N * 16);
       if (smem > (size_t)TC_SMEM_MAX) continue;
       const int tx = (AW + Wt - 1) / Wt, ty = (AH + R - 1) / R;
@@ -398,6 +426,31 @@ static TcPlan tc_plan(int mode, int AH, int AW, int N, int ngrp, int ntw, bool s
   if (force) return atoi(force) == 3 && p3.ok ? p3 : p2;
   if (p3.ok && (!p2.ok || p3.cost <= 1.12 * p2.cost)) return p3;
   return p2;
+}
+
+typedef CUresult (*TcEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// P8 / P8Q source seen as [planes][rows][pitch px * 4 words] (32-bit words: a staged row of P pixels is ONE
+// contiguous inner extent of 16*P bytes) with box [4P][box_rows][1].
+static int tc_make_tmap(CUtensorMap* tm, const void* base, int planes, int rows, int pitch, int P, int box_rows) {
+  static TcEncodeFn enc = nullptr;
+  if (!enc) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) return NCONV_ERR_UNSUPPORTED;
+    enc = (TcEncodeFn)fn;
+  }
+  if (P * 4 > 256 || box_rows > 256) return NCONV_ERR_UNSUPPORTED;
+  const cuuint64_t gdim[3] = {(cuuint64_t)pitch * 4, (cuuint64_t)rows, (cuuint64_t)planes};
+  const cuuint64_t gstr[2] = {(cuuint64_t)pitch * 16, (cuuint64_t)rows * pitch * 16};
+  const cuuint32_t box[3] = {(cuuint32_t)P * 4, (cuuint32_t)box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : NCONV_ERR_BAD_ARG;
 }
 
 template <int N, int MODE, bool STACK = false>
@@ -423,13 +476,22 @@ static int launch_tc(const TcArgs& a, const TcPlan& p, cudaStream_t st) {
   const int CI = 16 * nk;
   // flops: real taps per output pixel (9, 9+1, or 4 of the 16 per output phase)
   const double taps_per_out = (a.mode == TC_T) ? 4.0 : (double)a.ntaps;
+  alignas(64) CUtensorMap tm[2];
+  memset(tm, 0, sizeof(tm));
+  if (a.use_tmap) {
+    for (int si = 0; si < 2; ++si) {
+      const int use = (a.src[si] && a.c8[si] > 0) ? si : 0;
+      const int rc = tc_make_tmap(&tm[si], a.src[use], a.B * a.c8[use] * 2 * a.G, a.src_rows, a.src_pitch, a.P, a.rows_ld);
+      if (rc) return rc;
+    }
+  }
   char label[64];
   snprintf(label, sizeof(label), "tc_conv%s %d->%d @%dx%d", a.mode == TC_S1 ? "3x3" : (a.mode == TC_S2 ? "3x3s2" : "T4x4s2"),
            CI, N, a.OH, a.OW);
   {
     // algorithmic bytes: fp32-equivalent activations in and out (P8 holds the same 4 B per value)
     LaunchScope ls(st, label, 2.0 * CI * N * taps_per_out * opx, 4.0 * (CI * ipx + N * opx * (a.outq ? 2.0 : 1.0)));
-    kern<<<grid, TC_THREADS, p.smem, st>>>(a);
+    kern<<<grid, TC_THREADS, p.smem, st>>>(a, tm[0], tm[1]);
   }
   return (int)cudaGetLastError();
 }
@@ -573,6 +635,15 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   a.tiles_x = p.tiles_x; a.tiles_y = p.tiles_y; a.ntiles = p.tiles_x * p.tiles_y * d->B;
   a.relu = d->relu; a.mode = mode; a.stages = p.stages;
   { static const char* dbg = getenv("NCONV_B200_TC_DEBUG"); a.dbg = dbg ? atoi(dbg) : 0; }
+  {
+    // Tensor-map loads pay where a stage is many short rows: the stride-2 layers stage 16 planes of 17-pixel rows
+    // (32->64 s2 @240x320: 0.71 -> 0.50 ms).  The stride-1 / transposed layers measured 0-9 % slower with them
+    // (one box completes as a whole; row copies trickle in), so they keep per-row bulk copies.
+    // NCONV_B200_TC_TMAP=0/1 forces either path (A/B measurements only).
+    static const char* force = getenv("NCONV_B200_TC_TMAP");
+    a.use_tmap = force ? (atoi(force) != 0) : (mode == TC_S2);
+    if (p.P * 4 > 256) a.use_tmap = 0;
+  }
   tc_build_taps(a, mode, has_1x1);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == TC_S1) {

@@ -360,30 +360,6 @@ static TcxPlan tcx_plan(int AH, int AW, int nk) {
   return best;
 }
 
-typedef CUresult (*TcxEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-// P8 source [planes = B*C8*2][H+2][(W+2)*8 bf16 = (W+2)*4 words] as a 3-D tensor map with box [4P][rows][1]
-static int tcx_make_tmap(CUtensorMap* tm, const void* base, int planes, int Hp, int Wp, int P, int rows) {
-  static TcxEncodeFn enc = nullptr;
-  if (!enc) {
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) return NCONV_ERR_UNSUPPORTED;
-    enc = (TcxEncodeFn)fn;
-  }
-  const cuuint64_t gdim[3] = {(cuuint64_t)Wp * 4, (cuuint64_t)Hp, (cuuint64_t)planes};
-  const cuuint64_t gstr[2] = {(cuuint64_t)Wp * 16, (cuuint64_t)Hp * Wp * 16};
-  const cuuint32_t box[3] = {(cuuint32_t)P * 4, (cuuint32_t)rows, 1};
-  const cuuint32_t estr[3] = {1, 1, 1};
-  if (P * 4 > 256) return NCONV_ERR_UNSUPPORTED;
-  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<void*>(base), gdim, gstr, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : NCONV_ERR_BAD_ARG;
-}
-
 static int launch_tcx(const TcxArgs& a, const TcxPlan& p, cudaStream_t st) {
   static bool attr_done[NCONV_MAX_DEVICES] = {};
   static int sm_count[NCONV_MAX_DEVICES] = {};
@@ -405,7 +381,7 @@ static int launch_tcx(const TcxArgs& a, const TcxPlan& p, cudaStream_t st) {
   alignas(64) CUtensorMap tm[2];
   for (int si = 0; si < 2; ++si) {
     const int use = (a.src[si] && a.c8[si] > 0) ? si : 0;
-    const int rc = tcx_make_tmap(&tm[si], a.src[use], a.B * a.c8[use] * 2, a.AH + 2, a.AW + 2, a.P, a.rows_ld);
+    const int rc = tc_make_tmap(&tm[si], a.src[use], a.B * a.c8[use] * 2, a.AH + 2, a.AW + 2, a.P, a.rows_ld);
     if (rc) return rc;
   }
   char label[64];
