@@ -403,7 +403,7 @@ static TcPlan tc_plan_stages(int mode, int AH, int AW, int N, int ngrp, int ntw,
       if (T > tmax) break;
       const int maxshift = hr * P + hc;
       int rows_alloc = (T * 128 + maxshift + P) / P;
-      while ((rows_alloc * P) % 8) ++rows_alloc;        // 128 B aligned planes (TMA tensor copies)
+      if (mode == TC_S2) while ((rows_alloc * P) % 8) ++rows_alloc;   // 128 B aligned planes (TMA tensor copies)
       const size_t smem = (size_t)stages * ((size_t)G * 4 * rows_alloc * P * 16 + (size_t)ntw * 2 * 2 * N * 16);
       if (smem > (size_t)TC_SMEM_MAX) continue;
       const int tx = (AW + Wt - 1) / Wt, ty = (AH + R - 1) / R;
@@ -642,7 +642,7 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
     // NCONV_B200_TC_TMAP=0/1 forces either path (A/B measurements only).
     static const char* force = getenv("NCONV_B200_TC_TMAP");
     a.use_tmap = force ? (atoi(force) != 0) : (mode == TC_S2);
-    if (p.P * 4 > 256) a.use_tmap = 0;
+    if (p.P * 4 > 256 || (p.rows_alloc * p.P) % 8) a.use_tmap = 0;
   }
   tc_build_taps(a, mode, has_1x1);
   cudaStream_t st = (cudaStream_t)stream;
