@@ -321,7 +321,7 @@ def run_b200(args):
         "clocks": clocks,
         "roofline": roof,
         "nconv_roofline": [roofline_of(r, peaks) for r in nconv_rows[:3]],
-        "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()} for r in rows[:12]],
+        "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()} for r in rows[:40]],
     }
     if world == 1 and not args.no_cpu_baseline:
         times, nfr, cores = time_cpu_oracle(1, min_seconds=10.0, max_reps=8, warmup=1)

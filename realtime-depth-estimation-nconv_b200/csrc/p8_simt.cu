@@ -22,6 +22,7 @@ struct SmallArgs {
 };
 
 constexpr int SM_THREADS = 128;
+constexpr int SM_ROWS = 8;        // rows per CTA of small_to_p8
 
 // One thread = PXT pixels (128 apart along x, so every access is coalesced) x all CO channels.
 template <int CI, int CO, int PXT>
@@ -43,8 +44,13 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
   }
   __syncthreads();
 
-  const int n = blockIdx.z, y = blockIdx.y;
+  const int n = blockIdx.z;
   const int xb = blockIdx.x * (SM_THREADS * PXT) + tid;
+  const P8Geom g = P8Geom::make(a.B, CO, a.H, a.W);
+  const P8QGeom qg = P8QGeom::make(a.B, CO, a.H, a.W);
+  // a CTA walks SM_ROWS rows of its column block: the weight staging above is paid once per SM_ROWS rows
+#pragma unroll 1
+  for (int y = blockIdx.y * SM_ROWS; y < min((int)(blockIdx.y + 1) * SM_ROWS, a.H); ++y) {
   u64 acc2[PXT][CO / 2];          // packed pairs of output channels (FFMA2: weight pair x broadcast input)
 #pragma unroll
   for (int p = 0; p < PXT; ++p)
@@ -86,8 +92,6 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
     }
   }
 
-  const P8Geom g = P8Geom::make(a.B, CO, a.H, a.W);
-  const P8QGeom qg = P8QGeom::make(a.B, CO, a.H, a.W);
 #pragma unroll
   for (int p = 0; p < PXT; ++p) {
     const int x = xb + p * SM_THREADS;
@@ -115,6 +119,7 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
         *reinterpret_cast<uint4*>(a.yq + qg.slab(n, ch, 1) + qg.pixel(y, x)) = lo;
       }
     }
+  }
   }
 }
 
@@ -195,7 +200,7 @@ __global__ void __launch_bounds__(HD_THREADS) head_p8_kernel(const HeadArgs a) {
 
 template <int CI, int CO, int PXT>
 static int launch_small(const SmallArgs& a, cudaStream_t st) {
-  dim3 grid(ceil_div(a.W, SM_THREADS * PXT), a.H, a.B);
+  dim3 grid(ceil_div(a.W, SM_THREADS * PXT), ceil_div(a.H, SM_ROWS), a.B);
   char label[64];
   snprintf(label, sizeof(label), "small_to_p8 %d->%d @%dx%d", CI, CO, a.H, a.W);
   const double px = (double)a.B * a.H * a.W;
