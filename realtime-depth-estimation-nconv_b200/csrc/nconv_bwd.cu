@@ -12,6 +12,7 @@
 // correlation of nconv_tiled.cuh run on (gN,gD) with flipped weights; (3) weight gradient as a
 // persistent tiled reduction with per-CTA partials and a fixed-order (deterministic) final sum.
 #include "nconv_tiled.cuh"
+#include "nconv_bwd_stream.cuh"
 #include <cstdio>
 
 namespace nconv {
@@ -402,6 +403,7 @@ extern "C" size_t nconv_b200_nconv2d_bwd_workspace_bytes(int B, int Ci, int Co, 
   size_t fl = align_up((size_t)Co, 64);
   int K = kh > kw ? kh : kw;
   fl += wgrad_partial_floats(Ci, Co, K) + 64;
+  if (Co == 2 && Ci <= 2 && K == 3) { size_t bs = (size_t)BS_MAX_UNITS * (Co * Ci * 9 + 2 * Co) + 64; if (bs > fl) fl = bs; }
   return fl * sizeof(float);
 }
 
@@ -463,6 +465,21 @@ extern "C" int nconv_b200_nconv2d_bwd(const float* gy, const float* gcout, const
   cudaStream_t st = (cudaStream_t)stream;
   float* wsum = (float*)workspace;
   float* part = wsum + align_up((size_t)Co, 64);
+
+  // HBM-bound small-channel shapes (BASELINE.json config 2): one fused streaming pass (nconv_bwd_stream.cuh).
+  // NCONV_B200_NO_BWD_STREAM=1 keeps them on the tiled kernels (A/B measurements only).
+  {
+    static const bool no_stream = getenv("NCONV_B200_NO_BWD_STREAM") != nullptr;
+    const bool vec = (W % 4 == 0) && aligned16(gy) && aligned16(y) && aligned16(cout) && (!gcout || aligned16(gcout)) &&
+                     aligned16(x) && aligned16(c) && (!gx || aligned16(gx)) && (!gc || aligned16(gc));
+    if (!no_stream && gx && gc && gw && vec && kh == 3 && kw == 3 && ph == 1 && pw == 1 && Co == 2 && (Ci == 1 || Ci == 2)) {
+      BsArgs a = {};
+      a.gy = gy; a.gco = gcout; a.y = y; a.co = cout; a.x = x; a.c = c; a.w = w; a.bias = bias;
+      a.gx = gx; a.gc = gc; a.partial = (float*)workspace; a.B = B; a.H = H; a.W = W; a.eps = eps;
+      const int rc = (Ci == 1) ? launch_bwd_stream<1, 2>(a, gw, gb, st) : launch_bwd_stream<2, 2>(a, gw, gb, st);
+      if (rc != NCONV_ERR_UNSUPPORTED) return rc;
+    }
+  }
 
   {
     LaunchScope ls(st, "wsum", 0.0, 4.0 * Co * Ci * kh * kw);

@@ -77,6 +77,35 @@ def test_nconv2d_stream_kernel_vs_oracle(K, cfg, shape):
     assert O.max_rel_err(cout, c_ref) <= REL_TOL
 
 
+@pytest.mark.parametrize("cfg", [(1, 2, 3), (2, 2, 3)])
+@pytest.mark.parametrize("shape", [(2, 37, 132), (1, 9, 128), (3, 50, 300), (2, 480, 640)])
+@pytest.mark.parametrize("with_gc", [True, False])
+def test_nconv2d_bwd_stream_kernel_vs_oracle_autograd(K, cfg, shape, with_gc):
+    """The fused streaming backward (csrc/nconv_bwd_stream.cuh) against autograd through the CPU oracle in
+    fp64: partial strips, segments shorter than RS, image borders, exact-zero confidence, absent gcout."""
+    ci, co, k = cfg
+    B, H, W = shape
+    g = torch.Generator().manual_seed(B * 1000 + H + ci * 7 + k + 17)
+    x = torch.rand(B, ci, H, W, generator=g) * 10
+    c = torch.rand(B, ci, H, W, generator=g) * (torch.rand(B, ci, H, W, generator=g) < 0.5)
+    w = O.softplus_beta10(torch.rand(co, ci, k, k, generator=g))
+    b = torch.full((co,), 0.01)
+    gy = torch.randn(B, co, H, W, generator=g)
+    gc = torch.randn(B, co, H, W, generator=g)
+    xd, cd, wd, bd = (t.double().requires_grad_(True) for t in (x, c, w, b))
+    y_ref, c_ref = O.nconv2d(xd, cd, wd, bd, (1, 1))
+    loss = (y_ref * gy.double()).sum() + ((c_ref * gc.double()).sum() if with_gc else 0.0)
+    loss.backward()
+    xg, cg, wg, bg = (t.to(dev()).requires_grad_(True) for t in (x, c, w, b))
+    y, cout = K.nconv2d(xg, cg, wg, bg, 1, 1, 1e-7)
+    l2 = (y * gy.to(dev())).sum()
+    if with_gc:
+        l2 = l2 + (cout * gc.to(dev())).sum()
+    l2.backward()
+    for name, t, r in (("gx", xg.grad, xd.grad), ("gc", cg.grad, cd.grad), ("gw", wg.grad, wd.grad), ("gb", bg.grad, bd.grad)):
+        assert grad_err(t, r.float()) <= GRAD_TOL, name
+
+
 def test_nconv2d_module_hook_semantics(K):
     """KA4: training forward overwrites the stored weight with softplus(w, beta=10) in place;
     eval leaves it alone; the gradient is straight-through (w.r.t. the transformed weight)."""
