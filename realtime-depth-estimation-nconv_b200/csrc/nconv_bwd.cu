@@ -75,11 +75,20 @@ __global__ void __launch_bounds__(WG_THREADS, 2) nconv_wgrad_tiled(const WGradAr
 
   for (int i = tid; i < C::PART_FLOATS; i += WG_THREADS) s_part[i] = 0.f;
 
-  float acc[CO_T][K];
+  // With an even CO_T the FMA stream is packed (FFMA2): gN / gD of a channel PAIR sit interleaved in shared
+  // memory, so one 64-bit operand x one broadcast activation updates the taps of two output channels.
+  constexpr bool PACK = (CO_T % 2 == 0);
+  constexpr int CO_P = PACK ? CO_T / 2 : 1;
+  float acc[PACK ? 1 : CO_T][K];
+  u64 acc2[CO_P][K];
 #pragma unroll
-  for (int o = 0; o < CO_T; ++o)
+  for (int o = 0; o < (PACK ? 1 : CO_T); ++o)
 #pragma unroll
     for (int v = 0; v < K; ++v) acc[o][v] = 0.f;
+#pragma unroll
+  for (int o = 0; o < CO_P; ++o)
+#pragma unroll
+    for (int v = 0; v < K; ++v) acc2[o][v] = 0ull;
 
   const int tiles_x = ceil_div(a.WO, WG_TW), tiles_y = ceil_div(a.HO, WG_TH);
   const int ntiles = a.B * tiles_y * tiles_x;
@@ -91,14 +100,12 @@ __global__ void __launch_bounds__(WG_THREADS, 2) nconv_wgrad_tiled(const WGradAr
     const int ox0 = txi * WG_TW, oy0 = tyi * WG_TH;
     __syncthreads();
     // ---- stage gN, gD for CO_T channels (and the per-channel sums for gb and the gcout term)
-    for (int idx = tid; idx < CO_T * WG_TH * (WG_TW / 4); idx += WG_THREADS) {
-      int j = idx % (WG_TW / 4);
-      int r = (idx / (WG_TW / 4)) % WG_TH;
-      int o = idx / ((WG_TW / 4) * WG_TH);     // warp-uniform: 128 slots per channel
-      int oo = oc * CO_T + o;
-      int gy_ = oy0 + r, gx_ = ox0 + 4 * j;
-      float n4[4] = {0.f, 0.f, 0.f, 0.f}, d4[4] = {0.f, 0.f, 0.f, 0.f};
-      float sgy = 0.f, sT = 0.f;
+    // one slot = 4 pixels of one channel (scalar path) or of a channel PAIR (packed path: the pair of a pixel
+    // is written as one 64-bit word, two conflict-free 128-bit stores per slot)
+    auto load_channel = [&](int oo, int gy_, int gx_, float* n4, float* d4, float& sgy, float& sT) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { n4[e] = 0.f; d4[e] = 0.f; }
+      sgy = 0.f; sT = 0.f;
       if (gy_ < a.HO) {
         size_t base = ((size_t)(b * CO + oo) * a.HO + gy_) * a.WO;
         float g1[4] = {0.f, 0.f, 0.f, 0.f}, g2[4] = {0.f, 0.f, 0.f, 0.f}, yv[4] = {0.f, 0.f, 0.f, 0.f},
@@ -132,12 +139,35 @@ __global__ void __launch_bounds__(WG_THREADS, 2) nconv_wgrad_tiled(const WGradAr
           }
         }
       }
-      int so = (o * WG_TH + r) * WG_TW + 4 * j;
-      *reinterpret_cast<float4*>(s_gn + so) = make_float4(n4[0], n4[1], n4[2], n4[3]);
-      *reinterpret_cast<float4*>(s_gd + so) = make_float4(d4[0], d4[1], d4[2], d4[3]);
+    };
+    constexpr int SLOT_CH = PACK ? 2 : 1;
+    for (int idx = tid; idx < (CO_T / SLOT_CH) * WG_TH * (WG_TW / 4); idx += WG_THREADS) {
+      int j = idx % (WG_TW / 4);
+      int r = (idx / (WG_TW / 4)) % WG_TH;
+      int os = idx / ((WG_TW / 4) * WG_TH);    // warp-uniform: 128 slots per channel (pair)
+      const int gy_ = oy0 + r, gx_ = ox0 + 4 * j;
+      float n4[SLOT_CH][4], d4[SLOT_CH][4], sgy[SLOT_CH], sT[SLOT_CH];
+#pragma unroll
+      for (int h = 0; h < SLOT_CH; ++h) load_channel(oc * CO_T + os * SLOT_CH + h, gy_, gx_, n4[h], d4[h], sgy[h], sT[h]);
+      if constexpr (PACK) {
+        float* pn = s_gn + ((os * WG_TH + r) * WG_TW + 4 * j) * 2;
+        float* pd = s_gd + ((os * WG_TH + r) * WG_TW + 4 * j) * 2;
+        *reinterpret_cast<float4*>(pn) = make_float4(n4[0][0], n4[1][0], n4[0][1], n4[1][1]);
+        *reinterpret_cast<float4*>(pn + 4) = make_float4(n4[0][2], n4[1][2], n4[0][3], n4[1][3]);
+        *reinterpret_cast<float4*>(pd) = make_float4(d4[0][0], d4[1][0], d4[0][1], d4[1][1]);
+        *reinterpret_cast<float4*>(pd + 4) = make_float4(d4[0][2], d4[1][2], d4[0][3], d4[1][3]);
+      } else {
+        int so = (os * WG_TH + r) * WG_TW + 4 * j;
+        *reinterpret_cast<float4*>(s_gn + so) = make_float4(n4[0][0], n4[0][1], n4[0][2], n4[0][3]);
+        *reinterpret_cast<float4*>(s_gd + so) = make_float4(d4[0][0], d4[0][1], d4[0][2], d4[0][3]);
+      }
       if (ic == 0) {
-        sgy = warp_sum(sgy); sT = warp_sum(sT);
-        if (lane == 0) { s_part[(warp * 2 + 0) * 8 + o] += sgy; s_part[(warp * 2 + 1) * 8 + o] += sT; }
+#pragma unroll
+        for (int h = 0; h < SLOT_CH; ++h) {
+          const float a1 = warp_sum(sgy[h]), a2 = warp_sum(sT[h]);
+          const int o = os * SLOT_CH + h;
+          if (lane == 0) { s_part[(warp * 2 + 0) * 8 + o] += a1; s_part[(warp * 2 + 1) * 8 + o] += a2; }
+        }
       }
     }
     // ---- stage x*c and c halo tiles for CCH input channels
@@ -172,18 +202,35 @@ __global__ void __launch_bounds__(WG_THREADS, 2) nconv_wgrad_tiled(const WGradAr
         const float* pc = s_c + (pi * RH + r + pu) * SW + 4 * j;
 #pragma unroll
         for (int q = 0; q < 3; ++q) { VecLoad<4>::ld(xr + 4 * q, px + 4 * q); VecLoad<4>::ld(cr + 4 * q, pc + 4 * q); }
+        if constexpr (PACK) {
 #pragma unroll
-        for (int o = 0; o < CO_T; ++o) {
-          float gn[4], gd[4];
-          VecLoad<4>::ld(gn, s_gn + (o * WG_TH + r) * WG_TW + 4 * j);
-          VecLoad<4>::ld(gd, s_gd + (o * WG_TH + r) * WG_TW + 4 * j);
+          for (int o = 0; o < CO_P; ++o) {
+            const ulonglong2* pn = reinterpret_cast<const ulonglong2*>(s_gn + ((o * WG_TH + r) * WG_TW + 4 * j) * 2);
+            const ulonglong2* pd = reinterpret_cast<const ulonglong2*>(s_gd + ((o * WG_TH + r) * WG_TW + 4 * j) * 2);
+            const ulonglong2 n01 = pn[0], n23 = pn[1], d01 = pd[0], d23 = pd[1];
+            const u64 gn2[4] = {n01.x, n01.y, n23.x, n23.y}, gd2[4] = {d01.x, d01.y, d23.x, d23.y};
 #pragma unroll
-          for (int v = 0; v < K; ++v)
+            for (int v = 0; v < K; ++v)
 #pragma unroll
-            for (int p = 0; p < 4; ++p) {
-              acc[o][v] = fmaf(gn[p], xr[OFF + p + v], acc[o][v]);
-              acc[o][v] = fmaf(gd[p], cr[OFF + p + v], acc[o][v]);
-            }
+              for (int p = 0; p < 4; ++p) {
+                ffma2(acc2[o][v], gn2[p], xr[OFF + p + v]);
+                ffma2(acc2[o][v], gd2[p], cr[OFF + p + v]);
+              }
+          }
+        } else {
+#pragma unroll
+          for (int o = 0; o < CO_T; ++o) {
+            float gn[4], gd[4];
+            VecLoad<4>::ld(gn, s_gn + (o * WG_TH + r) * WG_TW + 4 * j);
+            VecLoad<4>::ld(gd, s_gd + (o * WG_TH + r) * WG_TW + 4 * j);
+#pragma unroll
+            for (int v = 0; v < K; ++v)
+#pragma unroll
+              for (int p = 0; p < 4; ++p) {
+                acc[o][v] = fmaf(gn[p], xr[OFF + p + v], acc[o][v]);
+                acc[o][v] = fmaf(gd[p], cr[OFF + p + v], acc[o][v]);
+              }
+          }
         }
       }
     }
@@ -197,7 +244,10 @@ __global__ void __launch_bounds__(WG_THREADS, 2) nconv_wgrad_tiled(const WGradAr
 #pragma unroll
       for (int o = 0; o < CO_T; ++o)
 #pragma unroll
-        for (int v = 0; v < K; ++v) s_red[(pair * CO_T + o) * K + v] += acc[o][v];
+        for (int v = 0; v < K; ++v) {
+          const float av = PACK ? ((o & 1) ? hi32f(acc2[PACK ? o >> 1 : 0][v]) : lo32f(acc2[PACK ? o >> 1 : 0][v])) : acc[PACK ? 0 : o][v];
+          s_red[(pair * CO_T + o) * K + v] += av;
+        }
     }
     __syncthreads();
   }
