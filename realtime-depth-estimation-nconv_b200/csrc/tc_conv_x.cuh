@@ -19,10 +19,12 @@
 //   8-channel chunk; a third MMA per 16 channels is W_lo * x_hi.  Per kernel row and 16 input
 //   channels: 3 MMAs of 128x256x16 = 384 cycles for 256 pixels, against 3 taps x 2 MMAs x ~80
 //   cycles x 2 (128-pixel tiles) = 960 cycles in the pixel-M kernel.
-// * All packed weights of the layer stay resident in shared memory (<= 144 KB for 64 input
-//   channels); only pixel stages stream through the ring.
+// * All packed weights of the layer stay resident in shared memory (24 KB per 16 input channels: the
+//   [W_hi ; W_hi] tiles alias their two K-halves with LBO = 0); only pixel stages stream through the ring,
+//   one TMA tensor copy per staged plane.
 //
-// Warp roles: warps 0, 6, 7 producers (bulk row copies), warp 1 MMA issuer, warps 2-5 epilogue set 0 and,
+// Warp roles: warp 0 producer (weights once, then 4 tensor copies per K-stage), warp 1 MMA issuer, warps 6-7
+// idle (they keep the epilogue warps' ids aligned with the TMEM lane quarters), warps 2-5 epilogue set 0 and,
 // with ESETS = 2 (layers whose resident weights leave room for a second staging ring), warps 8-11 epilogue
 // set 1: set h handles accumulator columns [128h, 128h+128).  A warp may only read the TMEM lane quarter
 // (warp id % 4).  TMEM: two 256-column accumulators (tile i's epilogue overlaps tile i+1's MMAs).
