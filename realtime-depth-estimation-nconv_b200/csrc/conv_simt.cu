@@ -64,11 +64,21 @@ __global__ void __launch_bounds__(CT_THREADS, 2) conv_fwd_tiled(const ConvArgs a
   const int ox0 = blockIdx.x * CT_TW, oy0 = blockIdx.y * TH;
   const int CI = a.CA + a.CB;
 
-  float acc[CO_TT][CT_PX];
+  // Even channel counts run the FMA stream packed (FFMA2, common.cuh): the weight PAIR of two adjacent output
+  // channels is a 64-bit half of the broadcast LDS.128, the activation the scalar-broadcast operand; same
+  // products in the same order as the scalar loop, two per issue slot.
+  constexpr bool PACK = (CO_TT % 4 == 0);
+  constexpr int CO_P = PACK ? CO_TT / 2 : 1;
+  float acc[PACK ? 1 : CO_TT][CT_PX];
+  u64 acc2[CO_P][CT_PX];
 #pragma unroll
-  for (int o = 0; o < CO_TT; ++o)
+  for (int o = 0; o < (PACK ? 1 : CO_TT); ++o)
 #pragma unroll
     for (int p = 0; p < CT_PX; ++p) acc[o][p] = 0.f;
+#pragma unroll
+  for (int o = 0; o < CO_P; ++o)
+#pragma unroll
+    for (int p = 0; p < CT_PX; ++p) acc2[o][p] = 0ull;
 
   const int gx0a = ox0 * S - PAD - OFF;
   const int gy0 = oy0 * S - PAD;
@@ -124,6 +134,17 @@ __global__ void __launch_bounds__(CT_THREADS, 2) conv_fwd_tiled(const ConvArgs a
         }
 #pragma unroll
         for (int v = 0; v < K; ++v) {
+          if constexpr (PACK) {
+#pragma unroll
+            for (int o = 0; o < CO_P; o += 2) {
+              const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(wrow + (u * K + v) * CO_T + 2 * o);
+#pragma unroll
+              for (int p = 0; p < CT_PX; ++p) {
+                ffma2(acc2[o][p], t.x, xr[OFF + p * S + v]);
+                ffma2(acc2[o + 1][p], t.y, xr[OFF + p * S + v]);
+              }
+            }
+          } else {
           float wv[CO_TT];
 #pragma unroll
           for (int o = 0; o < CO_TT; o += WV) {
@@ -139,6 +160,7 @@ __global__ void __launch_bounds__(CT_THREADS, 2) conv_fwd_tiled(const ConvArgs a
 #pragma unroll
             for (int p = 0; p < CT_PX; ++p)
               acc[o][p] = fmaf(wv[o], xr[OFF + p * S + v], acc[o][p]);
+          }
         }
       }
     }
@@ -155,7 +177,8 @@ __global__ void __launch_bounds__(CT_THREADS, 2) conv_fwd_tiled(const ConvArgs a
     float r[CT_PX];
 #pragma unroll
     for (int p = 0; p < CT_PX; ++p) {
-      float v = fmaf(acc[o][p], sc, sh);
+      const float av = PACK ? ((o & 1) ? hi32f(acc2[PACK ? o >> 1 : 0][p]) : lo32f(acc2[PACK ? o >> 1 : 0][p])) : acc[PACK ? 0 : o][p];
+      float v = fmaf(av, sc, sh);
       if (a.relu) v = fmaxf(v, 0.f);
       r[p] = v;
     }

@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
   constexpr int PER = 4 * K * K;
   constexpr int TILE = CO_B * GP + WG_CIB * K * XCP, RED = TMG * WG_CIB * PER;
   static_assert(NSUB >= 1 && PXT * NSUB == WG_CH, "bad wgrad tiling");
-  __shared__ float s_all[TILE > RED ? TILE : RED];
+  __shared__ __align__(16) float s_all[TILE > RED ? TILE : RED];
   float* s_g = s_all;
   float* s_x = s_all + CO_B * GP;
 
@@ -335,11 +335,18 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
   // Two-level accumulation: `acc` sums one chunk (PXT products), `tot` sums the chunks.  The rounding
   // error then grows with sqrt(PXT) + sqrt(chunks per CTA) instead of sqrt(all pixels of the CTA): these
   // sums run over up to 10^5 products of un-normalised activations with heavy cancellation.
+  // The chunk sums run packed (FFMA2, common.cuh): the gradients of an output-channel PAIR are one 64-bit word
+  // in shared memory, the activation is the scalar-broadcast operand.
   float acc[4][K * K], tot[4][K * K];
+  u64 acc2[2][K * K];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
     for (int t = 0; t < K * K; ++t) { acc[j][t] = 0.f; tot[j][t] = 0.f; }
+#pragma unroll
+  for (int j = 0; j < 2; ++j)
+#pragma unroll
+    for (int t = 0; t < K * K; ++t) acc2[j][t] = 0ull;
 
   for (long long ch = blockIdx.x; ch < a.chunks; ch += a.nsplit) {
     const int cx = (int)(ch % a.chunks_x);
@@ -351,7 +358,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
       const int px = idx % WG_CH, co = idx / WG_CH;
       float v = 0.f;
       if (co0 + co < a.CO && ox0 + px < a.WO) v = __ldg(a.g + (((size_t)b * a.CO + co0 + co) * a.HO + oy) * a.WO + ox0 + px);
-      s_g[co * GP + px] = v;
+      s_g[(co >> 1) * (2 * GP) + 2 * px + (co & 1)] = v;          // [co/2][px][co&1]
     }
     for (int idx = tid; idx < WG_CIB * K * XC; idx += 256) {
       const int xc = idx % XC, u = (idx / XC) % K, cc = idx / (XC * K);
@@ -362,7 +369,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
       s_x[(cc * K + u) * XCP + xc] = v;
     }
     __syncthreads();
-    const float* gx = s_g + (4 * tm) * GP + sub * PXT;
+    const float* gx = s_g + (2 * tm) * (2 * GP) + 2 * sub * PXT;     // pairs (4tm, 4tm+1), (4tm+2, 4tm+3)
     const float* xx = s_x + ci_l * K * XCP + sub * PXT * S;
     float win[K][K];
 #pragma unroll
@@ -378,20 +385,23 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
 #pragma unroll
         for (int v = (K - S > 0 ? K - S : 0); v < K; ++v) win[u][v] = xx[u * XCP + p * S + v];
       }
-      float gv[4];
+      u64 gv2[2];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) gv[j] = gx[j * GP + p];
+      for (int j = 0; j < 2; ++j) gv2[j] = *reinterpret_cast<const u64*>(gx + j * (2 * GP) + 2 * p);
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
+      for (int j = 0; j < 2; ++j)
 #pragma unroll
         for (int u = 0; u < K; ++u)
 #pragma unroll
-          for (int v = 0; v < K; ++v) acc[j][u * K + v] = fmaf(gv[j], win[u][v], acc[j][u * K + v]);
+          for (int v = 0; v < K; ++v) ffma2(acc2[j][u * K + v], gv2[j], win[u][v]);
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 2; ++j)
 #pragma unroll
-      for (int t = 0; t < K * K; ++t) { tot[j][t] += acc[j][t]; acc[j][t] = 0.f; }
+      for (int t = 0; t < K * K; ++t) {
+        tot[2 * j][t] += lo32f(acc2[j][t]); tot[2 * j + 1][t] += hi32f(acc2[j][t]);
+        acc2[j][t] = 0ull;
+      }
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j)
