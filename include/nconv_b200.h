@@ -256,6 +256,42 @@ int nconv_b200_conv_small_p8(const float* x, const float* w, const float* w1, co
 int nconv_b200_head_p8(const void* f, const float* w, const float* residual, float* y, void* y8, int B,
                        int C, int H, int W, void* stream);
 
+/* ---- callers either side of the training path ------------------------------
+ * One scale of utils.py:63-71 (calculate_loss_multi_resolution) over utils.py:138-151
+ * (calculate_loss, use_gradient_loss = False):
+ *   up = F.interpolate(d, size=(H,W), mode='bilinear', align_corners=False)        d: [N,1,h,w]
+ *   loss (+)= weight * mean_{N,H,W}( (up.masked_fill(gt == 0, 0) - gt)^2 )         gt: [N,1,H,W]
+ * h == H, w == W is the plain calculate_loss. ws: masked_mse_ws_bytes() of scratch for either
+ * call; accumulate != 0 adds to *loss (the mean over scales is weight = 1/nscales).
+ * bwd: gd[N,1,h,w] = gloss[0] * dloss/dd  (overwrites gd; deterministic gather, no atomics; for
+ * h != H the masked residual at full resolution passes through ws). */
+size_t nconv_b200_masked_mse_ws_bytes(int N, int h, int w, int H, int W);
+int nconv_b200_masked_mse_bilinear_fwd(const float* d, const float* gt, float* loss, void* ws, size_t ws_bytes,
+                                       int N, int h, int w, int H, int W, float weight, int accumulate,
+                                       void* stream);
+int nconv_b200_masked_mse_bilinear_bwd(const float* d, const float* gt, const float* gloss, float* gd, void* ws,
+                                       size_t ws_bytes, int N, int h, int w, int H, int W, float weight,
+                                       void* stream);
+
+/* The same with use_gradient_loss = True (utils.py:142-147 over :95-136, the setting of train_step1.py:20):
+ *   rec = up.masked_fill(gt == 0, 0)
+ *   loss (+)= weight * (0.8*sqrt(mse(rec, gt)) + 0.2*(mean|sobel_x(gt-rec)| + mean|sobel_y(gt-rec)|))
+ * (3x3 cross-correlations with zero padding 1).  stats: 3 doubles on the device written by fwd (the three
+ * sums) and read by bwd.  ws: sobel_loss_ws_bytes() of scratch for either call.  N <= 65535. */
+size_t nconv_b200_sobel_loss_ws_bytes(int N, int h, int w, int H, int W);
+int nconv_b200_sobel_loss_fwd(const float* d, const float* gt, float* loss, double* stats, void* ws,
+                              size_t ws_bytes, int N, int h, int w, int H, int W, float weight, int accumulate,
+                              void* stream);
+int nconv_b200_sobel_loss_bwd(const float* d, const float* gt, const float* gloss, const double* stats,
+                              float* gd, void* ws, size_t ws_bytes, int N, int h, int w, int H, int W,
+                              float weight, void* stream);
+
+/* torch.optim.AdamW (utils.py:53-55 get_optimizer; amsgrad off) on flat fp32 buffers of n elements:
+ *   p *= 1 - lr*wd;  m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;
+ *   p -= lr/(1-b1^step) * m / (sqrt(v)/sqrt(1-b2^step) + eps)                      step >= 1 */
+int nconv_b200_adamw_step(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1,
+                          float beta2, float eps, float weight_decay, int step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,7 +21,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "realtime-depth-estimation-nconv_b200"))
 from oracle import ref_shim  # noqa: E402
 from nconv_b200.synthetic import (nconv_layer_case, NCONV_LAYER_CASES, sparse_depth_nyu,  # noqa: E402
-                                  sparse_depth_kitti, setp2_inputs, randomise_bn_stats)
+                                  sparse_depth_kitti, setp2_inputs, randomise_bn_stats, loss_case)
 
 OUT = os.path.join(ROOT, "tests", "golden")
 
@@ -255,6 +255,61 @@ def gen_setp2_train(r1, r2):
     np.savez_compressed(os.path.join(OUT, "setp2_train.npz"), **out)
 
 
+LOSS_CASES = [(2, 11, (1, 2, 4, 8)), (1, 12, (1,)), (3, 13, (2, 4)), (2, 14, (1, 3, 5, 16))]
+ADAMW_SHAPES = [(7,), (3, 5), (2, 3, 3, 3), (1,), (129,)]
+
+
+def gen_loss_optim():
+    """utils.py:63-71 / :138-151 (loss value + gradients, fp32 and fp64) and utils.py:53-55 (AdamW, 4 steps)
+    through the unmodified reference functions."""
+    u = ref_shim.load_reference_utils()
+    out = {}
+    for ci, (B, seed, scales) in enumerate(LOSS_CASES):
+        for tag, dt in (("", torch.float32), ("64", torch.float64)):
+            depths, gt = loss_case(B, seed, scales=scales)
+            depths = [d.to(dt).requires_grad_(True) for d in depths]
+            loss = u.calculate_loss_multi_resolution(depths, gt.to(dt), False)
+            loss.backward()
+            out["mr%d_loss%s" % (ci, tag)] = np.array(float(loss.detach()), dtype=np.float64)
+            for k, d in enumerate(depths):
+                out["mr%d_g%s_%d" % (ci, tag, k)] = subsample(_np(d.grad[0]))
+                assert float(d.grad[1:].abs().sum()) == 0.0     # utils.py:69: sample 0 only
+        # the plain single-resolution loss on the whole batch (utils.py:138-151)
+        depths, gt = loss_case(B, seed, scales=(1,))
+        d = depths[0].requires_grad_(True)
+        loss = u.calculate_loss(d, gt, False); loss.backward()
+        out["cl%d_loss" % ci] = np.array(float(loss.detach()), dtype=np.float64)
+        out["cl%d_g" % ci] = subsample(_np(d.grad))
+        # use_gradient_loss=True (train_step1.py:20,63): whole batch, single resolution ...
+        d = depths[0].detach().clone().requires_grad_(True)
+        loss = u.calculate_loss(d, gt, True); loss.backward()
+        out["sb%d_loss" % ci] = np.array(float(loss.detach()), dtype=np.float64)
+        out["sb%d_g" % ci] = subsample(_np(d.grad))
+        # ... and through the multi-resolution wrapper (sample 0 only)
+        depths, gt = loss_case(B, seed, scales=scales)
+        depths = [x.requires_grad_(True) for x in depths]
+        loss = u.calculate_loss_multi_resolution(depths, gt, True); loss.backward()
+        out["sbmr%d_loss" % ci] = np.array(float(loss.detach()), dtype=np.float64)
+        for k, x in enumerate(depths):
+            out["sbmr%d_g_%d" % (ci, k)] = subsample(_np(x.grad[0]))
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            g = torch.Generator().manual_seed(77)
+            self.ps = torch.nn.ParameterList([torch.nn.Parameter(torch.randn(*s, generator=g)) for s in ADAMW_SHAPES])
+    net = Net()
+    opt = u.get_optimizer(net, "adam", 1e-2, 1e-2)
+    g = torch.Generator().manual_seed(78)
+    for step in range(4):
+        for p in net.ps:
+            p.grad = torch.randn(p.shape, generator=g) * (0.1 + step)
+        opt.step()
+        for k, p in enumerate(net.ps):
+            out["adamw_s%d_p%d" % (step, k)] = _np(p).copy()
+    np.savez_compressed(os.path.join(OUT, "loss_optim.npz"), **out)
+
+
 def main():
     assert ref_shim.reference_available(), "needs /root/reference"
     os.makedirs(OUT, exist_ok=True)
@@ -271,6 +326,8 @@ def main():
         gen_setp2(r1, r2)
     if not only or "setp2train" in only:
         gen_setp2_train(r1, r2)
+    if not only or "loss" in only:
+        gen_loss_optim()
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

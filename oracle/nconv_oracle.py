@@ -11,6 +11,8 @@ What it is: a functional (state_dict in, tensors out) fp32 restatement, in plain
   * `DNET.forward`               /root/reference/models/step1.py:51-94
   * `SETP2_BP_TRAIN/EXPORT.forward` and their blocks
                                  /root/reference/models/step2.py:60-77, 105-126, 134-297
+  * `calculate_loss`, `calculate_loss_multi_resolution`, AdamW of `get_optimizer`
+                                 /root/reference/utils.py:138-151, 63-71, 53-55
 The arithmetic below the reference's call sites lives in ATen (torch 2.11.0 in this image;
 the authors pinned pytorch 2.2.2, environment.yml:240) — a third-party dependency that is
 not under /root/reference.  The restatement therefore issues the same ATen calls in the
@@ -184,6 +186,80 @@ def setp2_forward(sd, rgb0, depth0, rgb1, depth1, export, bn_training=False,
         d3[:, :, :, :20] = 0          # :124
         return d3
     return [d0, d1, d2, d3]
+
+
+# --------------------------------------------------------------------------------------
+# Training-loop callers (utils.py): masked multi-resolution MSE, AdamW
+# --------------------------------------------------------------------------------------
+def upsample_bilinear_af(x: torch.Tensor, H: int, W: int) -> torch.Tensor:
+    """F.interpolate(x, size=(H, W), mode='bilinear', align_corners=False) — utils.py:67 — restated from
+    ATen's upsample_bilinear2d (UpSample.h area_pixel_compute_source_index / compute_source_index_and_lambda):
+    src = max((dst + 0.5) * in/out - 0.5, 0); i0 = floor(src); i1 = i0 + (i0 < in-1); lambda = src - i0.
+    Works in the dtype of x (the scale is a float32 value in ATen for float32 input)."""
+    h, w = x.shape[-2:]
+
+    def axis(n_in, n_out):
+        scale = torch.tensor(n_in / n_out, dtype=x.dtype)
+        src = ((torch.arange(n_out, dtype=x.dtype) + 0.5) * scale - 0.5).clamp_min(0)
+        i0 = src.floor().long().clamp_max(n_in - 1)
+        i1 = i0 + (i0 < n_in - 1).long()
+        lam = src - i0.to(x.dtype)
+        return i0, i1, lam
+
+    y0, y1, ly = axis(h, H)
+    x0, x1, lx = axis(w, W)
+    ly = ly.view(-1, 1)
+    top = x[..., y0, :][..., x0] * (1 - lx) + x[..., y0, :][..., x1] * lx
+    bot = x[..., y1, :][..., x0] * (1 - lx) + x[..., y1, :][..., x1] * lx
+    return top * (1 - ly) + bot * ly
+
+
+SOBEL_X = [[1., 0., -1.], [2., 0., -2.], [1., 0., -1.]]      # utils.py:99-103
+SOBEL_Y = [[1., 2., 1.], [0., 0., 0.], [-1., -2., -1.]]      # utils.py:113-117
+
+
+def gradient_loss(target, predicted):
+    """utils.py:121-136: mean |sobel_x(target - predicted)| + mean |sobel_y(...)|, zero padding 1."""
+    diff = target - predicted
+    if diff.dim() == 3:
+        diff = diff.unsqueeze(0)
+    kx = torch.tensor([[SOBEL_X]], dtype=diff.dtype)
+    ky = torch.tensor([[SOBEL_Y]], dtype=diff.dtype)
+    return F.conv2d(diff, kx, padding=1).abs().mean() + F.conv2d(diff, ky, padding=1).abs().mean()
+
+
+def calculate_loss(reconstructed, target, use_gradient_loss=False):
+    """utils.py:138-151: mse over ALL elements after zeroing the prediction where target == 0;
+    with use_gradient_loss: 0.8*sqrt(mse) + 0.2*gradient_loss(target, masked prediction)."""
+    rec = reconstructed.masked_fill(target == 0, 0)
+    mse = ((rec - target) ** 2).mean()
+    if use_gradient_loss:
+        return torch.sqrt(mse) * 0.8 + gradient_loss(target, rec) * 0.2
+    return mse
+
+
+def calculate_loss_multi_resolution(depths, target, all_samples=False, use_gradient_loss=False):
+    """utils.py:63-71: upsample every scale to the target size, loss on sample 0 only ([0] at :69),
+    mean over scales.  all_samples=True is the batch-mean generalisation used by the weak-scaling bench."""
+    H, W = target.shape[-2:]
+    total = 0.0
+    for d in depths:
+        up = upsample_bilinear_af(d, H, W)
+        total = total + (calculate_loss(up, target, use_gradient_loss) if all_samples
+                         else calculate_loss(up[0], target[0], use_gradient_loss))
+    return total / len(depths)
+
+
+def adamw_step(p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2):
+    """torch.optim.AdamW single-tensor update (torch/optim/adam.py _single_tensor_adam with
+    decoupled_weight_decay; utils.py:55 constructs it with torch defaults).  Returns new (p, m, v)."""
+    p = p * (1 - lr * weight_decay)
+    m = m + (g - m) * (1 - beta1)
+    v = v * beta2 + g * g * (1 - beta2)
+    bc1 = 1 - beta1 ** step
+    bc2 = 1 - beta2 ** step
+    denom = v.sqrt() / (bc2 ** 0.5) + eps
+    return p - (lr / bc1) * (m / denom), m, v
 
 
 # --------------------------------------------------------------------------------------

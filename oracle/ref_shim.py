@@ -70,6 +70,35 @@ def load_reference():
     return r1, r2
 
 
+def load_reference_utils():
+    """The unmodified /root/reference/utils.py (calculate_loss*, get_optimizer) as a module."""
+    if "utils" in _CACHE:
+        return _CACHE["utils"]
+    if not os.path.isfile(os.path.join(REFERENCE_ROOT, "utils.py")):
+        raise RuntimeError("reference not present at %s" % REFERENCE_ROOT)
+    import importlib.util
+    load_reference()                      # installs the timm stub, imports torchvision first
+    saved = {k: sys.modules.pop(k) for k in list(sys.modules)
+             if k in ("models", "dataset", "utils") or k.startswith(("models.", "dataset."))}
+    old_path = list(sys.path)
+    sys.path[:] = [REFERENCE_ROOT] + [p for p in old_path
+                                      if not os.path.isdir(os.path.join(p or ".", "models"))]
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            spec = importlib.util.spec_from_file_location("ref_utils", os.path.join(REFERENCE_ROOT, "utils.py"))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+    finally:
+        sys.path[:] = old_path
+        for k in list(sys.modules):
+            if k in ("models", "dataset") or k.startswith(("models.", "dataset.")):
+                sys.modules["ref_" + k] = sys.modules.pop(k)
+        sys.modules.update(saved)
+    _CACHE["utils"] = mod
+    return mod
+
+
 class two_arg_step1:
     """Context manager: the shipped `SETP1_NCONV.forward(self, x0_d)` takes one tensor but
     `SETP2_BP_*` call it with two (`models/step2.py:62,107`).  The intended

@@ -96,6 +96,13 @@ SIGNATURES = {
     "nconv_b200_conv_tc": (c_int, [POINTER(TcDesc), c_void_p]),
     "nconv_b200_conv_small_p8": (c_int, [c_void_p] * 7 + [c_int] * 6 + [c_void_p]),
     "nconv_b200_head_p8": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
+    "nconv_b200_masked_mse_ws_bytes": (c_size_t, [c_int] * 5),
+    "nconv_b200_masked_mse_bilinear_fwd": (c_int, [c_void_p] * 4 + [c_size_t] + [c_int] * 5 + [c_float, c_int, c_void_p]),
+    "nconv_b200_masked_mse_bilinear_bwd": (c_int, [c_void_p] * 5 + [c_size_t] + [c_int] * 5 + [c_float, c_void_p]),
+    "nconv_b200_sobel_loss_ws_bytes": (c_size_t, [c_int] * 5),
+    "nconv_b200_sobel_loss_fwd": (c_int, [c_void_p] * 5 + [c_size_t] + [c_int] * 5 + [c_float, c_int, c_void_p]),
+    "nconv_b200_sobel_loss_bwd": (c_int, [c_void_p] * 6 + [c_size_t] + [c_int] * 5 + [c_float, c_void_p]),
+    "nconv_b200_adamw_step": (c_int, [c_void_p] * 4 + [c_longlong] + [c_float] * 5 + [c_int, c_void_p]),
 }
 
 _lib = None

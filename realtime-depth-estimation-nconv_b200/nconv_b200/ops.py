@@ -686,3 +686,162 @@ def bn_train(z, bn: "torch.nn.BatchNorm2d", residual=None, relu=True):
     if bn.track_running_stats and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
     return y
+
+
+# --------------------------------------------------------------------------------------
+# callers either side of the training path: masked multi-resolution MSE and AdamW
+# --------------------------------------------------------------------------------------
+class _DepthLossMultires(torch.autograd.Function):
+    """mean over scales of calculate_loss(upsample(d_s), gt): /root/reference/utils.py:63-71 over :138-151.
+    sobel=False: mse(up.masked_fill(gt == 0, 0), gt); sobel=True: 0.8*sqrt(mse) + 0.2*Sobel-L1 (utils.py:142-147).
+    `rows` = how many leading samples enter the loss (the reference indexes sample 0 only: utils.py:69)."""
+
+    @staticmethod
+    def forward(ctx, gt, rows, sobel, *depths):
+        gt = _prep(gt, "gt")
+        if gt.dim() != 4 or gt.shape[1] != 1:
+            raise ValueError("depth loss: gt must be [N,1,H,W]")
+        N, _, H, W = gt.shape
+        if not depths:
+            raise ValueError("depth loss: no prediction given")
+        rows = N if rows is None else int(rows)
+        if not 1 <= rows <= N:
+            raise ValueError("depth loss: rows must be in [1, N]")
+        ds = [_prep(d, "depth") for d in depths]
+        for d in ds:
+            if d.dim() != 4 or d.shape[0] != N or d.shape[1] != 1 or d.shape[2] < 1 or d.shape[3] < 1:
+                raise ValueError("depth loss: every prediction must be [N,1,h,w] with gt's N")
+        dev = gt.device
+        loss = torch.empty(1, device=dev, dtype=torch.float32)
+        wgt = 1.0 / len(ds)
+        stats = torch.empty((len(ds), 3), device=dev, dtype=torch.float64) if sobel else None
+        with torch.cuda.device(dev):
+            for i, d in enumerate(ds):
+                h, w = d.shape[2], d.shape[3]
+                if sobel:
+                    nb = int(_C.nconv_b200_sobel_loss_ws_bytes(rows, h, w, H, W))
+                    ws = _scratch(dev, nb)
+                    check(_C.nconv_b200_sobel_loss_fwd(_p(d), _p(gt), _p(loss), _p(stats[i]), _p(ws), nb, rows, h, w, H, W,
+                                                       wgt, int(i > 0), _stream(gt)), "sobel_loss_fwd")
+                else:
+                    nb = int(_C.nconv_b200_masked_mse_ws_bytes(rows, h, w, H, W))
+                    ws = _scratch(dev, nb)
+                    check(_C.nconv_b200_masked_mse_bilinear_fwd(_p(d), _p(gt), _p(loss), _p(ws), nb, rows, h, w, H, W, wgt,
+                                                                int(i > 0), _stream(gt)), "masked_mse_bilinear_fwd")
+        ctx.save_for_backward(gt, *ds)
+        ctx.cfg = (rows, sobel, stats)
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, gloss):
+        gt, *ds = ctx.saved_tensors
+        rows, sobel, stats = ctx.cfg
+        N, _, H, W = gt.shape
+        dev = gt.device
+        gloss = _prep(gloss.reshape(1), "gloss")
+        wgt = 1.0 / len(ds)
+        outs = []
+        with torch.cuda.device(dev):
+            for i, d in enumerate(ds):
+                if not ctx.needs_input_grad[3 + i]:
+                    outs.append(None)
+                    continue
+                h, w = d.shape[2], d.shape[3]
+                gd = torch.empty_like(d) if rows == N else torch.zeros_like(d)
+                if sobel:
+                    nb = int(_C.nconv_b200_sobel_loss_ws_bytes(rows, h, w, H, W))
+                    ws = _scratch(dev, nb)
+                    check(_C.nconv_b200_sobel_loss_bwd(_p(d), _p(gt), _p(gloss), _p(stats[i]), _p(gd), _p(ws), nb, rows, h, w,
+                                                       H, W, wgt, _stream(gt)), "sobel_loss_bwd")
+                else:
+                    nb = int(_C.nconv_b200_masked_mse_ws_bytes(rows, h, w, H, W))
+                    ws = _scratch(dev, nb)
+                    check(_C.nconv_b200_masked_mse_bilinear_bwd(_p(d), _p(gt), _p(gloss), _p(gd), _p(ws), nb, rows, h, w, H, W,
+                                                                wgt, _stream(gt)), "masked_mse_bilinear_bwd")
+                outs.append(gd)
+        return (None, None, None, *outs)
+
+
+def depth_loss_multires(depths, gt, rows=None, use_gradient_loss=False):
+    """Scalar loss tensor; `depths` is one [N,1,h,w] tensor or a sequence of them (one per scale)."""
+    if isinstance(depths, torch.Tensor):
+        depths = [depths]
+    return _DepthLossMultires.apply(gt, rows, bool(use_gradient_loss), *depths)
+
+
+class FusedAdamW:
+    """torch.optim.AdamW (amsgrad off) as ONE kernel per step over flat fp32 buffers.
+
+    Construction is lazy: at the first step() the parameters whose .grad is None (never reached by backward —
+    torch.optim skips those, e.g. the unused BatchNorm of the reference's NConv2d, step1.py:119) are left
+    out for good; the others are re-homed as views of one flat parameter buffer and their .grad as views of
+    one flat gradient buffer, so zero_grad() is one memset, the data-parallel all-reduce is one collective
+    on `flat_grad` with no staging copy, and the update is one launch.  A left-out parameter that later
+    receives a gradient raises."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2):
+        self.params = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("FusedAdamW: no trainable parameters")
+        dev = self.params[0].device
+        if dev.type != "cuda" or any(p.device != dev or p.dtype != torch.float32 for p in self.params):
+            raise ValueError("FusedAdamW: parameters must be float32 on one CUDA device")
+        self.lr, self.betas, self.eps, self.weight_decay = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
+        self.step_count = 0
+        self.active = None
+        self.flat_param = self.flat_grad = self.exp_avg = self.exp_avg_sq = None
+
+    def attach(self):
+        """Build the flat buffers from the gradients present now (call after the first backward)."""
+        if self.active is not None:
+            return
+        self.active = [p for p in self.params if p.grad is not None]
+        self.skipped = [p for p in self.params if p.grad is None]
+        if not self.active:
+            raise RuntimeError("FusedAdamW: no parameter has a gradient")
+        dev = self.active[0].device
+        # 4-element alignment keeps every view 16-byte aligned
+        offs, total = [], 0
+        for p in self.active:
+            offs.append(total)
+            total += (p.numel() + 3) // 4 * 4
+        self.flat_param = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.flat_grad = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.exp_avg = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(total, device=dev, dtype=torch.float32)
+        with torch.no_grad():
+            for p, off in zip(self.active, offs):
+                n = p.numel()
+                pv = self.flat_param[off:off + n].view(p.shape)
+                gv = self.flat_grad[off:off + n].view(p.shape)
+                pv.copy_(p.data); gv.copy_(p.grad)
+                p.data = pv
+                p.grad = gv
+
+    def zero_grad(self, set_to_none: bool = True):
+        if self.active is None:
+            for p in self.params:
+                p.grad = None
+            return
+        self.flat_grad.zero_()
+
+    def allreduce_mean(self, group=None):
+        """grad <- mean over ranks, one collective on the flat gradient buffer."""
+        import torch.distributed as dist
+        self.attach()
+        if dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=group)
+            self.flat_grad.mul_(1.0 / dist.get_world_size(group))
+
+    @torch.no_grad()
+    def step(self):
+        self.attach()
+        for p in self.skipped:
+            if p.grad is not None:
+                raise RuntimeError("FusedAdamW: a parameter without a gradient at attach() received one later")
+        self.step_count += 1
+        n = self.flat_param.numel()
+        with torch.cuda.device(self.flat_param.device):
+            check(_C.nconv_b200_adamw_step(_p(self.flat_param), _p(self.flat_grad), _p(self.exp_avg), _p(self.exp_avg_sq),
+                                           n, self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                                           self.step_count, _stream(self.flat_param)), "adamw_step")

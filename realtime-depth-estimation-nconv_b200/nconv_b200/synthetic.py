@@ -71,6 +71,15 @@ def setp2_inputs(B: int, seed: int = 7, H: int = 480, W: int = 640):
     return rgb0, d0, rgb1, d1
 
 
+def loss_case(B: int, seed: int, H: int = 480, W: int = 640, scales=(1, 2, 4, 8), valid: float = 0.7):
+    """Ground truth with holes (exact zeros, as in the NYU/KITTI gt maps) and one prediction per scale
+    (train_step2.py:62-64: SETP2_BP_TRAIN returns 4 depth maps, full to 1/8 resolution)."""
+    g = _gen(seed)
+    gt = (torch.rand(B, 1, H, W, generator=g) * 9 + 1) * (torch.rand(B, 1, H, W, generator=g) < valid)
+    depths = [torch.rand(B, 1, H // s, W // s, generator=g) * 10 for s in scales]
+    return depths, gt
+
+
 def randomise_bn_stats(model: torch.nn.Module, seed: int = 55) -> None:
     """Give every BatchNorm2d of the RGB-guided stack non-trivial running statistics and affine
     parameters so that BN folding is exercised (the unused NConv2d.bnorm modules are skipped)."""

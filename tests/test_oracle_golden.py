@@ -106,3 +106,100 @@ def test_setp2_export(golden):
     for i, n in enumerate(("fuse0", "fuse1", "fuse2")):
         assert O.max_rel_err(depths[i], T(g[n + "_depth"])) < ORACLE_TOL
     assert torch.all(out[:, :, :45] == 0) and torch.all(out[:, :, -45:] == 0) and torch.all(out[..., :20] == 0)
+
+
+# ---------------------------------------------------------------------------------------------
+# training-loop callers: utils.py:63-71 / :138-151 (loss) and :53-55 (AdamW)
+# ---------------------------------------------------------------------------------------------
+import torch.nn.functional as F  # noqa: E402
+from nconv_b200.synthetic import loss_case  # noqa: E402
+
+LOSS_CASES = [(2, 11, (1, 2, 4, 8)), (1, 12, (1,)), (3, 13, (2, 4)), (2, 14, (1, 3, 5, 16))]   # = gen_golden.py
+ADAMW_SHAPES = [(7,), (3, 5), (2, 3, 3, 3), (1,), (129,)]
+
+
+def _sub_np(t):
+    f = t.detach().cpu().reshape(-1)
+    return f if f.numel() <= 20000 else f[::13]
+
+
+@pytest.mark.parametrize("ci", range(len(LOSS_CASES)))
+@pytest.mark.parametrize("dt", [torch.float32, torch.float64])
+def test_multires_loss_oracle_vs_reference_golden(golden, ci, dt):
+    g = golden("loss_optim.npz")
+    B, seed, scales = LOSS_CASES[ci]
+    tag = "" if dt == torch.float32 else "64"
+    depths, gt = loss_case(B, seed, scales=scales)
+    depths = [d.to(dt).requires_grad_(True) for d in depths]
+    loss = O.calculate_loss_multi_resolution(depths, gt.to(dt))
+    loss.backward()
+    tol = ORACLE_TOL if dt == torch.float32 else 1e-12
+    ref = float(g["mr%d_loss%s" % (ci, tag)])
+    assert abs(float(loss) - ref) / abs(ref) < tol
+    for k, d in enumerate(depths):
+        r = T(g["mr%d_g%s_%d" % (ci, tag, k)])
+        assert float((_sub_np(d.grad[0]) - r).abs().max()) / float(r.abs().max()) < tol
+        assert float(d.grad[1:].abs().sum()) == 0.0
+
+
+@pytest.mark.parametrize("ci", range(len(LOSS_CASES)))
+def test_calculate_loss_oracle_vs_reference_golden(golden, ci):
+    g = golden("loss_optim.npz")
+    B, seed, _ = LOSS_CASES[ci]
+    depths, gt = loss_case(B, seed, scales=(1,))
+    d = depths[0].requires_grad_(True)
+    loss = O.calculate_loss(d, gt)
+    loss.backward()
+    ref = float(g["cl%d_loss" % ci])
+    assert abs(float(loss) - ref) / abs(ref) < ORACLE_TOL
+    r = T(g["cl%d_g" % ci])
+    assert float((_sub_np(d.grad) - r).abs().max()) / float(r.abs().max()) < ORACLE_TOL
+
+
+def test_upsample_restatement_vs_aten():
+    torch.manual_seed(4)
+    for (h, w, H, W) in [(60, 80, 480, 640), (7, 5, 20, 33), (48, 64, 48, 64), (33, 20, 7, 5), (1, 1, 4, 4)]:
+        x = torch.randn(2, 1, h, w, dtype=torch.float64)
+        ref = F.interpolate(x, size=(H, W), mode="bilinear", align_corners=False)
+        assert float((O.upsample_bilinear_af(x, H, W) - ref).abs().max()) < 1e-12
+
+
+def test_adamw_oracle_vs_reference_golden(golden):
+    g = golden("loss_optim.npz")
+    gen = torch.Generator().manual_seed(77)
+    ps = [torch.randn(*s, generator=gen) for s in ADAMW_SHAPES]
+    ms = [torch.zeros_like(p) for p in ps]
+    vs = [torch.zeros_like(p) for p in ps]
+    gen = torch.Generator().manual_seed(78)
+    for step in range(4):
+        for k in range(len(ps)):
+            grad = torch.randn(ps[k].shape, generator=gen) * (0.1 + step)
+            ps[k], ms[k], vs[k] = O.adamw_step(ps[k], grad, ms[k], vs[k], step + 1, lr=1e-2, weight_decay=1e-2)
+            ref = T(g["adamw_s%d_p%d" % (step, k)])
+            assert float((ps[k] - ref).abs().max()) < 1e-6 * (1 + float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("ci", range(len(LOSS_CASES)))
+def test_gradient_loss_oracle_vs_reference_golden(golden, ci):
+    """use_gradient_loss=True: 0.8*RMSE + 0.2*Sobel-L1 (utils.py:95-147)."""
+    g = golden("loss_optim.npz")
+    B, seed, scales = LOSS_CASES[ci]
+    depths, gt = loss_case(B, seed, scales=(1,))
+    d = depths[0].requires_grad_(True)
+    loss = O.calculate_loss(d, gt, True)
+    loss.backward()
+    ref = float(g["sb%d_loss" % ci])
+    assert abs(float(loss.detach()) - ref) / abs(ref) < ORACLE_TOL
+    r = T(g["sb%d_g" % ci])
+    assert float((_sub_np(d.grad) - r).abs().max()) / float(r.abs().max()) < ORACLE_TOL
+    depths, gt = loss_case(B, seed, scales=scales)
+    depths = [x.requires_grad_(True) for x in depths]
+    loss = O.calculate_loss_multi_resolution(depths, gt, use_gradient_loss=True)
+    loss.backward()
+    ref = float(g["sbmr%d_loss" % ci])
+    assert abs(float(loss.detach()) - ref) / abs(ref) < ORACLE_TOL
+    for k, x in enumerate(depths):
+        r = T(g["sbmr%d_g_%d" % (ci, k)])
+        # a Sobel response within rounding of 0 may take the other sign: allow isolated pixels
+        bad = ((_sub_np(x.grad[0]) - r).abs() / float(r.abs().max()) >= ORACLE_TOL).float().mean()
+        assert float(bad) < 1e-4

@@ -12,9 +12,12 @@ all-reduce of the flat gradient bucket over NCCL (nconv_b200.distributed.GradBuc
 (lr 1e-4, wd 1e-7: train_step2.py:17-18, utils.py:53-61).
 
 `--frames` is the per-GPU batch (frames per stream = frames/2; config 5 = 16 per GPU x 8 GPUs = 128).
-The loss is utils.py:63-71's multi-resolution loss restated with a batch mean instead of the
-reference's sample-0-only indexing; it is caller-side PyTorch code, not part of
-the kernel path.  Prints one JSON line on rank 0.
+The loss is utils.py:63-71's multi-resolution masked MSE with a batch mean instead of the reference's
+sample-0-only indexing, and the optimizer utils.py:53-55's AdamW; both run on the
+package's own kernels (csrc/loss_optim.cu: one launch per scale per direction, one launch for the
+update over the flat buffer whose gradient half is also the all-reduce bucket).  `--torch-loss-optim`
+keeps the previous caller-side PyTorch loss + torch.optim.AdamW + GradBucket for comparison.
+Prints one JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -34,13 +37,11 @@ import torch.nn.functional as F  # noqa: E402
 
 
 def multires_loss(depths, gt):
-    """utils.py:63-71 + :138-151 with use_gradient_loss=False: mean over scales of sqrt(masked MSE)."""
+    """utils.py:63-71 + :138-151 with use_gradient_loss=False, batch mean, in eager PyTorch."""
     total = 0.0
-    mask = (gt > 0).float()
-    n = mask.sum().clamp_min(1.0)
     for d in depths:
         up = F.interpolate(d, size=gt.shape[2:], mode="bilinear", align_corners=False)
-        total = total + torch.sqrt((((up - gt) * mask) ** 2).sum() / n)
+        total = total + F.mse_loss(up.masked_fill(gt == 0, 0), gt)
     return total / len(depths)
 
 
@@ -51,6 +52,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--height", type=int, default=480)
     ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--torch-loss-optim", action="store_true")
     args = ap.parse_args()
     import torch.distributed as dist
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -76,8 +78,14 @@ def main():
     os.chdir(cwd)
     broadcast_parameters(model)
     params = [p for p in model.parameters() if p.requires_grad]
-    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-7)
-    bucket = GradBucket(params)
+    import utils as U
+    fused = not args.torch_loss_optim
+    if fused:
+        opt = U.get_optimizer(model, "adam", 1e-4, 1e-7)
+        bucket = None
+    else:
+        opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-7)
+        bucket = GradBucket(params)
     rgb0, d0, rgb1, d1 = (t.to(dev) for t in setp2_inputs(per, seed=100 + rank, H=H, W=W))
     g = torch.Generator().manual_seed(200 + rank)
     gt = (torch.rand(2 * per, 1, H, W, generator=g) * 9.5 + 0.5) * (torch.rand(2 * per, 1, H, W, generator=g) > 0.1)
@@ -87,9 +95,15 @@ def main():
         model.train()
         opt.zero_grad(set_to_none=False)
         a, b = model(rgb0, d0, rgb1, d1)
-        loss = multires_loss([torch.cat((x, y), 0) for x, y in zip(a, b)], gt)
-        loss.backward()
-        bucket.allreduce_mean()
+        depths = [torch.cat((x, y), 0) for x, y in zip(a, b)]
+        if fused:
+            loss = U.calculate_loss_multi_resolution(depths, gt, False, all_samples=True)
+            loss.backward()
+            opt.allreduce_mean()
+        else:
+            loss = multires_loss(depths, gt)
+            loss.backward()
+            bucket.allreduce_mean()
         opt.step()
         return loss
 
@@ -122,7 +136,8 @@ def main():
             "metric": "setp1+setp2_training_frames_per_s_480x640", "value": args.frames * world * args.steps / (ms / 1e3),
             "unit": "frames/s", "n_gpus": world, "steps": args.steps, "ms_per_step": ms / args.steps,
             "frames_per_gpu": args.frames, "global_batch": args.frames * world, "loss": float(loss),
-            "grad_bucket_bytes": bucket.nbytes, "gpu_launches_per_step": (ops.launch_count() - n0) / args.steps,
+            "loss_optim": "fused" if fused else "torch",
+            "grad_bucket_bytes": opt.flat_grad.numel() * 4 if fused else bucket.nbytes, "gpu_launches_per_step": (ops.launch_count() - n0) / args.steps,
             "peak_mem_GB": torch.cuda.max_memory_allocated(dev) / 2 ** 30,
             "kernels": [{"kernel": k, "ms_per_step": round(v[0] / args.steps, 3), "launches_per_step": v[1] / args.steps,
                          "tflops": round(v[2] / v[0] / 1e9, 2) if v[0] > 0 else 0.0} for k, v in top]}))
