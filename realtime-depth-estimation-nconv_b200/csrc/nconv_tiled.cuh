@@ -173,6 +173,60 @@ nconv_tiled(const TiledArgs a) {
     __syncthreads();
     // ---- stage CCH channels: halo tiles of both streams, zero-filled outside the image
     constexpr int SLOTS = CCH * RH * (SW / 4);
+    // Fast staging (forward, 128-bit path, chunk entirely from one source): the loads of STAGE_UN slots are issued
+    // before any of them is consumed, so a chunk costs ~NIT/STAGE_UN DRAM round trips instead of NIT (the generic
+    // loop below is load -> multiply -> STS per slot and its branches keep the compiler from hoisting the loads).
+    // With W % 4 == 0 and staged columns starting at a multiple of 4, a quad is entirely inside or outside the row.
+    bool staged = false;
+    if constexpr (!BWD) {
+      const bool from_a = (CB == 0) || (c0 + CCH <= CA);
+      const bool from_b = (CB > 0) && (c0 >= CA);
+      if (a.vec_ok && (from_a || (from_b && a.up2_vec))) {
+        staged = true;
+        constexpr int NIT = (SLOTS + NTHREADS - 1) / NTHREADS;
+        constexpr int STAGE_UN = 3;
+#pragma unroll
+        for (int it0 = 0; it0 < NIT; it0 += STAGE_UN) {
+          float4 xv[STAGE_UN], cv[STAGE_UN];
+          int so[STAGE_UN];
+          bool ok[STAGE_UN];
+#pragma unroll
+          for (int k = 0; k < STAGE_UN; ++k) {
+            const int idx = tid + (it0 + k) * NTHREADS;
+            const int j = idx % (SW / 4), r = (idx / (SW / 4)) % RH, cc = idx / ((SW / 4) * RH);
+            const int cs = c0 + cc, gy = gy0 + r, gx = gx0a + 4 * j;
+            so[k] = (it0 + k < NIT && idx < SLOTS) ? (cc * RH + r) * SW + 4 * j : -1;
+            ok[k] = so[k] >= 0 && gy >= 0 && gy < a.H && gx >= 0 && gx + 3 < a.W && cs < CI;
+            xv[k] = make_float4(0.f, 0.f, 0.f, 0.f); cv[k] = xv[k];
+            if (ok[k]) {
+              if (from_a) {
+                const size_t base = ((size_t)(b * CA + cs) * a.H + gy) * a.W + gx;
+                xv[k] = __ldg(reinterpret_cast<const float4*>(a.xa + base));
+                if (!THRESH) cv[k] = __ldg(reinterpret_cast<const float4*>(a.ca + base));
+              } else {
+                const size_t base = ((size_t)(b * CB + (cs - CA)) * a.HB + a.map_h(gy)) * a.WB + (gx >> 1);
+                const float2 x2 = __ldg(reinterpret_cast<const float2*>(a.xb + base));
+                const float2 c2 = __ldg(reinterpret_cast<const float2*>(a.cb + base));
+                xv[k] = make_float4(x2.x, x2.x, x2.y, x2.y);
+                cv[k] = make_float4(c2.x, c2.x, c2.y, c2.y);
+              }
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < STAGE_UN; ++k) {
+            if (so[k] < 0) continue;
+            float4 c4 = cv[k];
+            if (THRESH && from_a) {
+              c4.x = (ok[k] && xv[k].x > a.thr) ? 1.f : 0.f; c4.y = (ok[k] && xv[k].y > a.thr) ? 1.f : 0.f;
+              c4.z = (ok[k] && xv[k].z > a.thr) ? 1.f : 0.f; c4.w = (ok[k] && xv[k].w > a.thr) ? 1.f : 0.f;
+            }
+            *reinterpret_cast<float4*>(s_xc + so[k]) = make_float4(xv[k].x * c4.x, xv[k].y * c4.y, xv[k].z * c4.z, xv[k].w * c4.w);
+            *reinterpret_cast<float4*>(s_c + so[k]) = c4;
+          }
+        }
+      }
+    }
+    if (!staged)
     for (int idx = tid; idx < SLOTS; idx += NTHREADS) {
       int j = idx % (SW / 4);
       int r = (idx / (SW / 4)) % RH;
