@@ -1,6 +1,7 @@
 // NConv2d forward launchers (C ABI) — /root/reference/models/step1.py:116-149 and the fused
 // DNET stages (step1.py:51-94).  The kernel itself is nconv_tiled.cuh.
 #include "nconv_tiled.cuh"
+#include "nconv_pipe.cuh"
 #include "nconv_stream.cuh"
 #include <cstdlib>
 
@@ -82,11 +83,18 @@ extern "C" int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* 
              (thresh || aligned16(d->ca)) &&
              (tail ? aligned16(d->out_tail) : (aligned16(d->y) && aligned16(d->cout)));
 
+  // Persistent cp.async-pipelined kernel (nconv_pipe.cuh) for the FMA-bound DNET layers; NCONV_B200_NO_PIPE=1 keeps
+  // them on nconv_tiled (A/B measurements).  Bit-identical results.
+  static const bool no_pipe = getenv("NCONV_B200_NO_PIPE") != nullptr;
+  const bool pipe_ok = !no_pipe && a.vec_ok && (!thresh || d->thr >= 0.f) && (d->CB == 0 || a.up2_vec);
+
   // The nconv6+nconv7 tail evaluates the valid 3x3 "centred", i.e. with pad-1 geometry.
   if (tail) {
     if (!(d->K == 3 && d->pad == 0)) return NCONV_ERR_UNSUPPORTED;
-    if (d->CA == 8 && d->CB == 8 && d->CO == 8)
+    if (d->CA == 8 && d->CB == 8 && d->CO == 8) {
+      if (pipe_ok) return launch_pipe<8, 8, 8, 3, 1, NCONV_B200_F_TAIL>(a, st);
       return launch_tiled<8, 8, 8, 8, 3, 1, NCONV_B200_F_TAIL>(a, st);
+    }
     return NCONV_ERR_UNSUPPORTED;
   }
   // HBM-bound small-channel shapes (BASELINE.json config 2): streaming kernel, needs 128-bit rows.
@@ -114,6 +122,15 @@ extern "C" int nconv_b200_nconv2d_fwd_fused(const nconv_b200_fwd_desc* d, void* 
 #undef NCONV_STREAM_CASE
   }
   // DNET shapes (step1.py:38-49)
+#define NCONV_PIPE_CASE(ca_, cb_, co_, k_, pad_, fl_)                                                    \
+  if (pipe_ok && d->CA == ca_ && d->CB == cb_ && d->CO == co_ && d->K == k_ && d->pad == pad_ && d->flags == fl_) \
+    return launch_pipe<ca_, cb_, co_, k_, pad_, fl_>(a, st);
+  NCONV_PIPE_CASE(1, 0, 8, 5, 2, NCONV_B200_F_THRESH)
+  NCONV_PIPE_CASE(8, 0, 8, 5, 2, NCONV_B200_F_POOL)
+  NCONV_PIPE_CASE(8, 0, 8, 5, 2, 0)
+  NCONV_PIPE_CASE(8, 8, 8, 3, 1, 0)
+  NCONV_PIPE_CASE(16, 0, 8, 3, 1, 0)
+#undef NCONV_PIPE_CASE
   NCONV_CASE(1, 0, 8, 8, 5, 2, NCONV_B200_F_THRESH)
   NCONV_CASE(1, 0, 8, 8, 5, 2, 0)
   NCONV_CASE(8, 0, 8, 8, 5, 2, NCONV_B200_F_POOL)
