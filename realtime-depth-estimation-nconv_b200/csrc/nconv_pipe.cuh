@@ -39,8 +39,9 @@ struct PipeSmem {
   static constexpr size_t BYTES = sizeof(float) * (W_FLOATS + 16 + 4 * TILE_FLOATS);
 };
 
-// CO channels are all produced by one CTA (CO even, <= 8).  FLAGS: F_THRESH | F_POOL | F_TAIL as in nconv_tiled.
-template <int CA, int CB, int CO, int K, int PAD, int FLAGS>
+// One CTA produces CO (even, <= 8) of the layer's CO_ALL output channels: group blockIdx.y.  FLAGS: F_THRESH |
+// F_POOL | F_TAIL as in nconv_tiled.
+template <int CA, int CB, int CO_ALL, int CO, int K, int PAD, int FLAGS>
 __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int tiles_x, int tiles_y, int ntiles) {
   using SM = PipeSmem<CA, CB, CO, K>;
   constexpr int CI = SM::CI, CCH = SM::CCH, NCHUNK = SM::NCHUNK, RH = SM::RH;
@@ -52,7 +53,9 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
   constexpr int CO_P = CO / 2;
   constexpr int SLOTS = CCH * RH * (SW / 4);
   constexpr int NIT = (SLOTS + NTHREADS - 1) / NTHREADS;
-  static_assert(CO % 2 == 0 && CO <= 8, "nconv_pipe: CO must be even and <= 8");
+  static_assert(CO % 2 == 0 && CO <= 8 && CO_ALL % CO == 0, "nconv_pipe: CO must be even, <= 8 and divide CO_ALL");
+  static_assert(!TAIL || CO_ALL == CO, "tail needs all channels in one CTA");
+  const int cog = blockIdx.y;
   static_assert(CB == 0 || CA % CCH == 0, "nconv_pipe: a chunk must come from one source");
   static_assert(CI % CCH == 0, "nconv_pipe: whole chunks only");
   static_assert(4 * NV + 4 * (TW / PX - 1) <= SW, "staged row too narrow");
@@ -142,7 +145,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
     if (CB == 0) ciw = cs;
     else if (a.a_first) ciw = cs;
     else ciw = (cs < CA) ? (CB + cs) : (cs - CA);
-    s_w[idx] = __ldg(&a.w[(((size_t)o * CI + ciw) * K + u) * K + v]);
+    s_w[idx] = __ldg(&a.w[(((size_t)(cog * CO + o) * CI + ciw) * K + u) * K + v]);
   }
   __syncthreads();
   {
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
       float s = 0.f;
       for (int j = lane; j < CI * K * K; j += 32) s += s_w[j * CO + o];
       s = warp_sum(s);
-      if (lane == 0) { s_sum[o] = 1.f / s; s_bias[o] = __ldg(&a.bias[o]); }
+      if (lane == 0) { s_sum[o] = 1.f / s; s_bias[o] = __ldg(&a.bias[cog * CO + o]); }
     }
   }
   // (s_sum / s_bias are first read in an epilogue, after at least one __syncthreads of the chunk loop)
@@ -263,7 +266,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
       if (oy < a.HO && ox + 3 < a.WO) {
 #pragma unroll
         for (int o = 0; o < CO; ++o) {
-          const size_t base = (((size_t)b * CO + o) * a.HO + oy) * a.WO + ox;
+          const size_t base = (((size_t)b * CO_ALL + cog * CO + o) * a.HO + oy) * a.WO + ox;
           *reinterpret_cast<float4*>(a.y + base) = make_float4(yv[o][0], yv[o][1], yv[o][2], yv[o][3]);
           *reinterpret_cast<float4*>(a.co + base) = make_float4(cv[o][0], cv[o][1], cv[o][2], cv[o][3]);
         }
@@ -280,7 +283,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
             clo[p] = __shfl_xor_sync(0xffffffffu, cv[o][p], 16);
           }
           if ((ty & 1) == 0 && py < a.HP) {
-            const size_t base = (((size_t)b * CO + o) * a.HP + py) * a.WP;
+            const size_t base = (((size_t)b * CO_ALL + cog * CO + o) * a.HP + py) * a.WP;
 #pragma unroll
             for (int h = 0; h < PX / 2; ++h) {
               const int pxo = (ox >> 1) + h;
@@ -305,10 +308,11 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
 
 // Eligibility (checked by the caller): forward, a.vec_ok, thr >= 0 under F_THRESH, source B an exact 2x upsample
 // with 8-byte rows (a.up2_vec) when CB > 0.
-template <int CA, int CB, int CO, int K, int PAD, int FLAGS>
+template <int CA, int CB, int CO_ALL, int CO, int K, int PAD, int FLAGS>
 static int launch_pipe(const TiledArgs& a, cudaStream_t st) {
   using SM = PipeSmem<CA, CB, CO, K>;
-  auto kern = nconv_pipe<CA, CB, CO, K, PAD, FLAGS>;
+  constexpr int NG = CO_ALL / CO;
+  auto kern = nconv_pipe<CA, CB, CO_ALL, CO, K, PAD, FLAGS>;
   static bool attr_done[NCONV_MAX_DEVICES] = {};
   static int sm_count[NCONV_MAX_DEVICES] = {};
   int dev = 0;
@@ -326,19 +330,20 @@ static int launch_pipe(const TiledArgs& a, cudaStream_t st) {
   const int tiles_x = ceil_div(ow, TW), tiles_y = ceil_div(oh, TH);
   const long long ntiles = (long long)tiles_x * tiles_y * a.B;
   if (ntiles > 0x7fffffffLL) return NCONV_ERR_UNSUPPORTED;
-  const int grid = (int)(ntiles < 2LL * sm_count[dev] ? ntiles : 2LL * sm_count[dev]);
+  const long long slots = 2LL * sm_count[dev] / NG > 0 ? 2LL * sm_count[dev] / NG : 1;
+  const dim3 grid((unsigned)(ntiles < slots ? ntiles : slots), NG);
   const double px_in = (double)a.B * a.H * a.W, px_out = (double)a.B * oh * ow;
   double bytes, flops;
   if (TAIL) {
     bytes = 4.0 * (2.0 * CA * px_in + 2.0 * CB * a.B * a.HB * a.WB + px_out);
-    flops = 4.0 * (CA + CB) * CO * K * K * px_out + 4.0 * CO * px_out;
+    flops = 4.0 * (CA + CB) * CO_ALL * K * K * px_out + 4.0 * CO_ALL * px_out;
   } else {
-    bytes = 4.0 * ((THRESH ? 1.0 : 2.0) * CA * px_in + 2.0 * CB * a.B * a.HB * a.WB + 2.0 * CO * px_out +
-                   (POOL ? 2.0 * CO * a.B * a.HP * a.WP : 0.0));
-    flops = 4.0 * (CA + CB) * CO * K * K * px_out;
+    bytes = 4.0 * ((THRESH ? 1.0 : 2.0) * CA * px_in + 2.0 * CB * a.B * a.HB * a.WB + 2.0 * CO_ALL * px_out +
+                   (POOL ? 2.0 * CO_ALL * a.B * a.HP * a.WP : 0.0));
+    flops = 4.0 * (CA + CB) * CO_ALL * K * K * px_out;
   }
   char label[64];
-  snprintf(label, sizeof(label), "nconv_fwd %d+%d->%d k%d f%d", CA, CB, CO, K, FLAGS & 7);
+  snprintf(label, sizeof(label), "nconv_fwd %d+%d->%d k%d f%d", CA, CB, CO_ALL, K, FLAGS & 7);
   {
     LaunchScope ls(st, label, flops, bytes);
     kern<<<grid, NTHREADS, SM::BYTES, st>>>(a, tiles_x, tiles_y, (int)ntiles);
