@@ -190,6 +190,18 @@ def summarise_kernels(records, steps):
     return rows
 
 
+def measured_traffic(kernel_label):
+    """DRAM bytes (read + write) of one launch of `kernel_label` from a committed `ncu --set full` capture of this
+    very command (profiles/roofline_traffic.json names the capture), or None when no capture covers the kernel."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        with open(path) as f:
+            ent = json.load(f).get(kernel_label)
+        return float(ent["dram_bytes"]) if ent else None
+    except (OSError, ValueError, KeyError, TypeError):
+        return None
+
+
 def roofline_of(row, peaks, sustained=True):
     """Bound = whichever of the HBM time and the tensor-pipe time of the launch is longer.  The tcgen05
     convolutions spend THREE bf16 MMAs per algorithmic product (bf16x3 split precision: the 1e-4 parity
@@ -206,7 +218,7 @@ def roofline_of(row, peaks, sustained=True):
         mma_factor = (128.0 * 256.0) / (32.0 * 254.0)
     t_hbm = row["bytes"] / (peaks["hbm_gbs"] * 1e9)
     t_tc = mma_factor * row["flops"] / (tf_peak * 1e12) if tc else 0.0
-    common = {"kernel": row["kernel"], "traffic": None, "peak_source": peaks["source"], "avg_ms": row["avg_ms"],
+    common = {"kernel": row["kernel"], "traffic": measured_traffic(row["kernel"]), "peak_source": peaks["source"], "avg_ms": row["avg_ms"],
               "share_of_step": row["share"], "hbm_gbs": row["gbs"], "hbm_frac": row["gbs"] / peaks["hbm_gbs"]}
     if t_hbm >= t_tc:
         out = {"bound": "hbm", "achieved": row["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
         const int j = idx % (SW / 4), r = (idx / (SW / 4)) % RH, cc = idx / ((SW / 4) * RH);
         const int cs = c0 + cc, gy = gy0 + r, gx = gx0a + 4 * j;
         const bool ok = gy >= 0 && gy < a.H && gx >= 0 && gx + 3 < a.W;
-        const int so = (cc * RH + r) * SW + 4 * j;
+        const int so = 4 * idx;               // == (cc*RH + r)*SW + 4*j
         if (from_a) {
           const size_t base = ok ? ((size_t)(b * CA + cs) * a.H + gy) * a.W + gx : 0;
           cp_async16(dx + so, a.xa + base, ok);
@@ -106,8 +106,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) nconv_pipe(const TiledArgs a, int
     for (int it = 0; it < NIT; ++it) {
       const int idx = tid + it * NTHREADS;
       if (idx < SLOTS) {
-        const int j = idx % (SW / 4), r = (idx / (SW / 4)) % RH, cc = idx / ((SW / 4) * RH);
-        const int so = (cc * RH + r) * SW + 4 * j;
+        const int so = 4 * idx;               // slots are in memory order: (cc*RH + r)*SW + 4*j == 4*idx
         if (from_a) {
           float4 x4 = *reinterpret_cast<const float4*>(dx + so);
           float4 c4;
