@@ -42,15 +42,41 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
     s_scale[i] = a.scale ? __ldg(a.scale + i) : 1.f;
     s_shift[i] = a.shift ? __ldg(a.shift + i) : 0.f;
   }
+  // Input tile of the CTA's SM_ROWS rows (+1 halo each side), zero-filled outside the image, copied global -> shared
+  // once with 4-byte cp.async (rows start at x0-1: no wider alignment).  Before this the 27 loads per pixel were
+  // issued row by row and ncu showed 28 % of the warp samples stalled on them (long scoreboard at the first FFMA2 of
+  // every input channel); the 158 registers of the accumulators leave no room for a register prefetch.
+  // (The one-pixel-per-thread variants, 1->64, measured slower with the tile: they keep the direct loads.)
+  constexpr bool STAGE = PXT > 1;
+  constexpr int TWX = SM_THREADS * PXT + 2;
+  __shared__ float s_in[STAGE ? CI : 1][STAGE ? SM_ROWS + 2 : 1][STAGE ? TWX : 1];
+  const int n = blockIdx.z;
+  if constexpr (STAGE) {
+    const int x0 = blockIdx.x * (SM_THREADS * PXT) - 1, y0 = blockIdx.y * SM_ROWS - 1;
+#pragma unroll 4
+    for (int i = tid; i < CI * (SM_ROWS + 2) * TWX; i += SM_THREADS) {
+      const int c = i % TWX, r = (i / TWX) % (SM_ROWS + 2), ci = i / (TWX * (SM_ROWS + 2));
+      const int yy = y0 + r, xx = x0 + c;
+      const bool ok = yy >= 0 && yy < a.H && xx >= 0 && xx < a.W;
+      const float* src = a.x + (ok ? (((size_t)n * CI + ci) * a.H + yy) * a.W + xx : 0);
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(&s_in[ci][r][c]);
+      const int nbytes = ok ? 4 : 0;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  }
   __syncthreads();
 
-  const int n = blockIdx.z;
   const int xb = blockIdx.x * (SM_THREADS * PXT) + tid;
   const P8Geom g = P8Geom::make(a.B, CO, a.H, a.W);
   const P8QGeom qg = P8QGeom::make(a.B, CO, a.H, a.W);
   // a CTA walks SM_ROWS rows of its column block: the weight staging above is paid once per SM_ROWS rows
 #pragma unroll 1
   for (int y = blockIdx.y * SM_ROWS; y < min((int)(blockIdx.y + 1) * SM_ROWS, a.H); ++y) {
+  // the weights are loop-invariant shared-memory loads: an opaque zero keeps the compiler from hoisting all
+  // CI*9*CO of them out of the row loop into registers (255 registers + 3 KB of spills otherwise)
+  int wz = 0;
+  asm volatile("" : "+r"(wz));
   u64 acc2[PXT][CO / 2];          // packed pairs of output channels (FFMA2: weight pair x broadcast input)
 #pragma unroll
   for (int p = 0; p < PXT; ++p)
@@ -63,14 +89,19 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
     const float* plane = a.x + ((size_t)n * CI + ci) * a.H * a.W;
 #pragma unroll
     for (int u = 0; u < 3; ++u) {
+      const int r = y - blockIdx.y * SM_ROWS + u;          // tile row of image row y + u - 1
       const int yy = y + u - 1;
       float in[PXT][3];
 #pragma unroll
       for (int p = 0; p < PXT; ++p)
 #pragma unroll
         for (int v = 0; v < 3; ++v) {
-          const int xx = xb + p * SM_THREADS + v - 1;
-          in[p][v] = (yy >= 0 && yy < a.H && xx >= 0 && xx < a.W) ? __ldg(plane + (size_t)yy * a.W + xx) : 0.f;
+          if constexpr (STAGE) {
+            in[p][v] = s_in[ci][r][tid + p * SM_THREADS + v];
+          } else {
+            const int xx = xb + p * SM_THREADS + v - 1;
+            in[p][v] = (yy >= 0 && yy < a.H && xx >= 0 && xx < a.W) ? __ldg(plane + (size_t)yy * a.W + xx) : 0.f;
+          }
         }
       if (u == 1) {
 #pragma unroll
@@ -78,7 +109,7 @@ __global__ void __launch_bounds__(SM_THREADS) small_to_p8_kernel(const SmallArgs
       }
 #pragma unroll
       for (int v = 0; v < 3; ++v) {
-        const float* wr = s_w + (ci * 9 + u * 3 + v) * CO;
+        const float* wr = s_w + wz + (ci * 9 + u * 3 + v) * CO;
 #pragma unroll
         for (int o = 0; o < CO; o += 4) {
           const ulonglong2 w4 = *reinterpret_cast<const ulonglong2*>(wr + o);
@@ -147,30 +178,53 @@ __global__ void __launch_bounds__(HD_THREADS) head_p8_kernel(const HeadArgs a) {
   const int n = blockIdx.z, y0 = blockIdx.y * HD_TH, x0 = blockIdx.x * HD_TW;
   const P8Geom g = P8Geom::make(a.B, C, a.H, a.W);
   // ---- phase 1: nine partial dot products per staged pixel (padded coords: tile pixel (r, c) = image (y0+r-1, x0+c-1))
-  for (int p = threadIdx.x; p < HD_PH * HD_PW; p += HD_THREADS) {
-    const int r = p / HD_PW, c = p - r * HD_PW;
-    const int py = y0 + r, px = x0 + c;                  // padded plane coordinates
-    u64 acc[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
-    if (py < a.H + 2 && px < a.W + 2) {
-      const size_t off = ((size_t)py * g.Wp + px) * 8;
+  // Two staged pixels per thread and pass: every weight pair read from shared memory (5 LDS.64 per channel) feeds two
+  // FFMA2 instead of one — the kernel was L1/shared-pipe bound (ncu: l1tex 82 %) on exactly those broadcast reads.
+  constexpr int HD_NP = 2;
+  for (int p0 = threadIdx.x; p0 < HD_PH * HD_PW; p0 += HD_NP * HD_THREADS) {
+    int r[HD_NP], c[HD_NP];
+    bool live[HD_NP], in[HD_NP];
+    size_t off[HD_NP];
+    u64 acc[HD_NP][5];
+#pragma unroll
+    for (int k = 0; k < HD_NP; ++k) {
+      const int p = p0 + k * HD_THREADS;
+      live[k] = p < HD_PH * HD_PW;
+      r[k] = p / HD_PW; c[k] = p - r[k] * HD_PW;
+      const int py = y0 + r[k], px = x0 + c[k];          // padded plane coordinates
+      in[k] = live[k] && py < a.H + 2 && px < a.W + 2;
+      off[k] = in[k] ? ((size_t)py * g.Wp + px) * 8 : 0;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) acc[k][q] = 0ull;
+    }
 #pragma unroll 1
-      for (int ch = 0; ch < C / 8; ++ch) {
-        const uint4 hi = __ldg(reinterpret_cast<const uint4*>(a.f + g.plane(n, ch, 0) + off));
-        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(a.f + g.plane(n, ch, 1) + off));
-        float f[8];
-        join8(hi, lo, f);
+    for (int ch = 0; ch < C / 8; ++ch) {
+      float f[HD_NP][8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float* wr = s_w + (ch * 8 + e) * 10;
+      for (int k = 0; k < HD_NP; ++k) {
+        const uint4 hi = __ldg(reinterpret_cast<const uint4*>(a.f + g.plane(n, ch, 0) + off[k]));
+        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(a.f + g.plane(n, ch, 1) + off[k]));
+        join8(hi, lo, f[k]);
+      }
 #pragma unroll
-          for (int q = 0; q < 5; ++q) ffma2(acc[q], *reinterpret_cast<const u64*>(wr + 2 * q), f[e]);
+      for (int e = 0; e < 8; ++e) {
+        const float* wr = s_w + (ch * 8 + e) * 10;
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+          const u64 w2 = *reinterpret_cast<const u64*>(wr + 2 * q);
+#pragma unroll
+          for (int k = 0; k < HD_NP; ++k) ffma2(acc[k][q], w2, f[k][e]);
         }
       }
     }
 #pragma unroll
-    for (int q = 0; q < 5; ++q) {
-      s_t[2 * q][r][c] = lo32f(acc[q]);
-      if (2 * q + 1 < 9) s_t[2 * q + 1][r][c] = hi32f(acc[q]);
+    for (int k = 0; k < HD_NP; ++k) {
+      if (!live[k]) continue;
+#pragma unroll
+      for (int q = 0; q < 5; ++q) {
+        s_t[2 * q][r[k]][c[k]] = in[k] ? lo32f(acc[k][q]) : 0.f;
+        if (2 * q + 1 < 9) s_t[2 * q + 1][r[k]][c[k]] = in[k] ? hi32f(acc[k][q]) : 0.f;
+      }
     }
   }
   __syncthreads();
