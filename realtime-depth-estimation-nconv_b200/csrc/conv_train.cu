@@ -455,6 +455,82 @@ static inline int wgrad_nsplit(long long chunks, int ciblocks, int coblocks) {
   return (int)(want < 1 ? 1 : want);
 }
 
+// CO == 1, 3x3 / stride 1 / pad 1 (the C->1 depth heads, step2.py:156): the GEMM form above would spend 31 of its 32
+// output-channel rows on padding (measured 0.56 TFLOP/s, 3.2 ms per launch at 32->1 480x640).  Here the sum is
+// streamed: gw[ci][u][v] = sum_p x[ci][p] * g[p - (u-1, v-1)] — a thread takes one pixel p, loads the 3x3
+// neighbourhood of the single-channel gradient once and 8 input channels of x (coalesced), 72 FMAs; CTAs stride over
+// image rows (split-K), block-reduce their 8x9 sums and wgrad_reduce_kernel adds the partials in a fixed order.
+constexpr int W1_CIG = 8;
+__global__ void __launch_bounds__(256) conv_wgrad_co1_kernel(const float* __restrict__ g, const float* __restrict__ x,
+                                                             float* __restrict__ part, int B, int CI, int H, int W) {
+  __shared__ float s_red[8][W1_CIG * 9];
+  const int ci0 = blockIdx.y * W1_CIG;
+  float acc[W1_CIG][9];
+#pragma unroll
+  for (int j = 0; j < W1_CIG; ++j)
+#pragma unroll
+    for (int t = 0; t < 9; ++t) acc[j][t] = 0.f;
+  for (int unit = blockIdx.x; unit < B * H; unit += gridDim.x) {
+    const int b = unit / H, y = unit - b * H;
+    const float* gb = g + (size_t)b * H * W;
+    for (int xx = threadIdx.x; xx < W; xx += 256) {
+      float gn[9];
+#pragma unroll
+      for (int u = 0; u < 3; ++u)
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+          const int oy = y - (u - 1), ox = xx - (v - 1);
+          gn[u * 3 + v] = (oy >= 0 && oy < H && ox >= 0 && ox < W) ? __ldg(gb + (size_t)oy * W + ox) : 0.f;
+        }
+      float xv[W1_CIG];
+#pragma unroll
+      for (int j = 0; j < W1_CIG; ++j)
+        xv[j] = (ci0 + j < CI) ? __ldg(x + (((size_t)b * CI + ci0 + j) * H + y) * W + xx) : 0.f;
+#pragma unroll
+      for (int j = 0; j < W1_CIG; ++j)
+#pragma unroll
+        for (int t = 0; t < 9; ++t) acc[j][t] = fmaf(xv[j], gn[t], acc[j][t]);
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < W1_CIG; ++j)
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const float v = warp_sum(acc[j][t]);
+      if (lane == 0) s_red[warp][j * 9 + t] = v;
+    }
+  __syncthreads();
+  if (threadIdx.x < W1_CIG * 9) {
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v += s_red[k][threadIdx.x];
+    const int j = threadIdx.x / 9, t = threadIdx.x - j * 9;
+    if (ci0 + j < CI) part[(size_t)blockIdx.x * CI * 9 + (size_t)(ci0 + j) * 9 + t] = v;
+  }
+}
+
+static int launch_wgrad_co1(const float* g, const float* x, float* gw, void* ws, size_t ws_bytes, int B, int CI, int H,
+                            int W, cudaStream_t st) {
+  const int ciblocks = ceil_div(CI, W1_CIG);
+  int nsplit = (148 * 4 + ciblocks - 1) / ciblocks;
+  if (nsplit > B * H) nsplit = B * H;
+  if (nsplit > 512) nsplit = 512;
+  const size_t n = (size_t)CI * 9;
+  if (ws_bytes < n * nsplit * sizeof(float)) return NCONV_ERR_WORKSPACE;
+  char label[64];
+  snprintf(label, sizeof(label), "conv_wgrad k3 s1 %d->1 @%dx%d", CI, H, W);
+  {
+    LaunchScope ls(st, label, 2.0 * CI * 9 * (double)B * H * W, 4.0 * ((double)B * CI * H * W + (double)B * H * W));
+    conv_wgrad_co1_kernel<<<dim3(nsplit, ciblocks), 256, 0, st>>>(g, x, (float*)ws, B, CI, H, W);
+  }
+  {
+    LaunchScope ls(st, "wgrad_reduce", (double)n * nsplit, 4.0 * n * (nsplit + 1));
+    wgrad_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const float*)ws, gw, (int)n, nsplit);
+  }
+  return (int)cudaGetLastError();
+}
+
 template <int K, int S, int P>
 static int launch_wgrad(const float* g, const float* x, float* gw, void* ws, size_t ws_bytes, int B, int CI, int CO, int H,
                         int W, int HO, int WO, cudaStream_t st) {
@@ -497,6 +573,7 @@ extern "C" int nconv_b200_conv_wgrad(const float* g, const float* x, float* gw, 
   const int HO = (H + 2 * P - K) / S + 1, WO = (W + 2 * P - K) / S + 1;
   if (HO <= 0 || WO <= 0) return NCONV_ERR_BAD_ARG;
   cudaStream_t st = (cudaStream_t)stream;
+  if (K == 3 && S == 1 && P == 1 && CO == 1) return nconv::launch_wgrad_co1(g, x, gw, ws, ws_bytes, B, CI, H, W, st);
   if (K == 3 && S == 1 && P == 1) return nconv::launch_wgrad<3, 1, 1>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
   if (K == 3 && S == 2 && P == 1) return nconv::launch_wgrad<3, 2, 1>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);
   if (K == 1 && S == 1 && P == 0) return nconv::launch_wgrad<1, 1, 0>(g, x, gw, ws, ws_bytes, B, CI, CO, H, W, HO, WO, st);

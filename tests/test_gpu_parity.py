@@ -387,6 +387,7 @@ def _rel(a, ref):
     (16, 32, 3, 1, True, True, 2, 20, 36), (64, 64, 3, 1, True, True, 1, 15, 20), (128, 64, 3, 1, False, False, 1, 12, 70),
     (32, 64, 3, 2, False, True, 2, 16, 24), (32, 64, 1, 2, False, False, 2, 16, 24), (3, 32, 3, 1, False, True, 2, 9, 13),
     (3, 32, 1, 1, False, False, 2, 9, 13), (32, 1, 3, 1, False, False, 2, 24, 130), (1, 64, 3, 1, True, True, 1, 15, 20),
+    (64, 1, 3, 1, False, True, 2, 17, 300), (12, 1, 3, 1, False, False, 3, 5, 7),      # CO = 1: streamed weight gradient
 ])
 def test_conv_train_forward_backward_vs_fp64(cfg):
     """ops.conv_train (forward kernel + wgrad + dgrad + ReLU/bias backward, csrc/conv_train.cu) against
