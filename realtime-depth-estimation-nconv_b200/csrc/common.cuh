@@ -62,6 +62,25 @@ __device__ __forceinline__ float softplus_beta10(float x) {
 // Packed fp32 FMA (sm_100 FFMA2): acc.{lo,hi} += w.{lo,hi} * s.  ptxas folds the {s, s} pack into
 // the instruction's scalar-broadcast operand form (`FFMA2 Rd, Rw.F32x2.HI_LO, Rs.F32, Rd`), so no
 // extra register or MOV is spent on it.
+// Ampere-style asynchronous global -> shared copies; src-size 0 zero-fills the destination (out-of-image elements).
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, bool ok) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int n = ok ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, bool ok) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int n = ok ? 8 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, bool ok) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int n = ok ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+
 typedef unsigned long long u64;
 __device__ __forceinline__ void ffma2(u64& acc, u64 w, float s) {
   asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%2, %2};\n\tfma.rn.f32x2 %0, %1, t, %0;\n\t}" : "+l"(acc) : "l"(w), "f"(s));

@@ -19,6 +19,7 @@
 // fp64 through shared memory and one atomicAdd(double) per CTA), so BatchNorm statistics of the
 // un-normalised RGB activations (mean >> std) do not lose digits and results do not depend on the grid.
 #include "common.cuh"
+#include <type_traits>
 #include "nconv_b200.h"
 #include "launch_count.h"
 #include <cstdio>
@@ -315,18 +316,29 @@ struct WgradArgs {
   long long chunks;
 };
 
+template <int K, int S, int TMG>
+struct WgradCfg {
+  static constexpr int CO_B = 4 * TMG, NSUB = 256 / (TMG * WG_CIB), PXT = WG_CH / NSUB;
+  static constexpr int XC = (WG_CH - 1) * S + K;            // staged x columns
+  static constexpr int XCP = XC | 1;                        // odd row pitch: the 8 channels of a warp hit 8 distinct banks
+  static constexpr int GP = WG_CH + 1;
+  static constexpr int PER = 4 * K * K;
+  static constexpr int TILE = CO_B * GP + WG_CIB * K * XCP, RED = TMG * WG_CIB * PER;
+  static constexpr int NBUF = 2;                            // double-buffered tiles (dynamic shared memory)
+  static constexpr size_t SMEM = sizeof(float) * ((NBUF * TILE > RED) ? NBUF * TILE : RED);
+};
+
 template <int K, int S, int P, int TMG>
 __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
-  constexpr int CO_B = 4 * TMG, NSUB = 256 / (TMG * WG_CIB), PXT = WG_CH / NSUB;
-  constexpr int XC = (WG_CH - 1) * S + K;                   // staged x columns
-  constexpr int XCP = XC | 1;                               // odd row pitch: the 8 channels of a warp hit 8 distinct banks
-  constexpr int GP = WG_CH + 1;
-  constexpr int PER = 4 * K * K;
-  constexpr int TILE = CO_B * GP + WG_CIB * K * XCP, RED = TMG * WG_CIB * PER;
+  using CFG = WgradCfg<K, S, TMG>;
+  constexpr int CO_B = CFG::CO_B, NSUB = CFG::NSUB, PXT = CFG::PXT, XC = CFG::XC, XCP = CFG::XCP, GP = CFG::GP;
+  constexpr int TILE = CFG::TILE;
   static_assert(NSUB >= 1 && PXT * NSUB == WG_CH, "bad wgrad tiling");
-  __shared__ __align__(16) float s_all[TILE > RED ? TILE : RED];
-  float* s_g = s_all;
-  float* s_x = s_all + CO_B * GP;
+  // Double-buffered tiles: the copies of the CTA's next chunk are issued with cp.async before the current chunk is
+  // accumulated.  (ncu before: 42 % of the warp samples were STS instructions waiting for their global load — the
+  // staging loops were load -> store per element — and FFMA2 only 23 %.)
+  constexpr bool DB = true;
+  extern __shared__ __align__(16) float s_all[];
 
   const int tid = threadIdx.x;
   const int ci_l = tid % WG_CIB, tm = (tid / WG_CIB) % TMG, sub = tid / (WG_CIB * TMG);
@@ -348,27 +360,50 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
 #pragma unroll
     for (int t = 0; t < K * K; ++t) acc2[j][t] = 0ull;
 
-  for (long long ch = blockIdx.x; ch < a.chunks; ch += a.nsplit) {
+  // stage chunk `ch` into `tile`: ASYNC = cp.async (4-byte copies, zero-filled outside), else load + store
+  auto stage = [&](long long ch, float* tile, auto async_tag) {
+    constexpr bool ASYNC = decltype(async_tag)::value;
+    float* t_g = tile;
+    float* t_x = tile + CO_B * GP;
     const int cx = (int)(ch % a.chunks_x);
     const long long r = ch / a.chunks_x;
     const int oy = (int)(r % a.HO), b = (int)(r / a.HO);
     const int ox0 = cx * WG_CH;
-    __syncthreads();
     for (int idx = tid; idx < CO_B * WG_CH; idx += 256) {
       const int px = idx % WG_CH, co = idx / WG_CH;
-      float v = 0.f;
-      if (co0 + co < a.CO && ox0 + px < a.WO) v = __ldg(a.g + (((size_t)b * a.CO + co0 + co) * a.HO + oy) * a.WO + ox0 + px);
-      s_g[(co >> 1) * (2 * GP) + 2 * px + (co & 1)] = v;          // [co/2][px][co&1]
+      const bool ok = co0 + co < a.CO && ox0 + px < a.WO;
+      const float* src = a.g + (ok ? (((size_t)b * a.CO + co0 + co) * a.HO + oy) * a.WO + ox0 + px : 0);
+      float* dst = t_g + (co >> 1) * (2 * GP) + 2 * px + (co & 1);            // [co/2][px][co&1]
+      if constexpr (ASYNC) cp_async4(dst, src, ok); else *dst = ok ? __ldg(src) : 0.f;
     }
     for (int idx = tid; idx < WG_CIB * K * XC; idx += 256) {
       const int xc = idx % XC, u = (idx / XC) % K, cc = idx / (XC * K);
       const int iy = oy * S - P + u, ix = ox0 * S - P + xc;
-      float v = 0.f;
-      if (ci0 + cc < a.CI && iy >= 0 && iy < a.H && ix >= 0 && ix < a.W)
-        v = __ldg(a.x + (((size_t)b * a.CI + ci0 + cc) * a.H + iy) * a.W + ix);
-      s_x[(cc * K + u) * XCP + xc] = v;
+      const bool ok = ci0 + cc < a.CI && iy >= 0 && iy < a.H && ix >= 0 && ix < a.W;
+      const float* src = a.x + (ok ? (((size_t)b * a.CI + ci0 + cc) * a.H + iy) * a.W + ix : 0);
+      float* dst = t_x + (cc * K + u) * XCP + xc;
+      if constexpr (ASYNC) cp_async4(dst, src, ok); else *dst = ok ? __ldg(src) : 0.f;
     }
-    __syncthreads();
+  };
+
+  if constexpr (DB) {
+    if ((long long)blockIdx.x < a.chunks) stage(blockIdx.x, s_all, std::true_type{});
+  }
+  int it = 0;
+  for (long long ch = blockIdx.x; ch < a.chunks; ch += a.nsplit, ++it) {
+    float* tile = s_all;
+    if constexpr (DB) {
+      tile = s_all + (it & 1) * TILE;
+      cp_async_wait_all();
+      __syncthreads();            // chunk `ch` visible to all; everyone has finished the previous chunk (other buffer free)
+      if (ch + a.nsplit < a.chunks) stage(ch + a.nsplit, s_all + ((it & 1) ^ 1) * TILE, std::true_type{});
+    } else {
+      __syncthreads();
+      stage(ch, tile, std::false_type{});
+      __syncthreads();
+    }
+    const float* s_g = tile;
+    const float* s_x = tile + CO_B * GP;
     const float* gx = s_g + (2 * tm) * (2 * GP) + 2 * sub * PXT;     // pairs (4tm, 4tm+1), (4tm+2, 4tm+3)
     const float* xx = s_x + ci_l * K * XCP + sub * PXT * S;
     float win[K][K];
@@ -544,14 +579,26 @@ static int launch_wgrad(const float* g, const float* x, float* gw, void* ws, siz
   a.nsplit = wgrad_nsplit(a.chunks, ciblocks, coblocks);
   const size_t n = (size_t)CO * CI * K * K;
   if (ws_bytes < n * a.nsplit * sizeof(float)) return NCONV_ERR_WORKSPACE;
+  {
+    static bool attr_done[NCONV_MAX_DEVICES] = {};
+    int dev = 0;
+    NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
+    if (dev >= NCONV_MAX_DEVICES || !attr_done[dev]) {
+      NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(conv_wgrad_kernel<K, S, P, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)WgradCfg<K, S, 8>::SMEM));
+      NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(conv_wgrad_kernel<K, S, P, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)WgradCfg<K, S, 16>::SMEM));
+      if (dev < NCONV_MAX_DEVICES) attr_done[dev] = true;
+    }
+  }
   char label[64];
   snprintf(label, sizeof(label), "conv_wgrad k%d s%d %d->%d @%dx%d", K, S, CI, CO, H, W);
   {
     LaunchScope ls(st, label, 2.0 * CI * CO * K * K * (double)B * HO * WO,
                    4.0 * ((double)B * CI * H * W + (double)B * CO * HO * WO));
     dim3 grid(a.nsplit, ciblocks, coblocks);
-    if (small_co) conv_wgrad_kernel<K, S, P, 8><<<grid, 256, 0, st>>>(a);
-    else conv_wgrad_kernel<K, S, P, 16><<<grid, 256, 0, st>>>(a);
+    if (small_co) conv_wgrad_kernel<K, S, P, 8><<<grid, 256, WgradCfg<K, S, 8>::SMEM, st>>>(a);
+    else conv_wgrad_kernel<K, S, P, 16><<<grid, 256, WgradCfg<K, S, 16>::SMEM, st>>>(a);
   }
   {
     LaunchScope ls(st, "wgrad_reduce", (double)n * a.nsplit, 4.0 * n * (a.nsplit + 1));

@@ -16,18 +16,6 @@
 
 namespace nconv {
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, bool ok) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  const int n = ok ? 16 : 0;
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
-}
-__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, bool ok) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  const int n = ok ? 8 : 0;
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
 template <int CA, int CB, int CO, int K>
 struct PipeSmem {
   static constexpr int CI = CA + CB;
