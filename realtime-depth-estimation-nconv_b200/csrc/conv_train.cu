@@ -369,20 +369,45 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const WgradArgs a) {
     const long long r = ch / a.chunks_x;
     const int oy = (int)(r % a.HO), b = (int)(r / a.HO);
     const int ox0 = cx * WG_CH;
-    for (int idx = tid; idx < CO_B * WG_CH; idx += 256) {
-      const int px = idx % WG_CH, co = idx / WG_CH;
-      const bool ok = co0 + co < a.CO && ox0 + px < a.WO;
-      const float* src = a.g + (ok ? (((size_t)b * a.CO + co0 + co) * a.HO + oy) * a.WO + ox0 + px : 0);
-      float* dst = t_g + (co >> 1) * (2 * GP) + 2 * px + (co & 1);            // [co/2][px][co&1]
-      if constexpr (ASYNC) cp_async4(dst, src, ok); else *dst = ok ? __ldg(src) : 0.f;
+    // g tile: a thread keeps its pixel column and walks the output channels 4 apart (256 threads = 4 rows of 64 pixels):
+    // source and destination advance by constants, no division per element
+    {
+      const int px = tid % WG_CH, cb = tid / WG_CH;                 // cb in 0..3
+      const bool col_ok = ox0 + px < a.WO;
+      const size_t plane = (size_t)a.HO * a.WO;
+      const float* src = a.g + (((size_t)b * a.CO + co0 + cb) * a.HO + oy) * a.WO + ox0 + px;
+      float* dst = t_g + (cb >> 1) * (2 * GP) + 2 * px + (cb & 1);   // [co/2][px][co&1]
+#pragma unroll
+      for (int k = 0; k < CO_B / 4; ++k) {
+        const bool ok = col_ok && co0 + cb + 4 * k < a.CO;
+        if constexpr (ASYNC) cp_async4(dst, ok ? src : a.g, ok); else *dst = ok ? __ldg(src) : 0.f;
+        src += 4 * plane;
+        dst += 2 * (2 * GP);
+      }
     }
-    for (int idx = tid; idx < WG_CIB * K * XC; idx += 256) {
-      const int xc = idx % XC, u = (idx / XC) % K, cc = idx / (XC * K);
-      const int iy = oy * S - P + u, ix = ox0 * S - P + xc;
-      const bool ok = ci0 + cc < a.CI && iy >= 0 && iy < a.H && ix >= 0 && ix < a.W;
-      const float* src = a.x + (ok ? (((size_t)b * a.CI + ci0 + cc) * a.H + iy) * a.W + ix : 0);
-      float* dst = t_x + (cc * K + u) * XCP + xc;
-      if constexpr (ASYNC) cp_async4(dst, src, ok); else *dst = ok ? __ldg(src) : 0.f;
+    // x halo rows: warp w takes rows w, w+8, ... of the WG_CIB*K staged rows, lanes walk the columns
+    {
+      const int lane = tid & 31, wrp = tid >> 5;
+#pragma unroll
+      for (int i = 0; i < (WG_CIB * K + 7) / 8; ++i) {
+        const int row = wrp + 8 * i;
+        if (row >= WG_CIB * K) break;
+        const int cc = row / K, u = row - cc * K;
+        const int iy = oy * S - P + u;
+        const bool row_ok = ci0 + cc < a.CI && iy >= 0 && iy < a.H;
+        const float* srow = a.x + (row_ok ? (((size_t)b * a.CI + ci0 + cc) * a.H + iy) * a.W : 0);
+        float* drow = t_x + row * XCP;
+        const int ix0 = ox0 * S - P;
+#pragma unroll
+        for (int c = 0; c < (XC + 31) / 32; ++c) {
+          const int xc = lane + 32 * c;
+          if (xc < XC) {
+            const int ix = ix0 + xc;
+            const bool ok = row_ok && ix >= 0 && ix < a.W;
+            if constexpr (ASYNC) cp_async4(drow + xc, ok ? srow + ix : a.x, ok); else drow[xc] = ok ? __ldg(srow + ix) : 0.f;
+          }
+        }
+      }
     }
   };
 
