@@ -172,6 +172,36 @@ __global__ void __launch_bounds__(WG_THREADS, 2) nconv_wgrad_tiled(const WGradAr
     }
     // ---- stage x*c and c halo tiles for CCH input channels
     const int gx0a = ox0 - PAD - OFF, gy0 = oy0 - PAD;
+    if (a.vec_ok) {
+      // 128-bit rows (W % 4 == 0, staged columns start at a multiple of 4: a quad is entirely inside or outside the
+      // row): the loads of WS_UN slots are issued before the first is consumed, as in nconv_tiled's forward staging
+      constexpr int WSLOTS = CCH * RH * (SW / 4), WNIT = (WSLOTS + WG_THREADS - 1) / WG_THREADS, WS_UN = 3;
+#pragma unroll
+      for (int it0 = 0; it0 < WNIT; it0 += WS_UN) {
+        float4 xq[WS_UN], cq[WS_UN];
+        int so[WS_UN];
+#pragma unroll
+        for (int k = 0; k < WS_UN; ++k) {
+          const int idx = tid + (it0 + k) * WG_THREADS;
+          const int j = idx % (SW / 4), r = (idx / (SW / 4)) % RH, cc = idx / ((SW / 4) * RH);
+          const int gy_ = gy0 + r, gx_ = gx0a + 4 * j;
+          so[k] = (it0 + k < WNIT && idx < WSLOTS) ? 4 * idx : -1;            // slots are in memory order
+          const bool ok = so[k] >= 0 && gy_ >= 0 && gy_ < a.H && gx_ >= 0 && gx_ + 3 < a.W;
+          xq[k] = make_float4(0.f, 0.f, 0.f, 0.f); cq[k] = xq[k];
+          if (ok) {
+            const size_t base = ((size_t)(b * CI + ic * CCH + cc) * a.H + gy_) * a.W + gx_;
+            xq[k] = __ldg(reinterpret_cast<const float4*>(a.x + base));
+            cq[k] = __ldg(reinterpret_cast<const float4*>(a.c + base));
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < WS_UN; ++k) {
+          if (so[k] < 0) continue;
+          *reinterpret_cast<float4*>(s_xc + so[k]) = make_float4(xq[k].x * cq[k].x, xq[k].y * cq[k].y, xq[k].z * cq[k].z, xq[k].w * cq[k].w);
+          *reinterpret_cast<float4*>(s_c + so[k]) = cq[k];
+        }
+      }
+    } else
     for (int idx = tid; idx < CCH * RH * (SW / 4); idx += WG_THREADS) {
       int j = idx % (SW / 4);
       int r = (idx / (SW / 4)) % RH;
