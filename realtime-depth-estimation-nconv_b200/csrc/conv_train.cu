@@ -19,6 +19,7 @@
 // fp64 through shared memory and one atomicAdd(double) per CTA), so BatchNorm statistics of the
 // un-normalised RGB activations (mean >> std) do not lose digits and results do not depend on the grid.
 #include "common.cuh"
+#include <cstdint>
 #include <type_traits>
 #include "nconv_b200.h"
 #include "launch_count.h"
@@ -776,6 +777,83 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(const GatherArgs a) {
   }
 }
 
+// Data gradient of ConvTranspose2d(4, 2, 1) — the strided 4x4 gather of MODE 1 — specialised: per reduction channel
+// and kernel row a thread reads the 10 CONTIGUOUS gradient columns its 4 output pixels need (2 x LDG.128 + 2 scalars;
+// the generic kernel issued 16 stride-2 scalar loads for the same 128 products) and runs the products packed over
+// output-channel pairs (FFMA2).  Same thread/CTA geometry and weight chunking as conv_gather_kernel<1, ...>.
+__global__ void __launch_bounds__(256) convT_dgrad_k4s2_kernel(const GatherArgs a) {
+  __shared__ __align__(16) float s_w[16 * 8 * 8];      // [tap][rc 8][oc 8]
+  const int nob = (a.OC + 7) / 8;
+  const int z = blockIdx.z;
+  const int ob = z % nob, b = z / nob;
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int q4 = 4 * (blockIdx.x * 32 + lane), j = blockIdx.y * 8 + wrp;
+  const bool active = (j < a.OH) && (q4 < a.OW);
+  const bool vec = (a.GW % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.g) & 15) == 0) && (2 * q4 + 7 < a.GW);
+
+  u64 acc2[4][4];                                      // [oc pair][pixel]
+#pragma unroll
+  for (int o = 0; o < 4; ++o)
+#pragma unroll
+    for (int p = 0; p < 4; ++p) acc2[o][p] = 0ull;
+
+  for (int rc0 = 0; rc0 < a.RC; rc0 += 8) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < 16 * 64; idx += 256) {
+      const int o = idx & 7, r = (idx >> 3) & 7, tap = idx >> 6;
+      float v = 0.f;
+      if (rc0 + r < a.RC && ob * 8 + o < a.OC) v = __ldg(a.wt + ((size_t)tap * a.RC + rc0 + r) * a.OC + ob * 8 + o);
+      s_w[idx] = v;
+    }
+    __syncthreads();
+    if (!active) continue;
+    const int nr = min(8, a.RC - rc0);
+    for (int r = 0; r < nr; ++r) {
+      const float* gp = a.g + ((size_t)b * a.RC + rc0 + r) * a.GH * a.GW;
+#pragma unroll
+      for (int kh = 0; kh < 4; ++kh) {
+        const int gy = 2 * j - 1 + kh;
+        if (gy < 0 || gy >= a.GH) continue;
+        const float* grow = gp + (size_t)gy * a.GW;
+        const int c0 = 2 * q4 - 1;                     // column of gv[0]
+        float gv[10];
+        if (vec) {
+          const float4 m0 = __ldg(reinterpret_cast<const float4*>(grow + c0 + 1));
+          const float4 m1 = __ldg(reinterpret_cast<const float4*>(grow + c0 + 5));
+          gv[0] = (c0 >= 0) ? __ldg(grow + c0) : 0.f;
+          gv[1] = m0.x; gv[2] = m0.y; gv[3] = m0.z; gv[4] = m0.w;
+          gv[5] = m1.x; gv[6] = m1.y; gv[7] = m1.z; gv[8] = m1.w;
+          gv[9] = (c0 + 9 < a.GW) ? __ldg(grow + c0 + 9) : 0.f;
+        } else {
+#pragma unroll
+          for (int t = 0; t < 10; ++t) gv[t] = (c0 + t >= 0 && c0 + t < a.GW) ? __ldg(grow + c0 + t) : 0.f;
+        }
+#pragma unroll
+        for (int kw = 0; kw < 4; ++kw) {
+          const ulonglong2 w01 = *reinterpret_cast<const ulonglong2*>(s_w + ((kh * 4 + kw) * 8 + r) * 8);
+          const ulonglong2 w23 = *reinterpret_cast<const ulonglong2*>(s_w + ((kh * 4 + kw) * 8 + r) * 8 + 4);
+#pragma unroll
+          for (int p = 0; p < 4; ++p) {
+            const float x = gv[2 * p + kw];
+            ffma2(acc2[0][p], w01.x, x); ffma2(acc2[1][p], w01.y, x);
+            ffma2(acc2[2][p], w23.x, x); ffma2(acc2[3][p], w23.y, x);
+          }
+        }
+      }
+    }
+  }
+  if (!active) return;
+#pragma unroll
+  for (int o = 0; o < 8; ++o) {
+    const int oc = ob * 8 + o;
+    if (oc >= a.OC) break;
+    float* orow = a.out + (((size_t)b * a.OC + oc) * a.OH + j) * a.OW;
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+      if (q4 + p < a.OW) orow[q4 + p] = (o & 1) ? hi32f(acc2[o >> 1][p]) : lo32f(acc2[o >> 1][p]);
+  }
+}
+
 // W[co][ci][u][v] -> W'[ci][co][K-1-u][K-1-v]
 __global__ void wflip_kernel(const float* __restrict__ w, float* __restrict__ wf, int CO, int CI, int K) {
   const int KK = K * K, total = CO * CI * KK;
@@ -815,7 +893,7 @@ extern "C" int nconv_b200_conv_dgrad_gather(const float* g, const float* w, floa
     const double taps = transposed ? (double)KK : (double)KK / (S * S);
     LaunchScope ls(st, label, 2.0 * CI * CO * taps * (double)B * H * W,
                    4.0 * ((double)B * CO * a.GH * a.GW + (double)B * CI * H * W));
-    if (transposed && K == 4 && S == 2 && P == 1) conv_gather_kernel<1, 4, 2, 1><<<grid, 256, 0, st>>>(a);
+    if (transposed && K == 4 && S == 2 && P == 1) convT_dgrad_k4s2_kernel<<<grid, 256, 0, st>>>(a);
     else if (transposed) conv_gather_kernel<1, 0, 0, 0><<<grid, 256, 0, st>>>(a);
     else if (K == 3 && S == 2 && P == 1) conv_gather_kernel<0, 3, 2, 1><<<grid, 256, 0, st>>>(a);
     else if (K == 1 && S == 2 && P == 0) conv_gather_kernel<0, 1, 2, 0><<<grid, 256, 0, st>>>(a);
