@@ -264,9 +264,12 @@ struct ConvTArgs {
   int B, CA, CB, CO, H, W, relu;
 };
 
+constexpr int TT_W_FLOATS = TT_CCH * 16 * TT_CO, TT_IN_FLOATS = TT_CCH * (TT_TH + 2) * TT_SW;
+constexpr int TT_BUF_FLOATS = TT_W_FLOATS + TT_IN_FLOATS;
+constexpr size_t TT_SMEM = sizeof(float) * 2 * TT_BUF_FLOATS;      // double-buffered chunks
+
 __global__ void __launch_bounds__(256, 2) convT4x4s2_kernel(const ConvTArgs a) {
-  __shared__ __align__(16) float s_w[TT_CCH * 16 * TT_CO];
-  __shared__ float s_in[TT_CCH][TT_TH + 2][TT_SW];
+  extern __shared__ __align__(16) float tt_smem[];   // 2 x { weights [CCH][16][CO] | inputs [CCH][TH+2][SW] }
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int NG = a.CO / TT_CO;
@@ -282,15 +285,17 @@ __global__ void __launch_bounds__(256, 2) convT4x4s2_kernel(const ConvTArgs a) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) acc[o][r][q] = 0.f;
 
-#pragma unroll 1
-  for (int c0 = 0; c0 < CI; c0 += TT_CCH) {
+  // the chunk of channels [c0, c0+CCH) is copied global -> shared with cp.async (4-byte copies: the halo starts at
+  // column b0-1; zero-filled outside the image) one chunk ahead of the FMA loop
+  auto stage = [&](int c0, float* buf) {
+    float* b_w = buf;
+    float* b_in = buf + TT_W_FLOATS;
     const int nch = min(TT_CCH, CI - c0);
-    __syncthreads();
     for (int idx = tid; idx < nch * 16 * TT_CO; idx += 256) {
       int o = idx % TT_CO;
       int tap = (idx / TT_CO) % 16;
       int cc = idx / (TT_CO * 16);
-      s_w[idx] = __ldg(&a.w[((size_t)(c0 + cc) * a.CO + cog * TT_CO + o) * 16 + tap]);
+      cp_async4(b_w + idx, &a.w[((size_t)(c0 + cc) * a.CO + cog * TT_CO + o) * 16 + tap], true);
     }
     for (int idx = tid; idx < nch * (TT_TH + 2) * TT_SW; idx += 256) {
       int j = idx % TT_SW;
@@ -298,14 +303,26 @@ __global__ void __launch_bounds__(256, 2) convT4x4s2_kernel(const ConvTArgs a) {
       int cc = idx / (TT_SW * (TT_TH + 2));
       int cs = c0 + cc;
       int gy = a0 - 1 + r, gx = b0 - 1 + j;
-      float v = 0.f;
-      if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
-        v = (cs < a.CA) ? __ldg(a.a + ((size_t)(b * a.CA + cs) * a.H + gy) * a.W + gx)
-                        : __ldg(a.b + ((size_t)(b * a.CB + cs - a.CA) * a.H + gy) * a.W + gx);
-      }
-      s_in[cc][r][j] = v;
+      const bool ok = gy >= 0 && gy < a.H && gx >= 0 && gx < a.W;
+      const float* src = a.a;
+      if (ok)
+        src = (cs < a.CA) ? a.a + ((size_t)(b * a.CA + cs) * a.H + gy) * a.W + gx
+                          : a.b + ((size_t)(b * a.CB + cs - a.CA) * a.H + gy) * a.W + gx;
+      cp_async4(b_in + idx, src, ok);                   // [cc][r][j] is idx in memory order
     }
-    __syncthreads();
+  };
+
+  stage(0, tt_smem);
+  int it = 0;
+#pragma unroll 1
+  for (int c0 = 0; c0 < CI; c0 += TT_CCH, ++it) {
+    const int nch = min(TT_CCH, CI - c0);
+    float* buf = tt_smem + (it & 1) * TT_BUF_FLOATS;
+    cp_async_wait_all();
+    __syncthreads();                 // chunk visible to all; everyone is done with the other buffer
+    if (c0 + TT_CCH < CI) stage(c0 + TT_CCH, tt_smem + ((it & 1) ^ 1) * TT_BUF_FLOATS);
+    const float* s_w = buf;
+    const float (*s_in)[TT_TH + 2][TT_SW] = reinterpret_cast<const float (*)[TT_TH + 2][TT_SW]>(buf + TT_W_FLOATS);
 #pragma unroll 1
     for (int cc = 0; cc < nch; ++cc) {
       float in[3][4];  // rows a-1..a+1, cols b-1..b+2 (b = b0 + 2*tx)
@@ -409,7 +426,14 @@ extern "C" int nconv_b200_convT4x4s2_fwd(const float* a, const float* b, const f
     const double pin = (double)B * H * W;
     LaunchScope ls((cudaStream_t)stream, label, 2.0 * (CA + CB) * CO * 16 * pin,
                    4.0 * ((CA + CB) * pin + 4.0 * CO * pin));
-    convT4x4s2_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t);
+    static bool attr_done[NCONV_MAX_DEVICES] = {};
+    int dev = 0;
+    NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
+    if (dev >= NCONV_MAX_DEVICES || !attr_done[dev]) {
+      NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(convT4x4s2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TT_SMEM));
+      if (dev < NCONV_MAX_DEVICES) attr_done[dev] = true;
+    }
+    convT4x4s2_kernel<<<grid, 256, TT_SMEM, (cudaStream_t)stream>>>(t);
   }
   return (int)cudaGetLastError();
 }
