@@ -24,6 +24,7 @@
 #include "nconv_b200.h"
 #include "launch_count.h"
 #include <cstdio>
+#include <cstdlib>
 
 namespace nconv {
 
@@ -854,6 +855,120 @@ __global__ void __launch_bounds__(256) convT_dgrad_k4s2_kernel(const GatherArgs 
   }
 }
 
+// Data gradient of Conv2d(3, 2, 1) specialised.  conv_gather_kernel<0,3,2,1> runs one CTA per output phase: the four
+// phases carry 1/2/2/4 taps (unbalanced CTAs), and each writes every second column (half-used sectors).  Here a thread
+// owns a gradient row j and 2 gradient columns q2, q2+1 and produces ALL four phases under them — output rows 2j, 2j+1 x
+// columns 2q2 .. 2q2+3 x 8 oc — from the 2 x 3 gradient values g[j..j+1][q2..q2+2] (LDG.64 + LDG.32 per row, prefetched
+// one reduction channel ahead); the 9 taps run as FFMA2 over oc pairs and the results leave as one STG.128 per row.
+//   row 2j   <- (u=1, g row j);   row 2j+1   <- (u=2, g row j), (u=0, g row j+1);   columns alike with v / q.
+__global__ void __launch_bounds__(256) conv_dgrad_k3s2_kernel(const GatherArgs a) {
+  __shared__ __align__(16) float s_w[9 * 8 * 8];       // [tap][rc 8][oc 8]
+  const int nob = (a.OC + 7) / 8;
+  const int z = blockIdx.z;
+  const int ob = z % nob, b = z / nob;
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int q2 = 2 * (blockIdx.x * 32 + lane), j = blockIdx.y * 8 + wrp;
+  const bool active = (j < a.GH) && (2 * j < a.OH) && (q2 < a.GW) && (2 * q2 < a.OW);
+  const bool vec2 = (a.GW % 2 == 0) && ((reinterpret_cast<uintptr_t>(a.g) & 7) == 0) && (q2 + 1 < a.GW);
+  const bool row1 = (j + 1 < a.GH);
+  const bool col2 = (q2 + 2 < a.GW);
+
+  u64 acc2[2][4][4];                                   // [output row][output column][oc pair]
+#pragma unroll
+  for (int y = 0; y < 2; ++y)
+#pragma unroll
+    for (int x = 0; x < 4; ++x)
+#pragma unroll
+      for (int o = 0; o < 4; ++o) acc2[y][x][o] = 0ull;
+
+  auto load6 = [&](const float* gp, float (&G)[2][3]) {
+    const float* r0 = gp + (size_t)j * a.GW + q2;
+    if (vec2) {
+      const float2 m = __ldg(reinterpret_cast<const float2*>(r0));
+      G[0][0] = m.x; G[0][1] = m.y;
+    } else {
+      G[0][0] = __ldg(r0); G[0][1] = (q2 + 1 < a.GW) ? __ldg(r0 + 1) : 0.f;
+    }
+    G[0][2] = col2 ? __ldg(r0 + 2) : 0.f;
+    if (row1) {
+      const float* r1 = r0 + a.GW;
+      if (vec2) {
+        const float2 m = __ldg(reinterpret_cast<const float2*>(r1));
+        G[1][0] = m.x; G[1][1] = m.y;
+      } else {
+        G[1][0] = __ldg(r1); G[1][1] = (q2 + 1 < a.GW) ? __ldg(r1 + 1) : 0.f;
+      }
+      G[1][2] = col2 ? __ldg(r1 + 2) : 0.f;
+    } else {
+      G[1][0] = G[1][1] = G[1][2] = 0.f;
+    }
+  };
+
+  const size_t plane = (size_t)a.GH * a.GW;
+  for (int rc0 = 0; rc0 < a.RC; rc0 += 8) {
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < 9 * 64; idx += 256) {
+      const int o = idx & 7, r = (idx >> 3) & 7, tap = idx >> 6;
+      float v = 0.f;
+      if (rc0 + r < a.RC && ob * 8 + o < a.OC) v = __ldg(a.wt + ((size_t)tap * a.RC + rc0 + r) * a.OC + ob * 8 + o);
+      s_w[idx] = v;
+    }
+    __syncthreads();
+    if (!active) continue;
+    const int nr = min(8, a.RC - rc0);
+    const float* gp = a.g + ((size_t)b * a.RC + rc0) * plane;
+    float G[2][3], Gn[2][3];
+    load6(gp, G);
+    for (int r = 0; r < nr; ++r) {
+      if (r + 1 < nr) load6(gp + (size_t)(r + 1) * plane, Gn);
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int y = (u == 1) ? 0 : 1, gr = (u == 0) ? 1 : 0;
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+          const int xo = (v == 1) ? 0 : 1, gc = (v == 0) ? 1 : 0;
+          const ulonglong2 w01 = *reinterpret_cast<const ulonglong2*>(s_w + ((u * 3 + v) * 8 + r) * 8);
+          const ulonglong2 w23 = *reinterpret_cast<const ulonglong2*>(s_w + ((u * 3 + v) * 8 + r) * 8 + 4);
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const float x = G[gr][c + gc];
+            ffma2(acc2[y][2 * c + xo][0], w01.x, x); ffma2(acc2[y][2 * c + xo][1], w01.y, x);
+            ffma2(acc2[y][2 * c + xo][2], w23.x, x); ffma2(acc2[y][2 * c + xo][3], w23.y, x);
+          }
+        }
+      }
+#pragma unroll
+      for (int y = 0; y < 2; ++y)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) G[y][c] = Gn[y][c];
+    }
+  }
+  if (!active) return;
+  const int ix0 = 2 * q2;
+  const bool st4 = (a.OW % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.out) & 15) == 0) && (ix0 + 3 < a.OW);
+#pragma unroll
+  for (int o = 0; o < 8; ++o) {
+    const int oc = ob * 8 + o;
+    if (oc >= a.OC) break;
+#pragma unroll
+    for (int y = 0; y < 2; ++y) {
+      const int iy = 2 * j + y;
+      if (iy >= a.OH) break;
+      float* orow = a.out + (((size_t)b * a.OC + oc) * a.OH + iy) * a.OW + ix0;
+      float r4[4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x) r4[x] = (o & 1) ? hi32f(acc2[y][x][o >> 1]) : lo32f(acc2[y][x][o >> 1]);
+      if (st4) {
+        *reinterpret_cast<float4*>(orow) = make_float4(r4[0], r4[1], r4[2], r4[3]);
+      } else {
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+          if (ix0 + x < a.OW) orow[x] = r4[x];
+      }
+    }
+  }
+}
+
 // W[co][ci][u][v] -> W'[ci][co][K-1-u][K-1-v]
 __global__ void wflip_kernel(const float* __restrict__ w, float* __restrict__ wf, int CO, int CI, int K) {
   const int KK = K * K, total = CO * CI * KK;
@@ -895,6 +1010,10 @@ extern "C" int nconv_b200_conv_dgrad_gather(const float* g, const float* w, floa
                    4.0 * ((double)B * CO * a.GH * a.GW + (double)B * CI * H * W));
     if (transposed && K == 4 && S == 2 && P == 1) convT_dgrad_k4s2_kernel<<<grid, 256, 0, st>>>(a);
     else if (transposed) conv_gather_kernel<1, 0, 0, 0><<<grid, 256, 0, st>>>(a);
+    else if (K == 3 && S == 2 && P == 1 && getenv("NCONV_B200_DGRAD_K3S2")) {     // opt-in until measured on the GPU
+      dim3 g2(nconv::ceil_div(nconv::ceil_div(a.GW, 2), 32), nconv::ceil_div(a.GH, 8), B * ((CI + 7) / 8));
+      conv_dgrad_k3s2_kernel<<<g2, 256, 0, st>>>(a);
+    }
     else if (K == 3 && S == 2 && P == 1) conv_gather_kernel<0, 3, 2, 1><<<grid, 256, 0, st>>>(a);
     else if (K == 1 && S == 2 && P == 0) conv_gather_kernel<0, 1, 2, 0><<<grid, 256, 0, st>>>(a);
     else conv_gather_kernel<0, 0, 0, 0><<<grid, 256, 0, st>>>(a);
