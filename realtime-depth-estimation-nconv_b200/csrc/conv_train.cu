@@ -1010,7 +1010,7 @@ extern "C" int nconv_b200_conv_dgrad_gather(const float* g, const float* w, floa
                    4.0 * ((double)B * CO * a.GH * a.GW + (double)B * CI * H * W));
     if (transposed && K == 4 && S == 2 && P == 1) convT_dgrad_k4s2_kernel<<<grid, 256, 0, st>>>(a);
     else if (transposed) conv_gather_kernel<1, 0, 0, 0><<<grid, 256, 0, st>>>(a);
-    else if (K == 3 && S == 2 && P == 1 && getenv("NCONV_B200_DGRAD_K3S2")) {     // opt-in until measured on the GPU
+    else if (K == 3 && S == 2 && P == 1 && !getenv("NCONV_B200_DGRAD_PHASED")) {
       dim3 g2(nconv::ceil_div(nconv::ceil_div(a.GW, 2), 32), nconv::ceil_div(a.GH, 8), B * ((CI + 7) / 8));
       conv_dgrad_k3s2_kernel<<<g2, 256, 0, st>>>(a);
     }

@@ -388,6 +388,8 @@ def _rel(a, ref):
     (32, 64, 3, 2, False, True, 2, 16, 24), (32, 64, 1, 2, False, False, 2, 16, 24), (3, 32, 3, 1, False, True, 2, 9, 13),
     (3, 32, 1, 1, False, False, 2, 9, 13), (32, 1, 3, 1, False, False, 2, 24, 130), (1, 64, 3, 1, True, True, 1, 15, 20),
     (64, 1, 3, 1, False, True, 2, 17, 300), (12, 1, 3, 1, False, False, 3, 5, 7),      # CO = 1: streamed weight gradient
+    # stride-2 data gradient (conv_dgrad_k3s2_kernel): odd sizes, a ragged channel block, vector and scalar stores
+    (3, 32, 3, 2, True, True, 2, 15, 21), (16, 16, 3, 2, True, True, 2, 32, 264),
 ])
 def test_conv_train_forward_backward_vs_fp64(cfg):
     """ops.conv_train (forward kernel + wgrad + dgrad + ReLU/bias backward, csrc/conv_train.cu) against
