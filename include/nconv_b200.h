@@ -112,8 +112,9 @@ int nconv_b200_upcat_bwd(const float* gout, float* gskip, float* glow, int B, in
 
 /* ---- (a4-a8) whole DNET.forward, inference — step1.py:51-94 ----------------------------
  * params: 18 pointers {w,b} for nconv1,nconv2,nconv_down1..3,nconv4,nconv5,nconv6,nconv7.
- * S: [B,1,H,W] -> out: [B,1,H,W] (crop generalised to [1:H+1,1:W+1]).
- * conf_out (optional, may be NULL): [B,1,H,W] confidence of the last layer, same crop. */
+ * S: [B,1,H,W] -> out: [B,1,H,W] (crop generalised to [1:H+1,1:W+1]).  The last layer's confidence
+ * is dropped as in the reference (step1.py:92-94); the opt-in (depth, confidence) return goes
+ * through the staged ops (models/step1.py::SETP1_NCONV.forward_with_confidence). */
 size_t nconv_b200_dnet_workspace_bytes(int B, int H, int W);
 int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out, int B, int H,
                             int W, void* workspace, size_t workspace_bytes, void* stream);

@@ -22,7 +22,7 @@ from torch.nn.modules.conv import _ConvNd
 
 from nconv_b200 import ops as _ops  # noqa: F401  (registers torch.ops.nconv_b200.*)
 
-_K = torch.ops.nconv_b200
+_K = _ops.K          # torch.ops.nconv_b200 (ATen restatements while a TorchScript trace is recorded: nconv_b200/export.py)
 
 
 class SETP1_NCONV(nn.Module):

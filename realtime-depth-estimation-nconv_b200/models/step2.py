@@ -24,6 +24,7 @@ the analytic forward+backward kernels of csrc/conv_train.cu (`ops.conv_train`, `
 from __future__ import annotations
 
 import math
+import threading
 from collections import OrderedDict
 
 import torch
@@ -32,7 +33,7 @@ import torch.nn as nn
 from nconv_b200 import ops as _ops  # noqa: F401
 from models.step1 import SETP1_NCONV
 
-_K = torch.ops.nconv_b200
+_K = _ops.K          # torch.ops.nconv_b200 (ATen restatements while a TorchScript trace is recorded: nconv_b200/export.py)
 
 
 def _recording(x, *params) -> bool:
@@ -48,6 +49,18 @@ def _fold(bn: nn.BatchNorm2d, conv_bias):
     if bn.training:
         raise RuntimeError("internal: eval-mode BatchNorm fold requested for a BatchNorm in training mode")
     return _K.bn_fold(bn.weight, bn.bias, bn.running_mean, bn.running_var, conv_bias, float(bn.eps))
+
+
+def _fold_recording(bn: nn.BatchNorm2d, conv_bias):
+    """Eval-mode BatchNorm as a per-channel affine (scale, shift) computed with autograd recording, so that a
+    frozen-statistics BatchNorm (model.eval() without no_grad, or fine-tuning with BN in eval mode) still passes
+    gradients to gamma / beta / the conv bias.  [C]-sized parameter arithmetic only; the activations go through the
+    library's kernels with the affine folded into the conv weights."""
+    scale = bn.weight * torch.rsqrt(bn.running_var + bn.eps)
+    shift = bn.bias - bn.running_mean * scale
+    if conv_bias is not None:
+        shift = shift + conv_bias * scale
+    return scale, shift
 
 
 def _interp_size(n: int, factor) -> int:
@@ -106,7 +119,10 @@ class SETP2_BP_EXPORT(nn.Module):
     def forward(self, rgb0, depth0, rgb1, depth1):
         depths, B = _setp2_trunk(self, rgb0, depth0, rgb1, depth1)
         out = depths[3]
-        _K.zero_border_(out, 45, 45, 20)          # step2.py:122-124
+        if _ops.exporting():
+            out = _K.border_zeroed(out, 45, 45, 20)      # functional form for graph capture
+        else:
+            _K.zero_border_(out, 45, 45, 20)             # step2.py:122-124
         return out[:B], out[B:]
 
 
@@ -136,6 +152,8 @@ def _setp2_trunk(m, rgb0, depth0, rgb1, depth1):
 # stride-2 encoders read phase-split copies); otherwise the exact-fp32 CUDA-core path above runs.
 # ---------------------------------------------------------------------------------------------
 def _tc_eligible(m, rgb) -> bool:
+    if _ops.exporting():
+        return False          # graph capture records the op-level path (decomposable; P8 workspaces are runtime state)
     if torch.is_grad_enabled() and (rgb.requires_grad or any(p.requires_grad for p in m.parameters())):
         return False
     if any(bn.training for bn in _stack_bns(m)):
@@ -150,15 +168,46 @@ def _stack_bns(m):
             if isinstance(sub, nn.BatchNorm2d) and not name.startswith(("step1.", "rgb_encoder4"))]
 
 
-_WS = {}      # (device index, 2B, H, W) -> dict of P8 activation buffers (rings zeroed once; kernels write interiors only)
-_PACK = {}    # id(module) -> (version key, packed weights / folded BN)
+class _Runtime:
+    """Per-module cache of derived device data for the tensor-core trunk: P8 activation workspaces and packed
+    split-bf16 weights / folded BatchNorm.  It hangs off the module instance (`m.__dict__`), not the process:
+      * keyed by device index inside, so nn.DataParallel replicas (shallow copies of the module made by
+        `replicate`, one thread per device: train_step1.py:153, train_step2.py:135) each use their own device's
+        entry and never evict another device's workspace; a lock guards the dict mutations;
+      * one live activation shape per device (the footprint at B = 32 is ~22 GB);
+      * never part of `state_dict()`, and `copy.deepcopy(model)` (train_step1.py:98) / pickling get a fresh,
+        empty cache instead of a copy of 22 GB of scratch."""
+
+    def __init__(self):
+        self.lock = threading.Lock()
+        self.ws = {}       # device index -> ((N, H, W), dict of P8 buffers)
+        self.pack = {}     # device index -> (version key, packed weights / folded BN)
+
+    def __deepcopy__(self, memo):
+        return _Runtime()
+
+    def __reduce__(self):
+        return (_Runtime, ())
 
 
-def _workspace(dev, N, H, W):
-    key = (dev.index, N, H, W)
-    ws = _WS.get(key)
-    if ws is not None:
-        return ws
+def _runtime(m) -> _Runtime:
+    rt = m.__dict__.get("_nconv_rt")
+    if rt is None:
+        rt = m.__dict__.setdefault("_nconv_rt", _Runtime())
+    return rt
+
+
+def _workspace(m, dev, N, H, W):
+    """P8 activation buffers of the trunk for this module on this device (rings zeroed once; kernels write
+    interiors only)."""
+    rt = _runtime(m)
+    key = (N, H, W)
+    with rt.lock:
+        hit = rt.ws.get(dev.index)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    with rt.lock:
+        rt.ws.pop(dev.index, None)           # release this device's previous shape before allocating the next
     P8 = _ops.P8
     ws = {}
     ws["r0"] = P8.empty(N, 32, H, W, dev, with_q=True)
@@ -177,17 +226,21 @@ def _workspace(dev, N, H, W):
         ws["f%d" % lvl] = P8.empty(N, Co, h, w, dev)
         if lvl < 3:
             ws["d8_%d" % lvl] = P8.empty(N, 1, h, w, dev)
-    _WS.clear()               # one live shape per process keeps the footprint bounded
-    _WS[key] = ws
+    with rt.lock:
+        rt.ws[dev.index] = (key, ws)
     return ws
 
 
-def _packed(m):
-    """Packed split-bf16 weights and folded BatchNorm scale/shift, rebuilt when any parameter or
-    running statistic changes (tensor version counters)."""
+def _packed(m, dev):
+    """Packed split-bf16 weights and folded BatchNorm scale/shift of this module on this device, rebuilt when any
+    parameter or running statistic changes: the key is every tensor's (data_ptr, version counter) plus the
+    library's mutation epoch (kernels that update parameters or running statistics through raw pointers —
+    fused AdamW, BatchNorm batch statistics — bump it; `load_state_dict` / in-place torch ops bump versions)."""
+    rt = _runtime(m)
     tensors = [t for n, t in list(m.named_parameters()) + list(m.named_buffers()) if not n.startswith("step1.")]
-    key = tuple((t.data_ptr(), t._version) for t in tensors)
-    hit = _PACK.get(id(m))
+    key = (_ops.mutation_epoch(),) + tuple((t.data_ptr(), t._version) for t in tensors)
+    with rt.lock:
+        hit = rt.pack.get(dev.index)
     if hit is not None and hit[0] == key:
         return hit[1]
     pk = {}
@@ -210,15 +263,16 @@ def _packed(m):
         pk["fc1_%d" % lvl] = _ops.tc_pack_weights(S1, fz.fuse_conv1.conv.weight, C, C)
         pk["fc2_%d" % lvl] = _ops.tc_pack_weights(S1, fz.fuse_conv2.conv.weight, C, 0)
         pk["fc3_%d" % lvl] = _ops.tc_pack_weights(S1, fz.fuse_conv3.conv.weight, fz.fuse_conv3.conv.in_channels, 0)
-    _PACK[id(m)] = (key, pk)
+    with rt.lock:
+        rt.pack[dev.index] = (key, pk)
     return pk
 
 
 def _setp2_trunk_tc(m, rgb, sparse):
     N, _, H, W = rgb.shape
     dev = rgb.device
-    ws = _workspace(dev, N, H, W)
-    pk = _packed(m)
+    ws = _workspace(m, dev, N, H, W)
+    pk = _packed(m, dev)
     S1, S2, TT = _ops.TC_S1, _ops.TC_S2, _ops.TC_T
     conv_tc, small, head = _ops.conv_tc, _ops.conv_small_p8, _ops.head_p8
 
@@ -285,8 +339,10 @@ class RGBEncoder(nn.Module):
             z = _ops.conv_train(x, conv.weight, conv.bias, None, self.stride, False)
             r = _ops.conv_train(x, w1, None, None, self.stride, False)
             return _ops.bn_train(z, bn, residual=r, relu=True)
-        if _recording(x, conv.weight, w1):
-            raise NotImplementedError("RGBEncoder: gradients through an eval-mode BatchNorm are not implemented")
+        if _recording(x, conv.weight, w1, bn.weight):
+            scale, shift = _fold_recording(bn, conv.bias)
+            t = _ops.conv_train(x, conv.weight * scale.view(-1, 1, 1, 1), shift, None, self.stride, True)
+            return _ops.conv_train(x, w1, None, t, self.stride, False)
         scale, shift = _fold(bn, conv.bias)
         t = _K.conv2d(x, None, conv.weight, scale, shift, None, self.stride, True)
         return _K.conv2d(x, None, w1, None, None, t, self.stride, False)
@@ -318,7 +374,8 @@ class Basic2d(nn.Module):
             return _ops.bn_train(z, self.conv.bn, relu=self._relu)
         if _recording(x, conv.weight, conv.bias) or (x2 is not None and x2.requires_grad and torch.is_grad_enabled()):
             if has_bn:
-                raise NotImplementedError("Basic2d: gradients through an eval-mode BatchNorm are not implemented")
+                scale, shift = _fold_recording(self.conv.bn, conv.bias)
+                return _ops.conv_train(_cat(x, x2), conv.weight * scale.view(-1, 1, 1, 1), shift, None, stride, self._relu)
             return _ops.conv_train(_cat(x, x2), conv.weight, conv.bias, None, stride, self._relu)
         if has_bn:
             scale, shift = _fold(self.conv.bn, conv.bias)
@@ -351,7 +408,10 @@ class Basic2dTrans(nn.Module):
                 raise NotImplementedError("Basic2dTrans: bias together with a norm layer is not a layer of this stack")
             return _ops.bn_train(_ops.convT_train(_cat(x, x2), self.conv.weight), self.bn, relu=True)
         if _recording(x, self.conv.weight) or (x2 is not None and x2.requires_grad and torch.is_grad_enabled()):
-            raise NotImplementedError("Basic2dTrans: gradients need the BatchNorm in training mode")
+            if is_bn:
+                scale, shift = _fold_recording(self.bn, self.conv.bias)
+                return _ops.convT_train(_cat(x, x2), self.conv.weight * scale.view(1, -1, 1, 1), shift, True)
+            return _ops.convT_train(_cat(x, x2), self.conv.weight, self.conv.bias, True)
         if is_bn:
             scale, shift = _fold(self.bn, self.conv.bias)
         else:

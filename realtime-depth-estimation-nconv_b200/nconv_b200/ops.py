@@ -7,6 +7,7 @@ Schemas live in the `nconv_b200` namespace:  torch.ops.nconv_b200.<op>.
 from __future__ import annotations
 
 import ctypes
+import threading
 from ctypes import byref, c_void_p
 from typing import List, Optional, Sequence, Tuple
 
@@ -46,6 +47,33 @@ def _define(schema: str, impl, fake=None):
     _LIB.impl(name, impl, "CUDA")
     if fake is not None:
         torch.library.register_fake("nconv_b200::" + name, fake)
+
+
+def exporting() -> bool:
+    """True while a graph of the model is being captured for export (torch.export / torch.onnx.export / jit trace):
+    the models then take the op-level path (no P8 workspaces, no in-place output edits)."""
+    if torch.jit.is_tracing() or torch.onnx.is_in_onnx_export():
+        return True
+    c = torch.compiler
+    return bool(getattr(c, "is_exporting", lambda: False)() or c.is_compiling())
+
+
+class _OpNamespace:
+    """`torch.ops.nconv_b200`, except while a TorchScript trace is being recorded (torch.onnx.export(dynamo=False),
+    torch.jit.trace): the tracer cannot look inside a ctypes launch, so the op names then resolve to their ATen
+    restatements in nconv_b200/export.py and the trace records plain ATen nodes.  torch.export keeps the custom ops
+    as opaque nodes and decomposes them afterwards (export.export_decomposed)."""
+
+    def __getattr__(self, name):
+        if torch.jit.is_tracing() or torch.onnx.is_in_onnx_export():
+            from . import export as _export
+            fn = _export.ATEN.get(name)
+            if fn is not None:
+                return fn
+        return getattr(torch.ops.nconv_b200, name)
+
+
+K = _OpNamespace()
 
 
 # --------------------------------------------------------------------------------------
@@ -269,7 +297,7 @@ def _dnet_forward(S, params: Sequence[torch.Tensor]):
     if B == 0:
         return out
     nbytes = int(_C.nconv_b200_dnet_workspace_bytes(B, H, W))
-    ws = torch.empty(nbytes, device=S.device, dtype=torch.uint8)
+    ws = _scratch(S.device, nbytes, "dnet")          # cached per (device, stream): 3.9 GB at B = 32, 480x640
     arr = (c_void_p * 18)(*[p.data_ptr() for p in params])
     with torch.cuda.device(S.device):
         check(_C.nconv_b200_dnet_forward(_p(S), arr, _p(out), B, H, W, _p(ws), nbytes, _stream(S)), "dnet_forward")
@@ -364,6 +392,18 @@ def _zero_border_(x, top: int, bottom: int, left: int) -> None:
 
 _define("zero_border_(Tensor(a!) x, int top, int bottom, int left) -> ()", _zero_border_,
         lambda x, top, bottom, left: None)
+
+
+def _border_zeroed(x, top: int, bottom: int, left: int):
+    """Functional form of zero_border_ (a copy with rows [:top], [-bottom:] and columns [:left] zero): what the
+    EXPORT forward records under torch.export / ONNX tracing, where an in-place op on a graph output is unwelcome."""
+    y = _prep(x, "x").clone()
+    _zero_border_(y, top, bottom, left)
+    return y
+
+
+_define("border_zeroed(Tensor x, int top, int bottom, int left) -> Tensor", _border_zeroed,
+        lambda x, top, bottom, left: torch.empty_like(x))
 
 
 def _bn_fold(gamma, beta, mean, var, conv_bias, eps: float):
@@ -505,16 +545,19 @@ def launch_count() -> int:
 # (csrc/conv_train.cu; the reference differentiates step2.py with autograd under model.train())
 # --------------------------------------------------------------------------------------
 _SCRATCH = {}
+_SCRATCH_LOCK = threading.Lock()
 
 
-def _scratch(dev, nbytes: int):
-    """Grow-only per-device scratch (fp64 channel sums, split-K partials, re-packed weights).  Kernels
-    using it are ordered on the current stream, so one buffer per purpose and device is enough."""
-    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
-    t = _SCRATCH.get(key)
-    if t is None or t.numel() < nbytes:
-        t = torch.empty(max(int(nbytes), 1 << 20), device=dev, dtype=torch.uint8)
-        _SCRATCH[key] = t
+def _scratch(dev, nbytes: int, tag: str = "train"):
+    """Grow-only scratch per (device, stream, purpose) (fp64 channel sums, split-K partials, re-packed weights,
+    the SETP1 activation workspace).  Kernels using one are ordered on that stream, so reuse is safe; the dict is
+    guarded because nn.DataParallel runs one thread per device."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream, tag)
+    with _SCRATCH_LOCK:
+        t = _SCRATCH.get(key)
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(max(int(nbytes), 1 << 20), device=dev, dtype=torch.uint8)
+            _SCRATCH[key] = t
     return t
 
 
@@ -602,27 +645,36 @@ def conv_train(x, weight, bias=None, residual=None, stride=1, relu=False):
 
 
 class _ConvTTrain(torch.autograd.Function):
-    """ConvTranspose2d(k=4, s=2, p=1, bias=False) (Basic2dTrans, step2.py:205) with the analytic backward."""
+    """[ReLU](ConvTranspose2d(k=4, s=2, p=1)(x, w) [+ bias]) (Basic2dTrans, step2.py:197-214) with the analytic
+    backward.  The reference's layer has no bias and no activation of its own (BatchNorm + ReLU follow, :208-213);
+    bias + ReLU serve the frozen-BatchNorm case, where the eval-mode BatchNorm is a per-channel affine folded into
+    the weights and this bias."""
 
     @staticmethod
-    def forward(ctx, x, weight):
-        x = _prep(x, "x"); weight = _prep(weight, "weight")
+    def forward(ctx, x, weight, bias, relu):
+        x = _prep(x, "x"); weight = _prep(weight, "weight"); bias = _prep_opt(bias, "bias")
         B, CI, H, W = x.shape
         CO = weight.shape[1]
         y = torch.empty((B, CO, 2 * H, 2 * W), device=x.device, dtype=torch.float32)
         with torch.cuda.device(x.device):
-            check(_C.nconv_b200_convT4x4s2_fwd(_p(x), None, _p(weight), None, None, _p(y), B, CI, 0, CO, H, W, 0,
+            check(_C.nconv_b200_convT4x4s2_fwd(_p(x), None, _p(weight), None, _p(bias), _p(y), B, CI, 0, CO, H, W, int(relu),
                                                _stream(x)), "convT4x4s2_fwd")
-        ctx.save_for_backward(x, weight)
+        ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.cfg = (bool(relu), bias is not None)
         return y
 
     @staticmethod
     def backward(ctx, gy):
-        x, weight = ctx.saved_tensors
+        x, weight, y = ctx.saved_tensors
+        relu, has_bias = ctx.cfg
         gy = _prep(gy, "gy")
         B, CI, H, W = x.shape
         CO = weight.shape[1]
-        gw = gx = None
+        gw = gx = gb = None
+        if relu or (has_bias and ctx.needs_input_grad[2]):
+            g2, gb = _relu_bias_bwd(gy, y, relu, want_g=relu, want_bias=has_bias and ctx.needs_input_grad[2])
+            if relu:
+                gy = g2
         if ctx.needs_input_grad[1]:
             # roles swapped: "input" = gy [B,CO,2H,2W], "output gradient" = x [B,CI,H,W]  ->  [CI][CO][4][4]
             gw = _conv_wgrad(x, gy, 4, 2, 1)
@@ -632,11 +684,11 @@ class _ConvTTrain(torch.autograd.Function):
             with torch.cuda.device(x.device):
                 check(_C.nconv_b200_conv_dgrad_gather(_p(gy), _p(weight), _p(gx), _p(ws), B, CI, CO, H, W, 4, 2, 1, 1,
                                                       _stream(x)), "conv_dgrad_gatherT")
-        return gx, gw
+        return gx, gw, gb, None
 
 
-def convT_train(x, weight):
-    return _ConvTTrain.apply(x, weight)
+def convT_train(x, weight, bias=None, relu=False):
+    return _ConvTTrain.apply(x, weight, bias, relu)
 
 
 class _BnTrain(torch.autograd.Function):
@@ -685,6 +737,7 @@ def bn_train(z, bn: "torch.nn.BatchNorm2d", residual=None, relu=True):
     y = _BnTrain.apply(z, bn.weight, bn.bias, rm, rv, residual, float(bn.eps), float(bn.momentum), relu)
     if bn.track_running_stats and bn.num_batches_tracked is not None:
         bn.num_batches_tracked.add_(1)
+    _note_mutation((rm, rv))                 # running statistics were written through raw pointers
     return y
 
 
@@ -769,8 +822,29 @@ def depth_loss_multires(depths, gt, rows=None, use_gradient_loss=False):
     return _DepthLossMultires.apply(gt, rows, bool(use_gradient_loss), *depths)
 
 
-class FusedAdamW:
-    """torch.optim.AdamW (amsgrad off) as ONE kernel per step over flat fp32 buffers.
+# Mutation epoch: kernels that write parameters / running statistics through raw pointers (fused AdamW, BatchNorm
+# batch statistics) never bump tensor version counters, so caches of derived data (packed tensor-core weights,
+# folded BatchNorm) also key on this counter.
+_MUTATION_EPOCH = [0]
+
+
+def mutation_epoch() -> int:
+    return _MUTATION_EPOCH[0]
+
+
+def _note_mutation(tensors=()):
+    _MUTATION_EPOCH[0] += 1
+    ts = [t for t in tensors if t is not None]
+    if ts:
+        torch.autograd.graph.increment_version(ts)
+
+
+class FusedAdamW(torch.optim.Optimizer):
+    """torch.optim.AdamW (amsgrad off) as ONE kernel per step over flat fp32 buffers — and still a
+    `torch.optim.Optimizer`: one param_group whose 'lr' / 'betas' / 'eps' / 'weight_decay' are read at every
+    step(), so `torch.optim.lr_scheduler.LinearLR` / `ReduceLROnPlateau` (train_step1.py:36-38, train_step2.py:35)
+    drive it unchanged, and `state_dict()` / `load_state_dict()` use torch.optim.AdamW's own format (per-parameter
+    'step', 'exp_avg', 'exp_avg_sq'), so optimizer checkpoints interchange with the reference's optimizer.
 
     Construction is lazy: at the first step() the parameters whose .grad is None (never reached by backward —
     torch.optim skips those, e.g. the unused BatchNorm of the reference's NConv2d, step1.py:119) are left
@@ -780,16 +854,32 @@ class FusedAdamW:
     receives a gradient raises."""
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2):
-        self.params = [p for p in params if p.requires_grad]
-        if not self.params:
+        params = [p for p in params if p.requires_grad]
+        if not params:
             raise ValueError("FusedAdamW: no trainable parameters")
-        dev = self.params[0].device
-        if dev.type != "cuda" or any(p.device != dev or p.dtype != torch.float32 for p in self.params):
+        dev = params[0].device
+        if dev.type != "cuda" or any(p.device != dev or p.dtype != torch.float32 for p in params):
             raise ValueError("FusedAdamW: parameters must be float32 on one CUDA device")
-        self.lr, self.betas, self.eps, self.weight_decay = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
+        super().__init__(params, dict(lr=float(lr), betas=(float(betas[0]), float(betas[1])), eps=float(eps),
+                                      weight_decay=float(weight_decay)))
+        if len(self.param_groups) != 1:
+            raise ValueError("FusedAdamW: one parameter group")
+        self.params = self.param_groups[0]["params"]
         self.step_count = 0
         self.active = None
+        self.skipped = []
+        self._offsets = []
+        self._pending = None          # state loaded before the flat buffers exist
         self.flat_param = self.flat_grad = self.exp_avg = self.exp_avg_sq = None
+
+    # hyper-parameters live in the param_group (that is what schedulers mutate)
+    @property
+    def lr(self):
+        return float(self.param_groups[0]["lr"])
+
+    @lr.setter
+    def lr(self, v):
+        self.param_groups[0]["lr"] = float(v)
 
     def attach(self):
         """Build the flat buffers from the gradients present now (call after the first backward)."""
@@ -798,6 +888,7 @@ class FusedAdamW:
         self.active = [p for p in self.params if p.grad is not None]
         self.skipped = [p for p in self.params if p.grad is None]
         if not self.active:
+            self.active = None
             raise RuntimeError("FusedAdamW: no parameter has a gradient")
         dev = self.active[0].device
         # 4-element alignment keeps every view 16-byte aligned
@@ -805,6 +896,7 @@ class FusedAdamW:
         for p in self.active:
             offs.append(total)
             total += (p.numel() + 3) // 4 * 4
+        self._offsets = offs
         self.flat_param = torch.zeros(total, device=dev, dtype=torch.float32)
         self.flat_grad = torch.zeros(total, device=dev, dtype=torch.float32)
         self.exp_avg = torch.zeros(total, device=dev, dtype=torch.float32)
@@ -817,6 +909,9 @@ class FusedAdamW:
                 pv.copy_(p.data); gv.copy_(p.grad)
                 p.data = pv
                 p.grad = gv
+        if self._pending is not None:
+            self._apply_loaded(self._pending)
+            self._pending = None
 
     def zero_grad(self, set_to_none: bool = True):
         if self.active is None:
@@ -834,14 +929,64 @@ class FusedAdamW:
             self.flat_grad.mul_(1.0 / dist.get_world_size(group))
 
     @torch.no_grad()
-    def step(self):
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
         self.attach()
         for p in self.skipped:
             if p.grad is not None:
                 raise RuntimeError("FusedAdamW: a parameter without a gradient at attach() received one later")
+        g = self.param_groups[0]
         self.step_count += 1
         n = self.flat_param.numel()
         with torch.cuda.device(self.flat_param.device):
             check(_C.nconv_b200_adamw_step(_p(self.flat_param), _p(self.flat_grad), _p(self.exp_avg), _p(self.exp_avg_sq),
-                                           n, self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
-                                           self.step_count, _stream(self.flat_param)), "adamw_step")
+                                           n, float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
+                                           float(g["weight_decay"]), self.step_count, _stream(self.flat_param)), "adamw_step")
+        _note_mutation(self.active)          # the kernel wrote the parameters through raw pointers
+        return loss
+
+    # ---- torch.optim.AdamW-format checkpoints -------------------------------------------------------------
+    def state_dict(self):
+        index = {id(p): i for i, p in enumerate(self.params)}
+        state = {}
+        if self.active is not None:
+            for p, off in zip(self.active, self._offsets):
+                n = p.numel()
+                state[index[id(p)]] = {"step": torch.tensor(float(self.step_count)),
+                                       "exp_avg": self.exp_avg[off:off + n].view(p.shape).clone(),
+                                       "exp_avg_sq": self.exp_avg_sq[off:off + n].view(p.shape).clone()}
+        elif self._pending is not None:
+            state = self._pending
+        group = {k: v for k, v in self.param_groups[0].items() if k != "params"}
+        group["params"] = list(range(len(self.params)))
+        return {"state": state, "param_groups": [group]}
+
+    def _apply_loaded(self, state):
+        index = {id(p): i for i, p in enumerate(self.params)}
+        with torch.no_grad():
+            for p, off in zip(self.active, self._offsets):
+                st = state.get(index[id(p)])
+                if st is None:
+                    continue
+                n = p.numel()
+                self.exp_avg[off:off + n].copy_(st["exp_avg"].reshape(-1).to(self.exp_avg.device, torch.float32))
+                self.exp_avg_sq[off:off + n].copy_(st["exp_avg_sq"].reshape(-1).to(self.exp_avg.device, torch.float32))
+                self.step_count = int(float(st["step"]))
+
+    def load_state_dict(self, state_dict):
+        groups = state_dict["param_groups"]
+        if len(groups) != 1 or len(groups[0]["params"]) != len(self.params):
+            raise ValueError("FusedAdamW.load_state_dict: parameter group mismatch")
+        for k, v in groups[0].items():
+            if k != "params":
+                self.param_groups[0][k] = v
+        state = {int(k): v for k, v in state_dict["state"].items()}
+        if self.active is not None:
+            self._apply_loaded(state)
+        else:
+            self._pending = state
+            steps = [int(float(v["step"])) for v in state.values()]
+            self.step_count = max(steps) if steps else 0

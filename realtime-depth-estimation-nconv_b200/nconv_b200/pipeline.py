@@ -9,16 +9,24 @@ nothing is cached or skipped — the copies just overlap the kernels.
 """
 from __future__ import annotations
 
-from typing import Callable, Iterable, List, Sequence
+from typing import Callable, Iterable, Optional, Sequence
 
 import torch
 
 
 class StreamedInference:
-    """run(batches) -> list of host outputs.  `model(*device_inputs)` must return a tensor or a tuple
-    of tensors; `batches` yields sequences of pinned host tensors of identical shapes."""
+    """run(batches, consume=None) -> list with one entry per batch, in order.
+
+    `model(*device_inputs)` must return a tensor or a tuple of tensors; `batches` yields sequences of pinned host
+    tensors of identical shapes.  Every batch's outputs are downloaded into one of `depth` pinned host slots; as
+    soon as a slot's download has finished — and before the slot is reused — its tensors are handed to
+    `consume(index, host_outputs)` (a view of the pinned slot, valid only during the call: copy or reduce there) and
+    the value `consume` returns is what `run` collects.  The default `consume` clones the slot, so `run(batches)`
+    returns every batch's outputs as ordinary host tensors."""
 
     def __init__(self, model: Callable, device: torch.device, depth: int = 2):
+        if depth < 2:
+            raise ValueError("StreamedInference: depth >= 2 (double buffering)")
         self.model, self.dev, self.depth = model, device, depth
         self.h2d = torch.cuda.Stream(device)
         self.d2h = torch.cuda.Stream(device)
@@ -29,13 +37,23 @@ class StreamedInference:
     def _alloc_inputs(self, batch: Sequence[torch.Tensor]):
         self._in = [[torch.empty(t.shape, dtype=t.dtype, device=self.dev) for t in batch] for _ in range(self.depth)]
 
-    def run(self, batches: Iterable[Sequence[torch.Tensor]], out_host: List[List[torch.Tensor]] = None):
+    def run(self, batches: Iterable[Sequence[torch.Tensor]], consume: Optional[Callable] = None):
+        if consume is None:
+            consume = lambda i, outs: [o.clone() for o in outs]      # noqa: E731
         compute = torch.cuda.current_stream(self.dev)
         it = iter(batches)
         slots_ready = [None] * self.depth          # event: upload of slot s finished
         slots_free = [None] * self.depth           # event: compute that read slot s finished
-        down_done = [None] * self.depth            # event: download of slot s finished
+        down_done = [None] * self.depth            # (batch index, event: download of slot s finished), not yet consumed
         results = []
+
+        def retire(s):
+            """Hand slot s's finished download to the consumer; after this the pinned slot may be overwritten."""
+            if down_done[s] is not None:
+                idx, ev = down_done[s]
+                ev.synchronize()
+                results.append((idx, consume(idx, self._host[s])))
+                down_done[s] = None
 
         def upload(s, batch):
             if self._in is None:
@@ -50,7 +68,7 @@ class StreamedInference:
 
         nxt = next(it, None)
         if nxt is None:
-            return results
+            return []
         upload(0, nxt)
         i = 0
         with torch.no_grad():
@@ -67,19 +85,17 @@ class StreamedInference:
                 if self._host is None:
                     self._host = [[torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs] for _ in range(self.depth)]
                     self._out = [None] * self.depth
+                retire(s)                                      # batch i - depth leaves this slot before it is refilled
                 with torch.cuda.stream(self.d2h):
                     self.d2h.wait_event(done)
-                    if down_done[s] is not None:
-                        down_done[s].synchronize()           # the host buffer of this slot was consumed last round
                     self._out[s] = outs
                     for h, o in zip(self._host[s], outs):
                         h.copy_(o, non_blocking=True)
                         o.record_stream(self.d2h)
                     ev = torch.cuda.Event(); ev.record(self.d2h)
-                    down_done[s] = ev
-                results.append((s, down_done[s]))
+                    down_done[s] = (i, ev)
                 i += 1
-        for ev in down_done:
-            if ev is not None:
-                ev.synchronize()
-        return [self._host[s] for s, _ in results[-self.depth:]]
+        for k in range(self.depth):                            # drain in batch order
+            retire((i + k) % self.depth)
+        results.sort(key=lambda r: r[0])
+        return [r for _, r in results]

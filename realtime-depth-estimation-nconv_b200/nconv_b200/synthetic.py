@@ -8,6 +8,7 @@ torch.Generator so the same tensors can be rebuilt anywhere from (config, seed).
 from __future__ import annotations
 
 import torch
+import torch.nn.functional as F
 
 # (Ci, Co, K, pad, B, H, W) — per-layer parity cases: DNET's shapes, BASELINE config 2's sweep,
 # ragged sizes (W % 4 != 0 -> scalar load path) and shapes served by the generic kernels.
@@ -92,3 +93,68 @@ def randomise_bn_stats(model: torch.nn.Module, seed: int = 55) -> None:
                 mod.running_var.copy_(torch.rand(n, generator=g) * 1.5 + 0.5)
                 mod.weight.copy_(torch.rand(n, generator=g) + 0.5)
                 mod.bias.copy_(torch.rand(n, generator=g) - 0.5)
+
+
+def synthetic_state_dict(seed: int = 5):
+    """A full SETP2_BP_EXPORT-shaped state_dict (step2.py:86-102 for the shapes) with
+    random-init weights of the reference's distributions: NConv weights = Poisson-bump + U[0,1)
+    (step1.py:159-169) passed once through softplus (what one training forward leaves stored,
+    step1.py:190-207), nconv7 positive, conv weights Kaiming-uniform-like, BatchNorm with
+    non-trivial running statistics.  Not RNG-identical to the reference constructors — it only
+    has to be the same tensors for the CUDA arm and the CPU arm."""
+    import numpy as np
+    from scipy.stats import poisson
+    g = torch.Generator().manual_seed(int(seed))
+    sd = {}
+
+    def nconv(name, ci, co, k):
+        pmf = poisson(k / 2).pmf(np.arange(0, k))
+        bump = torch.tensor(np.outer(pmf, pmf), dtype=torch.float32)
+        w = bump.expand(co, ci, k, k) + torch.rand(co, ci, k, k, generator=g)
+        sd["step1.d_net.%s.weight" % name] = F.softplus(w, beta=10).contiguous()
+        sd["step1.d_net.%s.bias" % name] = torch.full((co,), 0.01)
+
+    nconv("nconv1", 1, 8, 5)
+    for n in ("nconv2", "nconv_down1", "nconv_down2", "nconv_down3"):
+        nconv(n, 8, 8, 5)
+    for n in ("nconv4", "nconv5", "nconv6"):
+        nconv(n, 16, 8, 3)
+    nconv("nconv7", 8, 1, 1)
+
+    def conv(name, co, ci, k, bias):
+        bound = (1.0 / (ci * k * k)) ** 0.5
+        sd[name + ".weight"] = (torch.rand(co, ci, k, k, generator=g) * 2 - 1) * bound
+        if bias:
+            sd[name + ".bias"] = (torch.rand(co, generator=g) * 2 - 1) * bound
+
+    def bn(name, c):
+        sd[name + ".weight"] = torch.rand(c, generator=g) + 0.5
+        sd[name + ".bias"] = torch.rand(c, generator=g) - 0.5
+        sd[name + ".running_mean"] = torch.randn(c, generator=g) * 0.1
+        sd[name + ".running_var"] = torch.rand(c, generator=g) * 1.5 + 0.5
+        sd[name + ".num_batches_tracked"] = torch.tensor(1)
+
+    for i, (ci, co) in enumerate(((3, 32), (32, 64), (64, 64), (64, 64))):
+        p = "rgb_encoder%d" % i
+        conv(p + ".encoder.0", co, ci, 3, True)
+        bn(p + ".encoder.1", co)
+        conv(p + ".downsample.0", co, ci, 1, False)
+
+    def fusion(p, c, cout):
+        conv(p + ".rgb_conv.conv", c, c, 3, True)
+        conv(p + ".depth_conv.conv", c, 1, 3, True)
+        conv(p + ".fuse_conv1.conv", c, 2 * c, 3, True)
+        conv(p + ".fuse_conv2.conv", cout, c, 3, True)
+        conv(p + ".fuse_conv3.conv", cout, cout, 3, True)
+
+    fusion("fuse0.fuse", 64, 64)
+    conv("fuse0.conv", 1, 64, 3, False)
+    for name, c, cout in (("fuse1", 64, 64), ("fuse2", 64, 32), ("fuse3", 32, 32)):
+        bound = (1.0 / ((c + 1) * 16)) ** 0.5
+        sd[name + ".upcat.upf.conv.weight"] = (torch.rand(c + 1, c, 4, 4, generator=g) * 2 - 1) * bound
+        bn(name + ".upcat.upf.bn", c)
+        conv(name + ".upcat.conv.conv.conv", c, 2 * c, 3, False)
+        bn(name + ".upcat.conv.conv.bn", c)
+        fusion(name + ".fuse", c, cout)
+        conv(name + ".conv", 1, cout, 3, False)
+    return sd

@@ -5,12 +5,23 @@ running on the nconv_b200 CUDA kernels.  CUDA only: 
                                                       use_gradient_loss=True (train_step1.py:20)
   calculate_loss_multi_resolution  utils.py:63-71     mean over scales of the loss of the bilinear upsample
   get_optimizer                    utils.py:53-61     'adam' -> AdamW as one fused kernel over a flat buffer
+
+OPT-IN.  The reference's scripts do `from utils import *` (train_step1.py:3, train_step2.py:3) and need the rest of
+that module too (`get_performance`, `save_checkpoint`, `save_depth`, the star-leaked `os` / `DataLoader`), so the
+unchanged scripts keep importing the reference's own `utils.py` — with which the drop-in models work as they are
+(stock `F.mse_loss` / `torch.optim.AdamW` on CUDA tensors).  To route the loss and the optimizer through the
+library's kernels a maintainer adds ONE line after that import:
+
+    from utils import *
+    from nconv_b200.train_utils import *      # calculate_loss, calculate_loss_multi_resolution, get_optimizer
+
+This module deliberately is not named `utils.py`: it must never shadow the reference's module on sys.path.
 """
 from __future__ import annotations
 
 import torch
 
-from nconv_b200 import ops
+from . import ops
 
 __all__ = ["calculate_loss", "calculate_loss_multi_resolution", "get_optimizer"]
 

@@ -43,3 +43,18 @@ def golden():
 
 def T(a):
     return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def report(test: str, **values) -> None:
+    """Append achieved parity figures (max-rel errors, noise ratios ...) to gpurun_out/parity_report.jsonl so a
+    regression inside the tolerance is still visible; the file travels back from the GPU box and a copy of each
+    round's run is committed under profiles/."""
+    import json
+    d = os.path.join(ROOT, "gpurun_out")
+    try:
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "parity_report.jsonl"), "a") as f:
+            f.write(json.dumps({"test": test, **{k: (float(v) if isinstance(v, (int, float)) else v) for k, v in values.items()}}) + "\n")
+    except OSError:
+        pass
+    print("[parity] %s %s" % (test, values))

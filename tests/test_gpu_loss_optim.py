@@ -25,8 +25,8 @@ def dev():
 
 @pytest.fixture(scope="module")
 def U():
-    import utils as U  # the drop-in mirror of the reference's utils.py (raises if the .so is missing)
-    assert U.__file__.endswith("realtime-depth-estimation-nconv_b200/utils.py")
+    from nconv_b200 import train_utils as U  # the drop-in mirror of the reference's utils.py (raises if the .so is missing)
+    assert U.__file__.endswith("nconv_b200/train_utils.py")
     return U
 
 

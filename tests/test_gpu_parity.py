@@ -12,7 +12,7 @@ import pytest
 import torch
 import torch.nn.functional as F
 
-from conftest import REL_TOL, T
+from conftest import REL_TOL, T, report
 from oracle import nconv_oracle as O
 from nconv_b200.synthetic import (NCONV_LAYER_CASES, nconv_layer_case, sparse_depth_kitti, sparse_depth_nyu,
                                   setp2_inputs, randomise_bn_stats)
@@ -104,6 +104,52 @@ def test_nconv2d_bwd_stream_kernel_vs_oracle_autograd(K, cfg, shape, with_gc):
     l2.backward()
     for name, t, r in (("gx", xg.grad, xd.grad), ("gc", cg.grad, cd.grad), ("gw", wg.grad, wd.grad), ("gb", bg.grad, bd.grad)):
         assert grad_err(t, r.float()) <= GRAD_TOL, name
+
+
+def _poisson_softplus_weight(co, ci, k, gen):
+    """init_method='p' (step1.py:159-169: Poisson bump + U[0,1)) after one EnforcePos pass (:206-207)."""
+    from scipy.stats import poisson
+    pmf = poisson(k / 2).pmf(np.arange(0, k))
+    bump = torch.tensor(np.outer(pmf, pmf), dtype=torch.float32)
+    return O.softplus_beta10(bump.expand(co, ci, k, k) + torch.rand(co, ci, k, k, generator=gen)).contiguous()
+
+
+@pytest.mark.parametrize("cfg", [(4, 4, 3), (4, 4, 5), (16, 16, 3), (16, 16, 5), (1, 2, 5), (2, 2, 5)])
+def test_nconv2d_config2_full_size_vs_fp64(K, cfg):
+    """BASELINE config 2 AT THE MEASURED SIZE (B=16, 480x640: multi-wave persistent grids, split-K weight-gradient
+    partials, fp32 accumulation over 4.9 M pixels) — forward and backward of one NConv2d layer against the CPU
+    oracle in fp64 (`O.nconv2d` + autograd), every frame, every element.  The oracle walks the batch two frames at
+    a time so the fp64 temporaries stay small; the weight/bias gradients add up over the chunks (they are sums
+    over frames).  Tolerances as for the small cases: y/cout max-rel 1e-4 (|ref| floored at 1e-3), gradients
+    max|a-b| <= 1e-4 max|ref| per tensor; the achieved figures go to the parity report."""
+    from nconv_b200.synthetic import nconv_layer_inputs
+    ci, co, k = cfg
+    B, H, W, pad = 16, 480, 640, k // 2
+    x, c, gy, gc = nconv_layer_inputs(ci, co, k, pad, B, H, W, seed=1000 + ci * 10 + k)
+    gen = torch.Generator().manual_seed(ci * 100 + co + k)
+    w = _poisson_softplus_weight(co, ci, k, gen)
+    b = torch.full((co,), 0.01)
+    xg, cg, wg, bg = (t.to(dev()).requires_grad_(True) for t in (x, c, w, b))
+    y, cout = K.nconv2d(xg, cg, wg, bg, pad, pad, 1e-7)
+    ((y * gy.to(dev())).sum() + (cout * gc.to(dev())).sum()).backward()
+    torch.cuda.synchronize()
+    y, cout, gx, gcin = y.detach().cpu(), cout.detach().cpu(), xg.grad.cpu(), cg.grad.cpu()
+    wd, bd = w.double().requires_grad_(True), b.double().requires_grad_(True)
+    fwd_err = 0.0
+    gx_err = gc_err = gx_max = gc_max = 0.0
+    for i in range(0, B, 2):
+        xd, cd = x[i:i + 2].double().requires_grad_(True), c[i:i + 2].double().requires_grad_(True)
+        yr, cr = O.nconv2d(xd, cd, wd, bd, (pad, pad))
+        ((yr * gy[i:i + 2].double()).sum() + (cr * gc[i:i + 2].double()).sum()).backward()
+        fwd_err = max(fwd_err, O.max_rel_err(y[i:i + 2], yr), O.max_rel_err(cout[i:i + 2], cr))
+        gx_err = max(gx_err, float((gx[i:i + 2].double() - xd.grad).abs().max())); gx_max = max(gx_max, float(xd.grad.abs().max()))
+        gc_err = max(gc_err, float((gcin[i:i + 2].double() - cd.grad).abs().max())); gc_max = max(gc_max, float(cd.grad.abs().max()))
+    errs = {"fwd_max_rel": fwd_err, "gx": gx_err / gx_max, "gc": gc_err / gc_max,
+            "gw": grad_err(wg.grad, wd.grad), "gb": grad_err(bg.grad, bd.grad)}
+    report("nconv2d_config2_full_size_%d_%d_k%d" % cfg, **errs)
+    assert errs["fwd_max_rel"] <= REL_TOL
+    for name in ("gx", "gc", "gw", "gb"):
+        assert errs[name] <= GRAD_TOL, (name, errs)
 
 
 def test_nconv2d_module_hook_semantics(K):
@@ -272,6 +318,7 @@ def test_setp1_training_step_vs_reference_golden(golden):
     y = m(S)
     assert O.max_rel_err(y, T(g["out"])) <= REL_TOL
     (y * T(g["G"]).to(dev())).sum().backward()
+    ratios = {}
     for k, p in m.named_parameters():
         if "bnorm" in k:
             assert p.grad is None
@@ -282,7 +329,12 @@ def test_setp1_training_step_vs_reference_golden(golden):
         # ill-conditioned sum: the reference's fp32 autograd is 8.6e-4 from its fp64 result).
         g64 = T(g["g64_" + k].astype("float64"))
         noise = grad_err(T(g["g_" + k]), g64)
-        assert grad_err(p.grad, g64) <= max(2e-4, 3.0 * noise), (k, noise)
+        ours = grad_err(p.grad, g64)
+        ratios[k] = (ours, noise)
+        assert ours <= max(2e-4, 3.0 * noise), (k, noise)
+    worst = max(ratios, key=lambda k: ratios[k][0] / max(ratios[k][1], 1e-12))
+    report("setp1_train_step_gradients", worst_tensor=worst, ours_vs_fp64=ratios[worst][0], reference_fp32_vs_fp64=ratios[worst][1],
+           worst_ratio=ratios[worst][0] / max(ratios[worst][1], 1e-12), max_ours_vs_fp64=max(v[0] for v in ratios.values()))
 
 
 def test_batch_sharding_is_bit_identical(golden):
@@ -365,16 +417,45 @@ def test_setp2_export_vs_reference_golden(golden):
     rgb0, d0, rgb1, d1 = (t.to(dev()) for t in setp2_inputs(1, seed=7))
     with torch.no_grad():
         o0, o1 = m(rgb0, d0, rgb1, d1)
-    # SETP2 tolerance: max-rel 1e-4 with |ref| floored at SETP2_FLOOR = 0.1 m (1 % of the NYU depth
-    # range).  With random-init weights the refined depth crosses zero, and at a 1e-3 floor the
-    # reference's OWN fp32 result is 9.6e-5 from its fp64 result at those pixels (abs 1e-5 on
-    # values of ~6; DESIGN.md "Parity"), so a 1e-3 floor would test the summation order, not the
-    # arithmetic.  The global scaled error max|a-b|/max|b| is bounded at 1e-5 as well.
+    # SETP2 tolerance.  With random-init weights the refined depth crosses zero, so a max-rel figure depends on the
+    # floor put under |ref|.  Asserted, all three:
+    #  (1) vs the reference's fp32 output, |ref| floored at SETP2_FLOOR = 0.1 m (1 % of the NYU range): <= 1e-4, and
+    #      max|a-b| / max|b| <= 1e-5;
+    #  (2) vs the reference's fp64 output (1:3 grid of the interior, stored in the golden) at SURVEY 8c's floor of
+    #      1e-3: <= max(1e-4, 1.5 x the reference's OWN fp32-vs-fp64 figure on this input, also in the golden:
+    #      9.6e-5 / 8.0e-5) — the loosening is what the reference's fp32 rounding measures, not a constant;
+    #  (3) vs the reference's fp32 output at the 1e-3 floor, full frame: <= max(1e-4, 2.5 x that figure) (two fp32
+    #      results each within ~1.2 noise units of fp64).
+    # The achieved figures and the share of pixels above 1e-4 are printed and written to the parity report.
     for o, key in ((o0, "out0"), (o1, "out1")):
         ref = T(g[key])
         assert O.max_rel_err(o, ref, floor=SETP2_FLOOR) <= REL_TOL
         assert grad_err(o, ref) <= 1e-5
+        i = key[-1]
+        noise = float(g["ref32_vs_64_rel_floor1e3_" + i])
+        ref64 = torch.from_numpy(g["out%s_64_sub" % i])
+        ours64 = O.max_rel_err(o[:, :, 45:-45:3, 20::3], ref64, floor=1e-3)
+        ours32 = O.max_rel_err(o, ref, floor=1e-3)
+        rel = (o.double().cpu() - ref.double()).abs() / ref.double().abs().clamp_min(1e-3)
+        frac = float((rel > 1e-4).double().mean())
+        report("setp2_export_golden_" + key, rel_floor0p1=O.max_rel_err(o, ref, floor=SETP2_FLOOR), rel_vs_fp64_floor1e3=ours64,
+               rel_vs_fp32_floor1e3=ours32, reference_fp32_vs_fp64_floor1e3=noise, frac_pixels_above_1e4=frac)
+        assert ours64 <= max(1e-4, 1.5 * noise), (ours64, noise)
+        assert ours32 <= max(1e-4, 2.5 * noise), (ours32, ours64, noise)
     assert torch.all(o0[:, :, :45] == 0) and torch.all(o0[:, :, -45:] == 0) and torch.all(o0[..., :20] == 0)
+
+
+def test_setp2_bench_batch_parity():
+    """VERDICT r1 #1a: the batch bench.py times (config 4: 16 frames per stream, seed 7, the bench's own weights) was
+    only checked with isfinite.  Tile geometry is chosen per launch (tc_plan / tcx_plan), so a batch-dependent
+    defect would pass every B = 1 golden: first, last and two middle frames of both streams against the oracle."""
+    import bench
+    m = bench.build_model(dev())
+    host = setp2_inputs(bench.FRAMES_PER_STREAM, seed=7, H=bench.H, W=bench.W)
+    res = bench.bench_batch_parity(m, [t.to(dev()) for t in host], host)
+    report("setp2_bench_batch", **{k: v for k, v in res.items() if k != "frame_indices"})
+    assert res["max_rel_floor0p1"] <= REL_TOL, res
+    assert res["max_abs_over_max_ref"] <= 1e-5, res
 
 
 def _rel(a, ref):
@@ -515,8 +596,14 @@ def test_setp2_train_step_vs_reference_golden(golden, tmp_path, monkeypatch):
     assert ops.launch_count() - n0 > 150
     for i, d in enumerate(depths):
         ref = T(g["d%d" % i])
+        ref64 = torch.from_numpy(g["d64_%d" % i]).double()
         err = ((_sub(d) - ref).abs() / ref.abs().clamp_min(0.1)).max().item()
         assert err <= 1e-4, ("depth scale %d" % i, err)
+        # at SURVEY 8c's 1e-3 floor, against the reference's fp64 run, bounded by the reference's own fp32 noise
+        noise = ((ref.double() - ref64).abs() / ref64.abs().clamp_min(1e-3)).max().item()
+        ours = ((_sub(d).double() - ref64).abs() / ref64.abs().clamp_min(1e-3)).max().item()
+        report("setp2_train_step_depth_scale%d" % i, rel_floor0p1=err, rel_vs_fp64_floor1e3=ours, reference_fp32_vs_fp64_floor1e3=noise)
+        assert ours <= max(1e-4, 1.5 * noise), ("depth scale %d at floor 1e-3" % i, ours, noise)
     names = [str(n) for n in g["grad_names"]]
     params = dict(m.named_parameters())
     assert sorted(names) == sorted(k for k, p in params.items() if p.grad is not None)
@@ -535,6 +622,10 @@ def test_setp2_train_step_vs_reference_golden(golden, tmp_path, monkeypatch):
     med = sorted(r for _, r in dist.values())[len(dist) // 2]
     for k, (ours, ref_dist) in dist.items():
         assert ours <= max(2e-4, 3 * ref_dist, 2 * med), (k, ours, ref_dist, med)
+    worst = max(dist, key=lambda k: dist[k][0] / max(dist[k][1], med))
+    report("setp2_train_step_gradients", worst_tensor=worst, ours_vs_fp64=dist[worst][0], reference_fp32_vs_fp64=dist[worst][1],
+           worst_ratio_to_max_ref_med=dist[worst][0] / max(dist[worst][1], med), median_reference_noise=med,
+           tensors=len(dist), tensors_closer_than_reference=sum(1 for o, r in dist.values() if o <= r))
     sd = m.state_dict()
     for key in g.files:
         if key.startswith("bn_"):

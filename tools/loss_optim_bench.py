@@ -30,7 +30,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     args = ap.parse_args()
     dev = torch.device("cuda:0")
-    import utils as U
+    from nconv_b200 import train_utils as U
     from nconv_b200 import _lib, ops
     from nconv_b200.synthetic import loss_case
 

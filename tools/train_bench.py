@@ -45,6 +45,60 @@ def multires_loss(depths, gt):
     return total / len(depths)
 
 
+def make_trainer(dev, frames: int, H: int, W: int, rank: int = 0, fused: bool = True, seed_offset: int = 0):
+    """Build SETP2_BP_TRAIN (frozen step 1 from a freshly written checkpoint, train_step2.py:134), its optimizer and
+    one synthetic per-GPU batch; return (step, model, opt, bucket).  `step()` = train_step2.py:59-65 plus the
+    data-parallel gradient all-reduce."""
+    from models.step1 import SETP1_NCONV
+    from models.step2 import SETP2_BP_TRAIN
+    from nconv_b200.distributed import GradBucket, broadcast_parameters
+    from nconv_b200.synthetic import setp2_inputs
+    from nconv_b200 import train_utils as U
+    per = frames // 2
+    td = tempfile.mkdtemp()
+    os.makedirs(os.path.join(td, "checkpoints"))
+    torch.manual_seed(3)
+    torch.save({"state_dict": SETP1_NCONV().state_dict()}, os.path.join(td, "checkpoints", "s1.pth.tar"))
+    cwd = os.getcwd(); os.chdir(td)
+    try:
+        torch.manual_seed(5)
+        model = SETP2_BP_TRAIN("s1").to(dev).train()
+    finally:
+        os.chdir(cwd)
+    broadcast_parameters(model)
+    params = [p for p in model.parameters() if p.requires_grad]
+    if fused:
+        opt = U.get_optimizer(model, "adam", 1e-4, 1e-7)
+        bucket = None
+    else:
+        opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-7)
+        bucket = GradBucket(params)
+    rgb0, d0, rgb1, d1 = (t.to(dev) for t in setp2_inputs(per, seed=100 + rank + seed_offset, H=H, W=W))
+    g = torch.Generator().manual_seed(200 + rank + seed_offset)
+    gt = (torch.rand(2 * per, 1, H, W, generator=g) * 9.5 + 0.5) * (torch.rand(2 * per, 1, H, W, generator=g) > 0.1)
+    gt = gt.to(dev)
+
+    def step(sync: bool = True):
+        model.train()
+        opt.zero_grad(set_to_none=False)
+        a, b = model(rgb0, d0, rgb1, d1)
+        depths = [torch.cat((x, y), 0) for x, y in zip(a, b)]
+        if fused:
+            loss = U.calculate_loss_multi_resolution(depths, gt, False, all_samples=True)
+            loss.backward()
+            if sync:
+                opt.allreduce_mean()
+        else:
+            loss = multires_loss(depths, gt)
+            loss.backward()
+            if sync:
+                bucket.allreduce_mean()
+        opt.step()
+        return loss
+
+    return step, model, opt, bucket
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--frames", type=int, default=16)
@@ -61,51 +115,10 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    from models.step1 import SETP1_NCONV
-    from models.step2 import SETP2_BP_TRAIN
     from nconv_b200 import _lib, ops
-    from nconv_b200.distributed import GradBucket, broadcast_parameters
-    from nconv_b200.synthetic import setp2_inputs
 
-    H, W, per = args.height, args.width, args.frames // 2
-    td = tempfile.mkdtemp()
-    os.makedirs(os.path.join(td, "checkpoints"))
-    torch.manual_seed(3)
-    torch.save({"state_dict": SETP1_NCONV().state_dict()}, os.path.join(td, "checkpoints", "s1.pth.tar"))
-    cwd = os.getcwd(); os.chdir(td)
-    torch.manual_seed(5)
-    model = SETP2_BP_TRAIN("s1").to(dev).train()
-    os.chdir(cwd)
-    broadcast_parameters(model)
-    params = [p for p in model.parameters() if p.requires_grad]
-    import utils as U
     fused = not args.torch_loss_optim
-    if fused:
-        opt = U.get_optimizer(model, "adam", 1e-4, 1e-7)
-        bucket = None
-    else:
-        opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-7)
-        bucket = GradBucket(params)
-    rgb0, d0, rgb1, d1 = (t.to(dev) for t in setp2_inputs(per, seed=100 + rank, H=H, W=W))
-    g = torch.Generator().manual_seed(200 + rank)
-    gt = (torch.rand(2 * per, 1, H, W, generator=g) * 9.5 + 0.5) * (torch.rand(2 * per, 1, H, W, generator=g) > 0.1)
-    gt = gt.to(dev)
-
-    def step():
-        model.train()
-        opt.zero_grad(set_to_none=False)
-        a, b = model(rgb0, d0, rgb1, d1)
-        depths = [torch.cat((x, y), 0) for x, y in zip(a, b)]
-        if fused:
-            loss = U.calculate_loss_multi_resolution(depths, gt, False, all_samples=True)
-            loss.backward()
-            opt.allreduce_mean()
-        else:
-            loss = multires_loss(depths, gt)
-            loss.backward()
-            bucket.allreduce_mean()
-        opt.step()
-        return loss
+    step, model, opt, bucket = make_trainer(dev, args.frames, args.height, args.width, rank, fused)
 
     for _ in range(args.warmup):
         step()
