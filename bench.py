@@ -347,7 +347,7 @@ def setp1_kitti(dev, rank, world, steps, barrier, max_over_ranks):
         torch.cuda.synchronize(); barrier()
     ms = max_over_ranks(e0.elapsed_time(e1)) / steps
     mb, gf = 241.89, 6.569
-    return {"workload": "BASELINE config 3: SETP1_NCONV inference, 352x1216, 5 % density, 64 frames over %d GPU(s)" % world,
+    return {"workload": "BASELINE config 3: SETP1_NCONV inference, 352x1216, 5 %% density, 64 frames over %d GPU(s)" % world,
             "frames_per_gpu": frames, "value": frames * world / (ms / 1e3), "unit": "frames/s", "ms_per_step": ms, "steps": steps,
             "scaling": "strong", "layerwise_gbs_per_gpu": mb * frames / ms / 1e3, "layerwise_fp32_tflops_per_gpu": gf * frames / ms / 1e3}
 
@@ -464,6 +464,13 @@ def run_b200(args):
     _lib.profile_enable(False)
 
     # ---- e2e: pinned host inputs -> module call -> host result ------------------------------
+    # (diagnostic, untimed: this box's raw pinned-host -> device rate for one batch, so a slow e2e figure can be told
+    #  apart from a slow PCIe / NUMA path)
+    e0.record()
+    for dst, src in zip(resident, host):
+        dst.copy_(src, non_blocking=True)
+    e1.record(); torch.cuda.synchronize()
+    h2d_gbs = h2d / e0.elapsed_time(e1) / 1e6
     run_e2e(2)
     barrier(); torch.cuda.synchronize()
     e0.record()
@@ -509,7 +516,8 @@ def run_b200(args):
         "data": "synthetic",
         "config": workload_config(world),
         "e2e": {"value": frames * world * args.steps / (ms_e2e / 1e3), "unit": UNIT,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
+                "pinned_h2d_gbs_this_box": h2d_gbs},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roof,
