@@ -119,6 +119,46 @@ size_t nconv_b200_dnet_workspace_bytes(int B, int H, int W);
 int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out, int B, int H,
                             int W, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- tensor-core NConv2d for DNET's FMA-bound layers (8->8 5x5, [8|8]->8 3x3) — step1.py:116-149 on tcgen05 ----
+ * "N8" activation layout: an 8-channel (data, confidence) pair held as the two streams the layer
+ * correlates, split to bf16 hi/lo (16 mantissa bits) with a 2-pixel zero ring:
+ *     n8[n][stream: data*conf | conf][part: hi | lo][H+4][W+4][8]      (bf16, 64 B per pixel)
+ * Same bytes as the fp32 (data, conf) pair.  Kernels write interior pixels only; the ring is
+ * established by nconv_b200_n8_zero_ring.  pack/unpack convert from/to fp32 NCHW (tests, callers). */
+size_t nconv_b200_n8_bytes(int B, int H, int W);
+int nconv_b200_n8_zero_ring(void* n8, int B, int H, int W, void* stream);
+int nconv_b200_n8_pack(const float* x, const float* c, void* n8, int B, int H, int W, void* stream);
+int nconv_b200_n8_unpack(const void* n8, float* xc, float* c, int B, int H, int W, void* stream);
+
+/* nconv1 of DNET (step1.py:53-56): c0 = (S > thr), NConv2d 1->8 5x5 pad 2, output written as N8. */
+int nconv_b200_nconv1_n8(const float* S, const float* w, const float* bias, void* out_n8, int B,
+                         int H, int W, float thr, float eps, void* stream);
+
+/* Packed split-bf16 weights of one tensor-core NConv layer: w [8][CA+CB][K][K], K in {3,5}; source A
+ * holds weight input channels [0,8) when a_first (or CB == 0), else [8,16). */
+size_t nconv_b200_nconv_tc_wpack_bytes(int K, int CB);
+int nconv_b200_nconv_tc_pack_weights(const float* w, void* wpack, int K, int CB, int a_first,
+                                     void* stream);
+
+/* One NConv2d layer (8 or 8+8 -> 8 channels, K in {3,5}, pad K/2, stride 1) on N8 inputs of the SAME
+ * resolution (a nearest-upsampled source is supplied already expanded: see out_up).  Outputs, each
+ * optional (NULL = not written):
+ *   out_n8    (y, cout) as N8 at H x W                      [skip connection / next layer]
+ *   out_pool  N8 at H/2 x W/2 of the two INDEPENDENT 2x2 max-pools of y and cout (step1.py:62-74)
+ *   out_up    N8 at 2H x 2W, every pixel repeated 2x2 (F.interpolate nearest, exact 2x; :78-89)
+ *   y, cout   fp32 NCHW [B,8,H,W]
+ *   out_tail  fp32 [B,1,H,W]: the layer evaluated as step1.py:90 (valid 3x3, here centred) followed
+ *             by nconv7 (1x1, pad 2) and the crop of :92-94 (needs w_tail [8], b_tail [1]). */
+typedef struct {
+  const void* a; const void* b;          /* N8 sources (b may be NULL) */
+  const void* wpack; const float* w; const float* bias;   /* packed weights, original fp32 weights (for sum W), bias */
+  void* out_n8; void* out_pool; void* out_up; float* y; float* cout;
+  const float* w_tail; const float* b_tail; float* out_tail;
+  int B, H, W, K, CB;
+  float eps;
+} nconv_b200_nconv_tc_desc;
+int nconv_b200_nconv_tc(const nconv_b200_nconv_tc_desc* d, void* stream);
+
 /* ---- SETP2 building blocks — /root/reference/models/step2.py ---------------------------
  * Direct convolution y = act(scale[o]*conv(cat[a,b]) + shift[o]) + residual, covering
  * ConvBlock (:290-297), RGBEncoder (:134-154, BN folded to scale/shift), Basic2d (:178-195),

@@ -48,6 +48,16 @@ class TcDesc(Structure):
     ]
 
 
+class NconvTcDesc(Structure):
+    """nconv_b200_nconv_tc_desc"""
+    _fields_ = [
+        ("a", c_void_p), ("b", c_void_p), ("wpack", c_void_p), ("w", c_void_p), ("bias", c_void_p),
+        ("out_n8", c_void_p), ("out_pool", c_void_p), ("out_up", c_void_p), ("y", c_void_p), ("cout", c_void_p),
+        ("w_tail", c_void_p), ("b_tail", c_void_p), ("out_tail", c_void_p),
+        ("B", c_int), ("H", c_int), ("W", c_int), ("K", c_int), ("CB", c_int), ("eps", c_float),
+    ]
+
+
 # name -> (restype, argtypes); must list every symbol include/nconv_b200.h declares
 SIGNATURES = {
     "nconv_b200_abi_version": (c_int, []),
@@ -79,6 +89,14 @@ SIGNATURES = {
     "nconv_b200_dnet_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nconv_b200_dnet_forward": (c_int, [c_void_p, POINTER(c_void_p), c_void_p, c_int, c_int, c_int,
                                         c_void_p, c_size_t, c_void_p]),
+    "nconv_b200_n8_bytes": (c_size_t, [c_int] * 3),
+    "nconv_b200_n8_zero_ring": (c_int, [c_void_p] + [c_int] * 3 + [c_void_p]),
+    "nconv_b200_n8_pack": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
+    "nconv_b200_n8_unpack": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
+    "nconv_b200_nconv1_n8": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_float, c_float, c_void_p]),
+    "nconv_b200_nconv_tc_wpack_bytes": (c_size_t, [c_int] * 2),
+    "nconv_b200_nconv_tc_pack_weights": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
+    "nconv_b200_nconv_tc": (c_int, [POINTER(NconvTcDesc), c_void_p]),
     "nconv_b200_conv2d_fwd": (c_int, [POINTER(ConvDesc), c_void_p]),
     "nconv_b200_convT4x4s2_fwd": (c_int, [c_void_p] * 6 + [c_int] * 7 + [c_void_p]),
     "nconv_b200_bilinear_ac_fwd": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p]),

@@ -14,7 +14,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import ConvDesc, FwdDesc, TcDesc, check
+from ._lib import ConvDesc, FwdDesc, NconvTcDesc, TcDesc, check
 
 _C = _lib.load()
 
@@ -533,6 +533,95 @@ def head_p8(f: "P8", weight, residual, out8=None):
         check(_C.nconv_b200_head_p8(_p(f.buf), _p(weight), _p(residual), _p(y), None if out8 is None else _p(out8.buf),
                                     f.B, f.C, f.H, f.W, _stream(y)), "head_p8")
     return y, out8
+
+
+# --------------------------------------------------------------------------------------
+# tensor-core NConv2d: N8 activations + the tcgen05 layer kernel (csrc/nconv_tc.cu)
+# --------------------------------------------------------------------------------------
+class N8:
+    """An 8-channel (data, confidence) pair in the N8 device layout (csrc/n8.cuh): the two streams NConv2d
+    correlates (data*conf, conf), split bf16 hi/lo, 2-pixel zero ring."""
+    __slots__ = ("buf", "B", "H", "W")
+
+    def __init__(self, buf, B, H, W):
+        self.buf, self.B, self.H, self.W = buf, B, H, W
+
+    @staticmethod
+    def empty(B, H, W, device, zero_ring=True):
+        t = N8(torch.empty(int(_C.nconv_b200_n8_bytes(B, H, W)), device=device, dtype=torch.uint8), B, H, W)
+        if zero_ring:
+            with torch.cuda.device(device):
+                check(_C.nconv_b200_n8_zero_ring(_p(t.buf), B, H, W, _stream(t.buf)), "n8_zero_ring")
+        return t
+
+    @staticmethod
+    def pack(x, c):
+        x = _prep(x, "data"); c = _prep(c, "conf")
+        B, C, H, W = x.shape
+        if C != 8 or c.shape != x.shape:
+            raise ValueError("N8.pack: data and conf must be [B,8,H,W]")
+        t = N8.empty(B, H, W, x.device)
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_n8_pack(_p(x), _p(c), _p(t.buf), B, H, W, _stream(x)), "n8_pack")
+        return t
+
+    def unpack(self):
+        """-> (data*conf, conf) as fp32 [B,8,H,W]."""
+        xc = torch.empty((self.B, 8, self.H, self.W), device=self.buf.device, dtype=torch.float32)
+        c = torch.empty_like(xc)
+        with torch.cuda.device(xc.device):
+            check(_C.nconv_b200_n8_unpack(_p(self.buf), _p(xc), _p(c), self.B, self.H, self.W, _stream(xc)), "n8_unpack")
+        return xc, c
+
+
+def nconv1_n8(S, weight, bias, thr=0.01, eps=1e-7) -> "N8":
+    """step1.py:53-56: threshold + NConv2d(1->8, 5x5, pad 2) -> N8."""
+    S = _prep(S, "S"); weight = _prep(weight, "weight"); bias = _prep(bias, "bias")
+    B, _, H, W = S.shape
+    if S.shape[1] != 1 or tuple(weight.shape) != (8, 1, 5, 5):
+        raise ValueError("nconv1_n8: S [B,1,H,W], weight [8,1,5,5]")
+    out = N8.empty(B, H, W, S.device)
+    with torch.cuda.device(S.device):
+        check(_C.nconv_b200_nconv1_n8(_p(S), _p(weight), _p(bias), _p(out.buf), B, H, W, thr, eps, _stream(S)), "nconv1_n8")
+    return out
+
+
+def nconv_tc(a: "N8", b, weight, bias, a_first=True, eps=1e-7, want_n8=False, want_pool=False, want_up=False,
+             want_f32=False, tail=None):
+    """One NConv2d layer on the tcgen05 path: weight [8,8,5,5] (b is None) or [8,16,3,3] (b: N8 of a's size).
+    Returns a dict with the requested outputs: 'n8', 'pool', 'up' (N8), 'y'/'cout' (fp32), 'tail' (fp32 [B,1,H,W];
+    tail = (w7 [1,8,1,1], b7 [1]))."""
+    weight = _prep(weight, "weight"); bias = _prep(bias, "bias")
+    K = weight.shape[2]
+    CB = 0 if b is None else 8
+    if tuple(weight.shape) != (8, 8 + CB, K, K) or (K, CB) not in ((5, 0), (3, 8)):
+        raise ValueError("nconv_tc: weight must be [8,8,5,5] or [8,16,3,3] (with a second source)")
+    if b is not None and (b.B, b.H, b.W) != (a.B, a.H, a.W):
+        raise ValueError("nconv_tc: source shape mismatch")
+    dev = a.buf.device
+    wp = torch.empty(int(_C.nconv_b200_nconv_tc_wpack_bytes(K, CB)), device=dev, dtype=torch.uint8)
+    out = {}
+    with torch.cuda.device(dev):
+        check(_C.nconv_b200_nconv_tc_pack_weights(_p(weight), _p(wp), K, CB, int(a_first), _stream(wp)), "nconv_tc_pack_weights")
+        if want_n8:
+            out["n8"] = N8.empty(a.B, a.H, a.W, dev)
+        if want_pool:
+            out["pool"] = N8.empty(a.B, a.H // 2, a.W // 2, dev)
+        if want_up:
+            out["up"] = N8.empty(a.B, 2 * a.H, 2 * a.W, dev)
+        if want_f32:
+            out["y"] = torch.empty((a.B, 8, a.H, a.W), device=dev, dtype=torch.float32)
+            out["cout"] = torch.empty_like(out["y"])
+        w7 = b7 = None
+        if tail is not None:
+            w7, b7 = _prep(tail[0], "w_tail"), _prep(tail[1], "b_tail")
+            out["tail"] = torch.empty((a.B, 1, a.H, a.W), device=dev, dtype=torch.float32)
+        g = lambda k: _p(out[k].buf) if k in out else None      # noqa: E731
+        d = NconvTcDesc(_p(a.buf), None if b is None else _p(b.buf), _p(wp), _p(weight), _p(bias), g("n8"), g("pool"), g("up"),
+                        _p(out.get("y")), _p(out.get("cout")), _p(w7), _p(b7), _p(out.get("tail")),
+                        a.B, a.H, a.W, K, CB, eps)
+        check(_C.nconv_b200_nconv_tc(byref(d), _stream(a.buf)), "nconv_tc")
+    return out
 
 
 def launch_count() -> int:
