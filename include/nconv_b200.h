@@ -118,6 +118,11 @@ int nconv_b200_upcat_bwd(const float* gout, float* gskip, float* glow, int B, in
 size_t nconv_b200_dnet_workspace_bytes(int B, int H, int W);
 int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out, int B, int H,
                             int W, void* workspace, size_t workspace_bytes, void* stream);
+/* nconv_b200_dnet_forward runs the seven 8-channel layers on tcgen05 (split-bf16 operands, fp32 accumulate: y and cout
+ * within ~5e-6 of fp32) when H and W are multiples of 8 and W >= 224, else the fp32 CUDA-core pipeline; _fp32 always
+ * runs the latter (the frozen step 1 inside a training step uses it, so the training-step numerics stay pure fp32). */
+int nconv_b200_dnet_forward_fp32(const float* S, const float* const* params, float* out, int B,
+                                 int H, int W, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- tensor-core NConv2d for DNET's FMA-bound layers (8->8 5x5, [8|8]->8 3x3) — step1.py:116-149 on tcgen05 ----
  * "N8" activation layout: an 8-channel (data, confidence) pair held as the two streams the layer

@@ -5,6 +5,8 @@
 // the threshold is the prologue of nconv1 and nconv6 -> nconv7 -> crop is a single kernel.
 #include "common.cuh"
 #include "nconv_b200.h"
+#include "nconv_tc.h"
+#include <cstdlib>
 
 namespace {
 
@@ -36,22 +38,109 @@ static DnetPlan make_plan(int n, int H, int W) {
   return p;
 }
 
+// ---- tensor-core pipeline (csrc/nconv_tc.cu): every activation in the N8 split-bf16 layout, the seven 8-channel
+// layers on tcgen05, nconv1 on CUDA cores writing N8.  Needs exact 2x levels (H, W multiples of 8: pools floor and
+// the nearest upsample is "repeat 2x2") and a lowest level at least one staged row wide.
+enum { A0, TX1, TP1, TX2, TP2, TX3, TP3, TU4, TU34, TU23, TNBUF };
+static const int kTcLevel[TNBUF] = {0, 0, 1, 1, 2, 2, 3, 2, 1, 0};
+
+struct DnetTcPlan {
+  Level l[4];
+  size_t off[TNBUF], woff[7];
+  size_t total_bytes;
+};
+
+static bool tc_eligible(int H, int W) {
+  static const bool off = getenv("NCONV_B200_NO_NCONV_TC") != nullptr;      // A/B measurements only
+  return !off && H % 8 == 0 && W % 8 == 0 && W / 8 + 4 >= 32 && H / 8 >= 4;
+}
+
+static DnetTcPlan make_tc_plan(int n, int H, int W) {
+  DnetTcPlan p;
+  p.l[0] = {H, W};
+  for (int i = 1; i < 4; ++i) p.l[i] = {p.l[i - 1].H / 2, p.l[i - 1].W / 2};
+  size_t cur = 0;
+  for (int i = 0; i < TNBUF; ++i) {
+    p.off[i] = cur;
+    cur += (nconv_b200_n8_bytes(n, p.l[kTcLevel[i]].H, p.l[kTcLevel[i]].W) + 255) & ~(size_t)255;
+  }
+  for (int i = 0; i < 7; ++i) {
+    p.woff[i] = cur;
+    cur += (nconv_b200_nconv_tc_wpack_bytes(i < 4 ? 5 : 3, i < 4 ? 0 : 8) + 255) & ~(size_t)255;
+  }
+  p.total_bytes = cur;
+  return p;
+}
+
+static int dnet_forward_tc(const float* S, const float* const* params, float* out, int B, int H, int W, void* workspace,
+                           void* stream) {
+  const DnetTcPlan p = make_tc_plan(B, H, W);
+  uint8_t* ws = (uint8_t*)workspace;
+  auto buf = [&](int id) { return (void*)(ws + p.off[id]); };
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  {
+    nconv::N8RingJobs rj = {};
+    rj.B = B; rj.n = TNBUF;
+    for (int i = 0; i < TNBUF; ++i) { rj.buf[i] = buf(i); rj.H[i] = p.l[kTcLevel[i]].H; rj.W[i] = p.l[kTcLevel[i]].W; }
+    if ((rc = nconv::n8_zero_rings_multi(rj, st))) return rc;
+    // layers 1..7 of the parameter list: nconv2, nconv_down1..3 (8->8 5x5), nconv4, nconv5 (skip first), nconv6 (upsampled first)
+    nconv::NtPackJobs pj = {};
+    pj.n = 7;
+    for (int i = 0; i < 7; ++i) {
+      pj.w[i] = params[2 * (i + 1)]; pj.wpack[i] = ws + p.woff[i];
+      pj.K[i] = i < 4 ? 5 : 3; pj.nsrc[i] = i < 4 ? 1 : 2; pj.a_first[i] = (i == 6) ? 0 : 1;
+    }
+    if ((rc = nconv::nconv_tc_pack_multi(pj, st))) return rc;
+  }
+  const float eps = 1e-7f;
+  if ((rc = nconv_b200_nconv1_n8(S, params[0], params[1], buf(A0), B, H, W, 0.01f, eps, stream))) return rc;   // step1.py:53-56
+  auto layer = [&](int i, int lvl) {
+    nconv_b200_nconv_tc_desc d = {};
+    d.wpack = ws + p.woff[i]; d.w = params[2 * (i + 1)]; d.bias = params[2 * (i + 1) + 1];
+    d.B = B; d.H = p.l[lvl].H; d.W = p.l[lvl].W; d.K = i < 4 ? 5 : 3; d.CB = i < 4 ? 0 : 8; d.eps = eps;
+    return d;
+  };
+  { nconv_b200_nconv_tc_desc d = layer(0, 0); d.a = buf(A0); d.out_n8 = buf(TX1); d.out_pool = buf(TP1);       // nconv2 + pools, :57-64
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  { nconv_b200_nconv_tc_desc d = layer(1, 1); d.a = buf(TP1); d.out_n8 = buf(TX2); d.out_pool = buf(TP2);      // nconv_down1 + pools, :65-69
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  { nconv_b200_nconv_tc_desc d = layer(2, 2); d.a = buf(TP2); d.out_n8 = buf(TX3); d.out_pool = buf(TP3);      // nconv_down2 + pools, :70-74
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  { nconv_b200_nconv_tc_desc d = layer(3, 3); d.a = buf(TP3); d.out_up = buf(TU4);                             // nconv_down3, upsampled for :78-79
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  { nconv_b200_nconv_tc_desc d = layer(4, 2); d.a = buf(TX3); d.b = buf(TU4); d.out_up = buf(TU34);            // nconv4 on cat(x3, up(x4)), :80, :83-84
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  { nconv_b200_nconv_tc_desc d = layer(5, 1); d.a = buf(TX2); d.b = buf(TU34); d.out_up = buf(TU23);           // nconv5 on cat(x2, up(x34)), :85, :88-89
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  { nconv_b200_nconv_tc_desc d = layer(6, 0); d.a = buf(TX1); d.b = buf(TU23);                                  // nconv6 on cat(up(x23), x1) -> nconv7 -> crop, :90-94
+    d.w_tail = params[16]; d.b_tail = params[17]; d.out_tail = out;
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+  return 0;
+}
+
 }  // namespace
 
 extern "C" size_t nconv_b200_dnet_workspace_bytes(int B, int H, int W) {
   if (B <= 0 || H < 8 || W < 8) return 0;
-  return make_plan(B, H, W).total_floats * sizeof(float);
+  size_t n = make_plan(B, H, W).total_floats * sizeof(float);
+  if (tc_eligible(H, W)) {
+    const size_t t = make_tc_plan(B, H, W).total_bytes;
+    if (t > n) n = t;
+  }
+  return n;
 }
 
-extern "C" int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out,
-                                       int B, int H, int W, void* workspace, size_t workspace_bytes,
-                                       void* stream) {
+static int dnet_forward_impl(const float* S, const float* const* params, float* out, int B, int H, int W, void* workspace,
+                             size_t workspace_bytes, void* stream, bool allow_tc) {
   if (!S || !params || !out || !workspace || B <= 0) return NCONV_ERR_BAD_ARG;
   if (H < 8 || W < 8) return NCONV_ERR_BAD_ARG;  // three 2x2 pools must leave >= 1 pixel
   for (int i = 0; i < 18; ++i)
     if (!params[i]) return NCONV_ERR_BAD_ARG;
+  if (workspace_bytes < nconv_b200_dnet_workspace_bytes(B, H, W)) return NCONV_ERR_WORKSPACE;
+  if (allow_tc && tc_eligible(H, W) && (reinterpret_cast<uintptr_t>(workspace) & 255u) == 0)
+    return dnet_forward_tc(S, params, out, B, H, W, workspace, stream);
   DnetPlan p = make_plan(B, H, W);
-  if (workspace_bytes < p.total_floats * sizeof(float)) return NCONV_ERR_WORKSPACE;
   float* ws = (float*)workspace;
   auto buf = [&](int id) { return ws + p.off[id]; };
   const float eps = 1e-7f;  // step1.py:103
@@ -117,4 +206,14 @@ extern "C" int nconv_b200_dnet_forward(const float* S, const float* const* param
     if ((rc = nconv_b200_nconv2d_fwd_fused(&d, stream))) return rc;
   }
   return 0;
+}
+
+extern "C" int nconv_b200_dnet_forward(const float* S, const float* const* params, float* out, int B, int H, int W,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  return dnet_forward_impl(S, params, out, B, H, W, workspace, workspace_bytes, stream, true);
+}
+
+extern "C" int nconv_b200_dnet_forward_fp32(const float* S, const float* const* params, float* out, int B, int H, int W,
+                                            void* workspace, size_t workspace_bytes, void* stream) {
+  return dnet_forward_impl(S, params, out, B, H, W, workspace, workspace_bytes, stream, false);
 }

@@ -21,6 +21,7 @@
 #include "common.cuh"
 #include "launch_count.h"
 #include "n8.cuh"
+#include "nconv_tc.h"
 #include "nconv_b200.h"
 #include "p8.cuh"
 #include "tc_ptx.cuh"
@@ -107,7 +108,7 @@ __global__ void n8_unpack_kernel(const __nv_bfloat16* __restrict__ in, float* __
 // all 8 output channels of ONE pixel with FFMA2 over channel pairs (weights broadcast from shared memory) and writes
 // its four 16-byte N8 vectors (consecutive lanes = consecutive pixels: 512-byte runs).
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int N1_TW = 32, N1_TH = 8;
+constexpr int N1_TW = 32, N1_TH = 32, N1_PY = 4;     // a thread owns rows ty, ty+8, ty+16, ty+24 of its column: weight reads shared by 4 pixels
 
 __global__ void __launch_bounds__(256) nconv1_n8_kernel(const float* __restrict__ S, const float* __restrict__ w, const float* __restrict__ bias,
                                                         __nv_bfloat16* __restrict__ out, N8Geom g, float thr, float eps) {
@@ -130,48 +131,67 @@ __global__ void __launch_bounds__(256) nconv1_n8_kernel(const float* __restrict_
     s_rs[tid] = 1.f / s;
     s_b[tid] = __ldg(bias + tid);
   }
-  u64 aN[4] = {0ull, 0ull, 0ull, 0ull}, aD[4] = {0ull, 0ull, 0ull, 0ull};
+  u64 aN[N1_PY][4], aD[N1_PY][4];
+#pragma unroll
+  for (int p = 0; p < N1_PY; ++p)
+#pragma unroll
+    for (int o = 0; o < 4; ++o) { aN[p][o] = 0ull; aD[p][o] = 0ull; }
 #pragma unroll
   for (int u = 0; u < 5; ++u)
 #pragma unroll
     for (int v = 0; v < 5; ++v) {
-      const float x = s_in[ty + u][tx + v];
-      const float c = x > thr ? 1.f : 0.f;
-      const float xc = x * c;
       const ulonglong2 w01 = *reinterpret_cast<const ulonglong2*>(&s_w[u * 5 + v][0]);
       const ulonglong2 w23 = *reinterpret_cast<const ulonglong2*>(&s_w[u * 5 + v][4]);
-      ffma2(aN[0], w01.x, xc); ffma2(aN[1], w01.y, xc); ffma2(aN[2], w23.x, xc); ffma2(aN[3], w23.y, xc);
-      ffma2(aD[0], w01.x, c);  ffma2(aD[1], w01.y, c);  ffma2(aD[2], w23.x, c);  ffma2(aD[3], w23.y, c);
+#pragma unroll
+      for (int p = 0; p < N1_PY; ++p) {
+        const float x = s_in[ty + 8 * p + u][tx + v];
+        const float c = x > thr ? 1.f : 0.f;
+        const float xc = x * c;
+        ffma2(aN[p][0], w01.x, xc); ffma2(aN[p][1], w01.y, xc); ffma2(aN[p][2], w23.x, xc); ffma2(aN[p][3], w23.y, xc);
+        ffma2(aD[p][0], w01.x, c);  ffma2(aD[p][1], w01.y, c);  ffma2(aD[p][2], w23.x, c);  ffma2(aD[p][3], w23.y, c);
+      }
     }
   __syncthreads();
-  const int oy = y0 + ty, ox = x0 + tx;
-  if (oy >= g.H || ox >= g.W) return;
-  float xc[8], cc[8];
+  const int ox = x0 + tx;
+  if (ox >= g.W) return;
 #pragma unroll
-  for (int o = 0; o < 8; ++o) {
-    const float N = (o & 1) ? hi32f(aN[o >> 1]) : lo32f(aN[o >> 1]);
-    const float D = (o & 1) ? hi32f(aD[o >> 1]) : lo32f(aD[o >> 1]);
-    const float y = __fdividef(N, D + eps) + s_b[o];
-    cc[o] = D * s_rs[o];
-    xc[o] = y * cc[o];
+  for (int p = 0; p < N1_PY; ++p) {
+    const int oy = y0 + ty + 8 * p;
+    if (oy >= g.H) continue;
+    float xc[8], cc[8];
+#pragma unroll
+    for (int o = 0; o < 8; ++o) {
+      const float N = (o & 1) ? hi32f(aN[p][o >> 1]) : lo32f(aN[p][o >> 1]);
+      const float D = (o & 1) ? hi32f(aD[p][o >> 1]) : lo32f(aD[p][o >> 1]);
+      const float y = __fdividef(N, D + eps) + s_b[o];
+      cc[o] = D * s_rs[o];
+      xc[o] = y * cc[o];
+    }
+    uint4 h, l;
+    const size_t po = g.pixel(oy, ox);
+    split8(xc, h, l);
+    *reinterpret_cast<uint4*>(out + g.plane(n, 0, 0) + po) = h;
+    *reinterpret_cast<uint4*>(out + g.plane(n, 0, 1) + po) = l;
+    split8(cc, h, l);
+    *reinterpret_cast<uint4*>(out + g.plane(n, 1, 0) + po) = h;
+    *reinterpret_cast<uint4*>(out + g.plane(n, 1, 1) + po) = l;
   }
-  uint4 h, l;
-  const size_t po = g.pixel(oy, ox);
-  split8(xc, h, l);
-  *reinterpret_cast<uint4*>(out + g.plane(n, 0, 0) + po) = h;
-  *reinterpret_cast<uint4*>(out + g.plane(n, 0, 1) + po) = l;
-  split8(cc, h, l);
-  *reinterpret_cast<uint4*>(out + g.plane(n, 1, 0) + po) = h;
-  *reinterpret_cast<uint4*>(out + g.plane(n, 1, 1) + po) = l;
 }
+
+}  // namespace nconv
+
+namespace nconv {
 
 // ---------------------------------------------------------------------------------------------------------------
 // tcgen05 NConv2d
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int NT_THREADS = 192;             // warp 0: producer, warp 1: MMA issuer, warps 2-5: epilogue (TMEM lane quarter = warp % 4)
+constexpr int NT_ESETS = 2;                 // epilogue sets of 4 warps; set e drains the M-tiles with (running index) % NT_ESETS == e
+constexpr int NT_ISSUERS = 2;               // MMA issuer warps (1, 2): issuer i takes the M-tiles with (running index) % NT_ISSUERS == i
+constexpr int NT_THREADS = 128 + 128 * NT_ESETS;  // warp 0: producer, warps 1-2: MMA issuers, warp 3: idle, then the epilogue warps (TMEM lane quarter = warp % 4)
+constexpr int NT_PX_BYTES = NT_ESETS * 2 * 4 * 16 * 32 * 4;   // pool exchange: [set][parity][staged row in M-tile][y0..7 | c0..7][lane] floats
 constexpr int NT_P = 32;                    // staged row pitch in pixels: one staged row per epilogue warp
 constexpr int NT_ROW_BYTES = NT_P * 16;     // one staged row of one plane
-constexpr int NT_SMEM_MAX = 227 * 1024 - 20 * 1024;   // dynamic part (static: barriers, 16 KB of pool exchange buffers)
+constexpr int NT_SMEM_MAX = 227 * 1024 - 4 * 1024;    // dynamic part (static: barriers and per-channel constants)
 constexpr int NT_SMEM_MIN = 120 * 1024;     // > half an SM's shared memory: one CTA per SM (each allocates all 512 TMEM columns)
 
 template <int K> struct NtCfg {
@@ -229,13 +249,15 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
   __shared__ __align__(8) uint64_t s_full[2], s_empty[2], t_full[C::NSLOT], t_empty[C::NSLOT], s_wfull;
   __shared__ uint32_t s_tmem_base;
   __shared__ float s_rs[8], s_b[8], s_w7[8];
-  __shared__ float s_px[2][4][16][32];                         // pool exchange: [parity][staged row in M-tile][y0..7 | c0..7][lane]
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // the shuffle makes the warp index provably warp-uniform, so role branches are uniform branches and the MMA issue
+  // code below compiles to the uniform datapath
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t plane_bytes = (uint32_t)a.rows_ld * NT_ROW_BYTES;
   const uint32_t stage_bytes = NSRC * 4 * plane_bytes;
   const uint32_t smem_base = smem_u32(smem);
-  const uint32_t ring = smem_base + W_BYTES;
+  const uint32_t ring = smem_base + W_BYTES + NT_PX_BYTES;
+  float* s_px = reinterpret_cast<float*>(smem + W_BYTES);
 
   if (threadIdx.x < 8) {
     // cout = D / sum(W[o]) (step1.py:141-147) over the ORIGINAL fp32 weights
@@ -247,7 +269,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
     s_w7[threadIdx.x] = a.w_tail ? __ldg(a.w_tail + threadIdx.x) : 0.f;
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), NT_ISSUERS); }
     for (int s = 0; s < C::NSLOT; ++s) { mbar_init(smem_u32(&t_full[s]), 1); mbar_init(smem_u32(&t_empty[s]), 4); }
     mbar_init(smem_u32(&s_wfull), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -291,15 +313,22 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       __syncwarp();
       stage ^= 1; if (stage == 0) phase ^= 1;
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1 || warp == 2) {
+    // ===================== MMA issuers =====================
+    // Issuing one MMA costs ~100 cycles of the issuing warp (descriptor moves to uniform registers, elect, branch), more
+    // than the MMA itself at N = 32..48, so two warps issue for alternate M-tiles (independent accumulator slots).
+    const int issuer = warp - 1;
     constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(C::NROW >> 3) << 17) | ((128u >> 4) << 24);
     constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);      // SBO = 128 B, descriptor version 1
     mbar_wait(smem_u32(&s_wfull), 0);
     tc_fence_after();
-    uint32_t stage = 0, phase = 0, it = 0;
+    uint32_t stage = 0, phase = 0, it = 0, slot = 0, sphase = 0;
     const uint32_t w16 = smem_base >> 4;
-    const uint32_t lbo_hl = (plane_bytes >> 4) << 16;           // hi plane -> lo plane of the same stream
+    const uint32_t plane16 = plane_bytes >> 4;
+    const uint32_t lbo_hl = plane16 << 16;                      // hi plane -> lo plane of the same stream
+    constexpr uint32_t ROW16 = NT_ROW_BYTES >> 4, WBLK16 = C::WBLK >> 4;
+    // The whole issue loop is warp-convergent (every lane runs it on warp-uniform values, one lane is elected inside
+    // umma_bf16_ws): descriptors stay in uniform registers, UTCHMMAs issue back to back.
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
       const int ty = (tile / a.tiles_x) % a.tiles_y;
       const int rows_left = a.H - ty * rows_tile;
@@ -307,60 +336,63 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       mbar_wait(smem_u32(&s_full[stage]), phase);
       tc_fence_after();
       const uint32_t st16 = (ring + stage * stage_bytes) >> 4;
-      for (int t = 0; t < tmv; ++t, ++it) {
-        const uint32_t slot = it % C::NSLOT, sphase = (it / C::NSLOT) & 1;
-        mbar_wait(smem_u32(&t_empty[slot]), sphase ^ 1);
-        tc_fence_after();
-        if (lane == 0) {
+      for (int t = 0; t < tmv; ++t) {
+        if ((int)(it % NT_ISSUERS) == issuer) {
+          mbar_wait(smem_u32(&t_empty[slot]), sphase ^ 1);
+          tc_fence_after();
 #pragma unroll
           for (int s = 0; s < 2; ++s) {
             const uint32_t d = tmem_base + slot * C::SLOT_COLS + s * C::NROW;
-            uint32_t acc = 0;
+            const uint32_t xs = st16 + ((uint32_t)(s * 2) * a.rows_ld + 4 * t) * ROW16;     // stream s, part hi, first row of the M-tile
             // [x_hi@dy ; x_lo@dy] x [W_hi[dy] ; W_hi[dy]]  (B's two K-halves alias one block: LBO = 0)
 #pragma unroll
             for (int src = 0; src < NSRC; ++src)
 #pragma unroll
               for (int dy = 0; dy < K; ++dy) {
-                const uint32_t ax = st16 + (((uint32_t)(src * 4 + s * 2) * a.rows_ld + 4 * t + dy) * NT_ROW_BYTES >> 4);
-                const uint32_t bw = w16 + (((src * K + dy) * 2) * C::WBLK >> 4);
-                umma_bf16(d, ((uint64_t)DESC_HI << 32) | (ax | lbo_hl), ((uint64_t)DESC_HI << 32) | bw, IDESC, acc);
-                acc = 1;
+                const uint32_t ax = xs + (uint32_t)src * 4 * plane16 + dy * ROW16;
+                const uint32_t bw = w16 + ((src * K + dy) * 2) * WBLK16;
+                umma_bf16_ws(d, ((uint64_t)DESC_HI << 32) | (ax | lbo_hl), ((uint64_t)DESC_HI << 32) | bw, IDESC,
+                             (src == 0 && dy == 0) ? 0u : 1u);
               }
             // x_hi x W_lo, two chunks per MMA
             if constexpr (NSRC == 1) {
 #pragma unroll
               for (int dy = 0; dy < K; dy += 2) {
+                constexpr uint32_t A_LBO_PAIR = ROW16 << 16;
                 const bool pair = dy + 1 < K;
-                const uint32_t ax = st16 + (((uint32_t)(s * 2) * a.rows_ld + 4 * t + dy) * NT_ROW_BYTES >> 4);
-                const uint32_t bw = w16 + ((dy * 2 + 1) * C::WBLK >> 4);
+                const uint32_t ax = xs + dy * ROW16;
+                const uint32_t bw = w16 + (dy * 2 + 1) * WBLK16;
                 // paired: second K-half = next staged row against W_lo[dy+1]; last odd tap: both halves read row dy,
                 // the second against the zero block (which follows W_lo[K-1] in the packed weights)
-                const uint32_t a_lbo = pair ? ((uint32_t)NT_ROW_BYTES >> 4) << 16 : 0u;
-                const uint32_t b_lbo = (uint32_t)((pair ? 2 : 1) * C::WBLK >> 4) << 16;
-                umma_bf16(d, ((uint64_t)DESC_HI << 32) | (ax | a_lbo), ((uint64_t)DESC_HI << 32) | (bw | b_lbo), IDESC, 1u);
+                const uint32_t a_lbo = pair ? A_LBO_PAIR : 0u;
+                const uint32_t b_lbo = (uint32_t)((pair ? 2 : 1) * WBLK16) << 16;
+                umma_bf16_ws(d, ((uint64_t)DESC_HI << 32) | (ax | a_lbo), ((uint64_t)DESC_HI << 32) | (bw | b_lbo), IDESC, 1u);
               }
             } else {
 #pragma unroll
               for (int dy = 0; dy < K; ++dy) {
-                const uint32_t ax = st16 + (((uint32_t)(s * 2) * a.rows_ld + 4 * t + dy) * NT_ROW_BYTES >> 4);
-                const uint32_t bw = w16 + ((dy * 2 + 1) * C::WBLK >> 4);
-                const uint32_t a_lbo = ((4 * plane_bytes) >> 4) << 16;                  // same plane of source B
-                const uint32_t b_lbo = (uint32_t)(2 * K * C::WBLK >> 4) << 16;          // W_lo[B][dy]
-                umma_bf16(d, ((uint64_t)DESC_HI << 32) | (ax | a_lbo), ((uint64_t)DESC_HI << 32) | (bw | b_lbo), IDESC, 1u);
+                const uint32_t ax = xs + dy * ROW16;
+                const uint32_t bw = w16 + (dy * 2 + 1) * WBLK16;
+                const uint32_t a_lbo = (4 * plane16) << 16;                            // same plane of source B
+                constexpr uint32_t B_LBO = (uint32_t)(2 * K * WBLK16) << 16;           // W_lo[B][dy]
+                umma_bf16_ws(d, ((uint64_t)DESC_HI << 32) | (ax | a_lbo), ((uint64_t)DESC_HI << 32) | (bw | B_LBO), IDESC, 1u);
               }
             }
           }
-          umma_commit(smem_u32(&t_full[slot]));
+          umma_commit_ws(smem_u32(&t_full[slot]));
         }
-        __syncwarp();
+        ++it;
+        if (++slot == (uint32_t)C::NSLOT) { slot = 0; sphase ^= 1; }
       }
-      if (lane == 0) umma_commit(smem_u32(&s_empty[stage]));     // every MMA reading this stage has retired
-      __syncwarp();
+      umma_commit_ws(smem_u32(&s_empty[stage]));                 // every MMA of this issuer reading the stage has retired
       stage ^= 1; if (stage == 0) phase ^= 1;
     }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
+  } else if (warp >= 4) {
+    // ===================== epilogue (warps 4..) =====================
+    // One warp per SM sub-partition cannot hide its own instruction latencies (ncu/events: 2 090 cycles per M-tile with a
+    // single set against 512 of MMAs), so NT_ESETS sets of four warps work on alternate M-tiles.
     const int q = warp & 3;                                      // TMEM lane quarter = staged row of the M-tile
+    const int set = (warp - 4) >> 2;
     const N8Geom gs = N8Geom::make(a.B, a.H, a.W);
     const N8Geom gp = N8Geom::make(a.B, a.H / 2, a.W / 2);
     const N8Geom gu = N8Geom::make(a.B, 2 * a.H, 2 * a.W);
@@ -372,6 +404,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       const int rows_left = a.H - y0;
       const int tmv = rows_left >= rows_tile ? a.TM : (rows_left + 3) / 4;
       for (int t = 0; t < tmv; ++t, ++it) {
+        if ((int)(it % NT_ESETS) != set) continue;
         const uint32_t slot = it % C::NSLOT, sphase = (it / C::NSLOT) & 1;
         mbar_wait(smem_u32(&t_full[slot]), sphase);
         tc_fence_after();
@@ -432,10 +465,10 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
         if (a.out_pool) {
           // the two independent 2x2/2 max-pools (step1.py:62-74), ATen's window order and `(v > m) || isnan(v)` update.
           // The lower row of a window belongs to the next epilogue warp: exchanged through shared memory.
-          float(*px)[16][32] = s_px[it & 1];
+          float(*px)[16][32] = reinterpret_cast<float(*)[16][32]>(s_px + (size_t)(set * 2 + ((it / NT_ESETS) & 1)) * 4 * 16 * 32);
 #pragma unroll
           for (int co = 0; co < 8; ++co) { px[q][co][lane] = yv[co]; px[q][8 + co][lane] = cv[co]; }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(1 + set) : "memory");
           if ((q & 1) == 0) {
             float yp[8], cp[8];
 #pragma unroll
@@ -493,6 +526,67 @@ __global__ void nconv_tc_pack_kernel(const float* __restrict__ w, __nv_bfloat16*
   }
 }
 
+// ---- one launch for all ring fills / all weight packs of a DNET forward (dnet_pipeline.cu) -------------------------
+__global__ void n8_zero_rings_multi_kernel(const N8RingJobs jobs) {
+  const int j = blockIdx.y;
+  if (j >= jobs.n) return;
+  const N8Geom g = N8Geom::make(jobs.B, jobs.H[j], jobs.W[j]);
+  __nv_bfloat16* buf = reinterpret_cast<__nv_bfloat16*>(jobs.buf[j]);
+  const int ring_px = 2 * N8_RING * g.Wp + 2 * N8_RING * g.H;
+  const long long total = (long long)g.B * 4 * ring_px;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(idx % ring_px);
+    const long long pl = idx / ring_px;
+    int y, x;
+    if (r < 2 * N8_RING * g.Wp) {
+      const int rr = r / g.Wp; x = r % g.Wp;
+      y = rr < N8_RING ? rr : g.Hp - 2 * N8_RING + rr;
+    } else {
+      const int q = r - 2 * N8_RING * g.Wp;
+      const int cc = q % (2 * N8_RING);
+      y = N8_RING + q / (2 * N8_RING);
+      x = cc < N8_RING ? cc : g.Wp - 2 * N8_RING + cc;
+    }
+    *reinterpret_cast<uint4*>(buf + pl * g.plane_elems() + ((size_t)y * g.Wp + x) * 8) = make_uint4(0, 0, 0, 0);
+  }
+}
+
+int n8_zero_rings_multi(const N8RingJobs& jobs, cudaStream_t st) {
+  LaunchScope ls(st, "n8_zero_rings", 0.0, 0.0);
+  n8_zero_rings_multi_kernel<<<dim3(148, jobs.n), 256, 0, st>>>(jobs);
+  return (int)cudaGetLastError();
+}
+
+__global__ void nconv_tc_pack_multi_kernel(const NtPackJobs jobs) {
+  const int j = blockIdx.y;
+  if (j >= jobs.n) return;
+  const int K = jobs.K[j], NSRC = jobs.nsrc[j], a_first = jobs.a_first[j];
+  const int NROW = (K * 8 + 15) / 16 * 16;
+  const float* w = jobs.w[j];
+  __nv_bfloat16* wp = reinterpret_cast<__nv_bfloat16*>(jobs.wpack[j]);
+  const int nblk = 2 * NSRC * K + 1, total = nblk * NROW * 8, CI = 8 * NSRC;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int e = idx & 7, nrow = (idx >> 3) % NROW, blk = idx / (8 * NROW);
+    float v = 0.f;
+    const int part = blk & 1, sd = blk >> 1;
+    const int dx = nrow >> 3, co = nrow & 7;
+    if (blk < nblk - 1 && dx < K) {
+      const int src = sd / K, dy = sd % K;
+      const int ciw = (NSRC == 1) ? e : ((src == 0) == (a_first != 0) ? e : 8 + e);
+      v = __ldg(w + (((size_t)co * CI + ciw) * K + dy) * K + dx);
+    }
+    __nv_bfloat16 hi, lo;
+    split_bf16(v, hi, lo);
+    wp[idx] = part == 0 ? hi : lo;
+  }
+}
+
+int nconv_tc_pack_multi(const NtPackJobs& jobs, cudaStream_t st) {
+  LaunchScope ls(st, "tc_nconv_pack_weights", 0.0, 0.0);
+  nconv_tc_pack_multi_kernel<<<dim3(4, jobs.n), 256, 0, st>>>(jobs);
+  return (int)cudaGetLastError();
+}
+
 template <int K, int NSRC>
 static int launch_nconv_tc(const nconv_b200_nconv_tc_desc* d, cudaStream_t st) {
   using C = NtCfg<K>;
@@ -516,7 +610,7 @@ static int launch_nconv_tc(const nconv_b200_nconv_tc_desc* d, cudaStream_t st) {
   int TM = (d->H + 3) / 4;
   const int cap = (K == 5) ? 10 : 6;
   if (TM > cap) TM = cap;
-  while (TM > 1 && W_BYTES + 2 * (size_t)NSRC * 4 * (4 * TM + C::HALO) * NT_ROW_BYTES > (size_t)NT_SMEM_MAX) --TM;
+  while (TM > 1 && W_BYTES + NT_PX_BYTES + 2 * (size_t)NSRC * 4 * (4 * TM + C::HALO) * NT_ROW_BYTES > (size_t)NT_SMEM_MAX) --TM;
   NtArgs a = {};
   a.wpack = (const __nv_bfloat16*)d->wpack; a.w = d->w; a.bias = d->bias;
   a.out_n8 = (__nv_bfloat16*)d->out_n8; a.out_pool = (__nv_bfloat16*)d->out_pool; a.out_up = (__nv_bfloat16*)d->out_up;
@@ -526,7 +620,7 @@ static int launch_nconv_tc(const nconv_b200_nconv_tc_desc* d, cudaStream_t st) {
   a.tiles_x = (d->W + C::WT - 1) / C::WT; a.tiles_y = (d->H + 4 * TM - 1) / (4 * TM);
   a.ntiles = a.tiles_x * a.tiles_y * d->B;
   a.eps = d->eps;
-  size_t smem = W_BYTES + 2 * (size_t)NSRC * 4 * a.rows_ld * NT_ROW_BYTES;
+  size_t smem = W_BYTES + NT_PX_BYTES + 2 * (size_t)NSRC * 4 * a.rows_ld * NT_ROW_BYTES;
   if (smem < (size_t)NT_SMEM_MIN) smem = NT_SMEM_MIN;
   // N8 source seen as [planes = 4B][rows = H+4][(W+4)*4 32-bit words]; box [128 words][rows_ld][1]
   alignas(64) CUtensorMap tm[2];

@@ -86,7 +86,9 @@ class DNET(nn.Module):
             params = []
             for l in self._layers():
                 params += [l.weight, l.bias]
-            return _K.dnet_forward(S, params)
+            # inference (no_grad) takes the tensor-core pipeline where the shape allows; a frozen step 1 inside a
+            # recording (training) step stays on the fp32 CUDA-core pipeline
+            return _K.dnet_forward(S, params, torch.is_grad_enabled())
 
         # Staged graph (training): every stage is a custom op with an analytic backward.
         c0 = _K.confidence_mask(S, 0.01)

@@ -97,6 +97,8 @@ SIGNATURES = {
     "nconv_b200_nconv_tc_wpack_bytes": (c_size_t, [c_int] * 2),
     "nconv_b200_nconv_tc_pack_weights": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
     "nconv_b200_nconv_tc": (c_int, [POINTER(NconvTcDesc), c_void_p]),
+    "nconv_b200_dnet_forward_fp32": (c_int, [c_void_p, POINTER(c_void_p), c_void_p, c_int, c_int, c_int,
+                                             c_void_p, c_size_t, c_void_p]),
     "nconv_b200_conv2d_fwd": (c_int, [POINTER(ConvDesc), c_void_p]),
     "nconv_b200_convT4x4s2_fwd": (c_int, [c_void_p] * 6 + [c_int] * 7 + [c_void_p]),
     "nconv_b200_bilinear_ac_fwd": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p]),

@@ -51,7 +51,7 @@ def upcat(skip, low, skip_first: bool):
     return torch.cat((skip, up), 1) if skip_first else torch.cat((up, skip), 1)
 
 
-def dnet_forward(S, params: List[torch.Tensor]):
+def dnet_forward(S, params: List[torch.Tensor], fp32_only: bool = False):
     """DNET.forward, step1.py:51-94, crop generalised to [1:H+1, 1:W+1]."""
     def layer(i, x, c):
         return nconv2d(x, c, params[2 * i], params[2 * i + 1], _EPS_LAYERS[i][0], _EPS_LAYERS[i][1], 1e-7)

@@ -283,7 +283,7 @@ torch.library.register_autograd("nconv_b200::upcat", _upcat_bwd, setup_context=_
 # --------------------------------------------------------------------------------------
 # whole DNET forward (inference)
 # --------------------------------------------------------------------------------------
-def _dnet_forward(S, params: Sequence[torch.Tensor]):
+def _dnet_forward(S, params: Sequence[torch.Tensor], fp32_only: bool = False):
     S = _prep(S, "S")
     if S.dim() != 4 or S.shape[1] != 1:
         raise ValueError("dnet_forward: S must be [B,1,H,W]")
@@ -300,11 +300,13 @@ def _dnet_forward(S, params: Sequence[torch.Tensor]):
     ws = _scratch(S.device, nbytes, "dnet")          # cached per (device, stream): 3.9 GB at B = 32, 480x640
     arr = (c_void_p * 18)(*[p.data_ptr() for p in params])
     with torch.cuda.device(S.device):
-        check(_C.nconv_b200_dnet_forward(_p(S), arr, _p(out), B, H, W, _p(ws), nbytes, _stream(S)), "dnet_forward")
+        fn = _C.nconv_b200_dnet_forward_fp32 if fp32_only else _C.nconv_b200_dnet_forward
+        check(fn(_p(S), arr, _p(out), B, H, W, _p(ws), nbytes, _stream(S)), "dnet_forward")
     return out
 
 
-_define("dnet_forward(Tensor S, Tensor[] params) -> Tensor", _dnet_forward, lambda S, params: torch.empty_like(S))
+_define("dnet_forward(Tensor S, Tensor[] params, bool fp32_only=False) -> Tensor", _dnet_forward,
+        lambda S, params, fp32_only=False: torch.empty_like(S))
 
 
 # --------------------------------------------------------------------------------------
