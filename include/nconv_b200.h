@@ -124,6 +124,10 @@ int nconv_b200_dnet_forward(const float* S, const float* const* params, float* o
 int nconv_b200_dnet_forward_fp32(const float* S, const float* const* params, float* out, int B,
                                  int H, int W, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Debug aid (no reference counterpart): 64 bytes of pinned, device-mapped host memory in which a tcgen05 NConv kernel
+ * records {barrier code, block, warp, tile / M-tile index, parity} when one of its bounded barrier waits gives up. */
+int nconv_b200_debug_buffer(void* pinned_host_64_bytes);
+
 /* ---- tensor-core NConv2d for DNET's FMA-bound layers (8->8 5x5, [8|8]->8 3x3) — step1.py:116-149 on tcgen05 ----
  * "N8" activation layout: an 8-channel (data, confidence) pair held as the two streams the layer
  * correlates, split to bf16 hi/lo (16 mantissa bits) with a 2-pixel zero ring:

@@ -46,6 +46,13 @@ struct NearestMap {
 // ties, NaN propagates) — /root/reference/models/step1.py:62-74 via F.max_pool2d.
 __device__ __forceinline__ float pool_max(float m, float v) { return (v > m || v != v) ? v : m; }
 
+// Same value as a chain of pool_max updates over a window (max, NaN if any element is NaN), one FMNMX.NAN each.
+__device__ __forceinline__ float max_nan(float a, float b) {
+  float d;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+  return d;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);

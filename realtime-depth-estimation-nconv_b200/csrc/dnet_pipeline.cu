@@ -6,6 +6,7 @@
 #include "common.cuh"
 #include "nconv_b200.h"
 #include "nconv_tc.h"
+#include <cstdio>
 #include <cstdlib>
 
 namespace {
@@ -94,7 +95,17 @@ static int dnet_forward_tc(const float* S, const float* const* params, float* ou
     if ((rc = nconv::nconv_tc_pack_multi(pj, st))) return rc;
   }
   const float eps = 1e-7f;
+  // NCONV_B200_DNET_SYNC=1 (debugging only): synchronise after every launch and name the one that failed
+  static const bool dbg_sync = getenv("NCONV_B200_DNET_SYNC") != nullptr;
+  auto check = [&](const char* what) {
+    if (!dbg_sync) return 0;
+    const cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) fprintf(stderr, "[nconv_b200] dnet_forward_tc: %s failed: %s\n", what, cudaGetErrorString(e));
+    return (int)e;
+  };
+  if ((rc = check("prep"))) return rc;
   if ((rc = nconv_b200_nconv1_n8(S, params[0], params[1], buf(A0), B, H, W, 0.01f, eps, stream))) return rc;   // step1.py:53-56
+  if ((rc = check("nconv1"))) return rc;
   auto layer = [&](int i, int lvl) {
     nconv_b200_nconv_tc_desc d = {};
     d.wpack = ws + p.woff[i]; d.w = params[2 * (i + 1)]; d.bias = params[2 * (i + 1) + 1];
@@ -102,20 +113,27 @@ static int dnet_forward_tc(const float* S, const float* const* params, float* ou
     return d;
   };
   { nconv_b200_nconv_tc_desc d = layer(0, 0); d.a = buf(A0); d.out_n8 = buf(TX1); d.out_pool = buf(TP1);       // nconv2 + pools, :57-64
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv2"))) return rc; }
   { nconv_b200_nconv_tc_desc d = layer(1, 1); d.a = buf(TP1); d.out_n8 = buf(TX2); d.out_pool = buf(TP2);      // nconv_down1 + pools, :65-69
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv_down1"))) return rc; }
   { nconv_b200_nconv_tc_desc d = layer(2, 2); d.a = buf(TP2); d.out_n8 = buf(TX3); d.out_pool = buf(TP3);      // nconv_down2 + pools, :70-74
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv_down2"))) return rc; }
   { nconv_b200_nconv_tc_desc d = layer(3, 3); d.a = buf(TP3); d.out_up = buf(TU4);                             // nconv_down3, upsampled for :78-79
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv_down3"))) return rc; }
   { nconv_b200_nconv_tc_desc d = layer(4, 2); d.a = buf(TX3); d.b = buf(TU4); d.out_up = buf(TU34);            // nconv4 on cat(x3, up(x4)), :80, :83-84
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv4"))) return rc; }
   { nconv_b200_nconv_tc_desc d = layer(5, 1); d.a = buf(TX2); d.b = buf(TU34); d.out_up = buf(TU23);           // nconv5 on cat(x2, up(x34)), :85, :88-89
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv5"))) return rc; }
   { nconv_b200_nconv_tc_desc d = layer(6, 0); d.a = buf(TX1); d.b = buf(TU23);                                  // nconv6 on cat(up(x23), x1) -> nconv7 -> crop, :90-94
     d.w_tail = params[16]; d.b_tail = params[17]; d.out_tail = out;
-    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc; }
+    if ((rc = nconv_b200_nconv_tc(&d, stream))) return rc;
+    if ((rc = check("nconv6"))) return rc; }
   return 0;
 }
 

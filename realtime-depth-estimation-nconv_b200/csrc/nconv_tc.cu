@@ -108,11 +108,11 @@ __global__ void n8_unpack_kernel(const __nv_bfloat16* __restrict__ in, float* __
 // all 8 output channels of ONE pixel with FFMA2 over channel pairs (weights broadcast from shared memory) and writes
 // its four 16-byte N8 vectors (consecutive lanes = consecutive pixels: 512-byte runs).
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int N1_TW = 32, N1_TH = 32, N1_PY = 4;     // a thread owns rows ty, ty+8, ty+16, ty+24 of its column: weight reads shared by 4 pixels
+constexpr int N1_TW = 32, N1_TH = 16, N1_PY = 2;     // a thread owns rows ty and ty+8 of its column: weight reads shared by 2 pixels
 
 __global__ void __launch_bounds__(256) nconv1_n8_kernel(const float* __restrict__ S, const float* __restrict__ w, const float* __restrict__ bias,
                                                         __nv_bfloat16* __restrict__ out, N8Geom g, float thr, float eps) {
-  __shared__ float s_in[N1_TH + 4][N1_TW + 4];
+  __shared__ float2 s_in[N1_TH + 4][N1_TW + 4];                   // (S*conf, conf) with conf = S > thr; zero outside the image
   __shared__ __align__(16) float s_w[25][8];
   __shared__ float s_rs[8], s_b[8];
   const int tid = threadIdx.x;
@@ -122,7 +122,9 @@ __global__ void __launch_bounds__(256) nconv1_n8_kernel(const float* __restrict_
   for (int i = tid; i < (N1_TH + 4) * (N1_TW + 4); i += 256) {
     const int r = i / (N1_TW + 4), cc = i % (N1_TW + 4);
     const int gy = y0 - 2 + r, gx = x0 - 2 + cc;
-    s_in[r][cc] = (gy >= 0 && gy < g.H && gx >= 0 && gx < g.W) ? __ldg(S + ((size_t)n * g.H + gy) * g.W + gx) : 0.f;
+    const float x = (gy >= 0 && gy < g.H && gx >= 0 && gx < g.W) ? __ldg(S + ((size_t)n * g.H + gy) * g.W + gx) : 0.f;
+    const float c = x > thr ? 1.f : 0.f;
+    s_in[r][cc] = make_float2(x * c, c);
   }
   __syncthreads();
   if (tid < 8) {
@@ -144,11 +146,9 @@ __global__ void __launch_bounds__(256) nconv1_n8_kernel(const float* __restrict_
       const ulonglong2 w23 = *reinterpret_cast<const ulonglong2*>(&s_w[u * 5 + v][4]);
 #pragma unroll
       for (int p = 0; p < N1_PY; ++p) {
-        const float x = s_in[ty + 8 * p + u][tx + v];
-        const float c = x > thr ? 1.f : 0.f;
-        const float xc = x * c;
-        ffma2(aN[p][0], w01.x, xc); ffma2(aN[p][1], w01.y, xc); ffma2(aN[p][2], w23.x, xc); ffma2(aN[p][3], w23.y, xc);
-        ffma2(aD[p][0], w01.x, c);  ffma2(aD[p][1], w01.y, c);  ffma2(aD[p][2], w23.x, c);  ffma2(aD[p][3], w23.y, c);
+        const float2 xc = s_in[ty + 8 * p + u][tx + v];
+        ffma2(aN[p][0], w01.x, xc.x); ffma2(aN[p][1], w01.y, xc.x); ffma2(aN[p][2], w23.x, xc.x); ffma2(aN[p][3], w23.y, xc.x);
+        ffma2(aD[p][0], w01.x, xc.y); ffma2(aD[p][1], w01.y, xc.y); ffma2(aD[p][2], w23.x, xc.y); ffma2(aD[p][3], w23.y, xc.y);
       }
     }
   __syncthreads();
@@ -169,10 +169,10 @@ __global__ void __launch_bounds__(256) nconv1_n8_kernel(const float* __restrict_
     }
     uint4 h, l;
     const size_t po = g.pixel(oy, ox);
-    split8(xc, h, l);
+    split8_fast(xc, h, l);
     *reinterpret_cast<uint4*>(out + g.plane(n, 0, 0) + po) = h;
     *reinterpret_cast<uint4*>(out + g.plane(n, 0, 1) + po) = l;
-    split8(cc, h, l);
+    split8_fast(cc, h, l);
     *reinterpret_cast<uint4*>(out + g.plane(n, 1, 0) + po) = h;
     *reinterpret_cast<uint4*>(out + g.plane(n, 1, 1) + po) = l;
   }
@@ -211,6 +211,7 @@ struct NtArgs {
   const float* w_tail; const float* b_tail; float* out_tail;
   int B, H, W, CI;
   int TM, rows_ld, tiles_x, tiles_y, ntiles;
+  int issuers, esets;          // active MMA issuer warps (<= NT_ISSUERS) / epilogue sets (<= NT_ESETS)
   float eps;
 };
 
@@ -228,15 +229,43 @@ template <int K> __device__ __forceinline__ void nt_load_stream(uint32_t taddr, 
   else { tmem_ld16(taddr, v); tmem_ld8(taddr + 16, v + 16); }
 }
 
-// 8 floats -> 4 x 16-byte N8 vectors at `po` of image n
-__device__ __forceinline__ void n8_store(__nv_bfloat16* buf, const N8Geom& g, int n, size_t po, const float* xc, const float* cc) {
-  uint4 h, l;
-  split8(xc, h, l);
-  *reinterpret_cast<uint4*>(buf + g.plane(n, 0, 0) + po) = h;
-  *reinterpret_cast<uint4*>(buf + g.plane(n, 0, 1) + po) = l;
-  split8(cc, h, l);
-  *reinterpret_cast<uint4*>(buf + g.plane(n, 1, 0) + po) = h;
-  *reinterpret_cast<uint4*>(buf + g.plane(n, 1, 1) + po) = l;
+// (data*conf, conf) of one pixel as its four 16-byte N8 vectors
+struct N8Px { uint4 xh, xl, ch, cl; };
+__device__ __forceinline__ N8Px n8_make(const float* xc, const float* cc) {
+  N8Px p;
+  split8_fast(xc, p.xh, p.xl);
+  split8_fast(cc, p.ch, p.cl);
+  return p;
+}
+__device__ __forceinline__ void n8_put(__nv_bfloat16* buf, const N8Geom& g, int n, size_t po, const N8Px& p) {
+  __nv_bfloat16* b0 = buf + g.plane(n, 0, 0) + po;
+  const size_t pe = g.plane_elems();
+  *reinterpret_cast<uint4*>(b0) = p.xh;
+  *reinterpret_cast<uint4*>(b0 + pe) = p.xl;
+  *reinterpret_cast<uint4*>(b0 + 2 * pe) = p.ch;
+  *reinterpret_cast<uint4*>(b0 + 3 * pe) = p.cl;
+}
+
+// Debug aid: nconv_b200_debug_buffer() hands the library 64 bytes of pinned host memory; a wait that times out records
+// {code, block, warp, extra} there before trapping, so the host can tell which barrier of which role gave up.
+__device__ unsigned int* g_nt_dbg = nullptr;
+// The loop exit is a warp vote, i.e. WARP-UNIFORM: every lane leaves the wait in the same iteration.  This matters for
+// the MMA issuer warps, whose code after the wait is warp-convergent and runs on the uniform datapath (one UTCHMMA /
+// commit per warp execution): with a per-lane exit (`while (!try_wait)`) the compiler emits no reconvergence point, the
+// lanes that saw the phase flip first ran ahead as their own group and the MMAs and commits were issued once per group
+// - duplicate barrier arrivals, and a deadlock that showed up only in long runs (B >= 34 at 352x1216).
+__device__ __forceinline__ void nt_wait(uint32_t bar, uint32_t parity, unsigned code, unsigned extra) {
+  uint32_t spins = 0;
+  while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+    if (++spins > (1u << 22)) {
+      unsigned int* d = g_nt_dbg;
+      if (d && atomicCAS(d, 0u, code) == 0u) {
+        d[1] = blockIdx.x; d[2] = threadIdx.x >> 5; d[3] = extra; d[4] = parity;
+        __threadfence_system();
+      }
+      __trap();
+    }
+  }
 }
 
 template <int K, int NSRC>
@@ -269,7 +298,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
     s_w7[threadIdx.x] = a.w_tail ? __ldg(a.w_tail + threadIdx.x) : 0.f;
   }
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), NT_ISSUERS); }
+    for (int s = 0; s < 2; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), a.issuers); }
     for (int s = 0; s < C::NSLOT; ++s) { mbar_init(smem_u32(&t_full[s]), 1); mbar_init(smem_u32(&t_empty[s]), 4); }
     mbar_init(smem_u32(&s_wfull), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -295,7 +324,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
       const int tx = tile % a.tiles_x, ty = (tile / a.tiles_x) % a.tiles_y, n = tile / (a.tiles_x * a.tiles_y);
       const int y0 = ty * rows_tile, x0 = tx * C::WT;
-      mbar_wait(smem_u32(&s_empty[stage]), phase ^ 1);
+      nt_wait(smem_u32(&s_empty[stage]), phase ^ 1, 1, tile);
       const uint32_t full = smem_u32(&s_full[stage]);
       if (lane == 0) mbar_arrive_expect_tx(full, stage_bytes);
       __syncwarp();
@@ -313,14 +342,14 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       __syncwarp();
       stage ^= 1; if (stage == 0) phase ^= 1;
     }
-  } else if (warp == 1 || warp == 2) {
+  } else if (warp == 1 || (warp == 2 && a.issuers == 2)) {
     // ===================== MMA issuers =====================
     // Issuing one MMA costs ~100 cycles of the issuing warp (descriptor moves to uniform registers, elect, branch), more
     // than the MMA itself at N = 32..48, so two warps issue for alternate M-tiles (independent accumulator slots).
     const int issuer = warp - 1;
     constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(C::NROW >> 3) << 17) | ((128u >> 4) << 24);
     constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);      // SBO = 128 B, descriptor version 1
-    mbar_wait(smem_u32(&s_wfull), 0);
+    nt_wait(smem_u32(&s_wfull), 0, 2, 0);
     tc_fence_after();
     uint32_t stage = 0, phase = 0, it = 0, slot = 0, sphase = 0;
     const uint32_t w16 = smem_base >> 4;
@@ -333,12 +362,12 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       const int ty = (tile / a.tiles_x) % a.tiles_y;
       const int rows_left = a.H - ty * rows_tile;
       const int tmv = rows_left >= rows_tile ? a.TM : (rows_left + 3) / 4;       // M-tiles holding image rows
-      mbar_wait(smem_u32(&s_full[stage]), phase);
+      nt_wait(smem_u32(&s_full[stage]), phase, 3, tile);
       tc_fence_after();
       const uint32_t st16 = (ring + stage * stage_bytes) >> 4;
       for (int t = 0; t < tmv; ++t) {
-        if ((int)(it % NT_ISSUERS) == issuer) {
-          mbar_wait(smem_u32(&t_empty[slot]), sphase ^ 1);
+        if ((int)(it % (uint32_t)a.issuers) == issuer) {
+          nt_wait(smem_u32(&t_empty[slot]), sphase ^ 1, 4, it);
           tc_fence_after();
 #pragma unroll
           for (int s = 0; s < 2; ++s) {
@@ -387,7 +416,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       umma_commit_ws(smem_u32(&s_empty[stage]));                 // every MMA of this issuer reading the stage has retired
       stage ^= 1; if (stage == 0) phase ^= 1;
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < 4 + 4 * a.esets) {
     // ===================== epilogue (warps 4..) =====================
     // One warp per SM sub-partition cannot hide its own instruction latencies (ncu/events: 2 090 cycles per M-tile with a
     // single set against 512 of MMAs), so NT_ESETS sets of four warps work on alternate M-tiles.
@@ -404,9 +433,9 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       const int rows_left = a.H - y0;
       const int tmv = rows_left >= rows_tile ? a.TM : (rows_left + 3) / 4;
       for (int t = 0; t < tmv; ++t, ++it) {
-        if ((int)(it % NT_ESETS) != set) continue;
+        if ((int)(it % (uint32_t)a.esets) != set) continue;
         const uint32_t slot = it % C::NSLOT, sphase = (it / C::NSLOT) & 1;
-        mbar_wait(smem_u32(&t_full[slot]), sphase);
+        nt_wait(smem_u32(&t_full[slot]), sphase, 5, it);
         tc_fence_after();
         const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + slot * C::SLOT_COLS;
         uint32_t vN[C::NUSE], vD[C::NUSE];
@@ -454,18 +483,21 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
               a.y[o] = yv[co]; a.cout[o] = cv[co];
             }
           }
-          if (a.out_n8) n8_store(a.out_n8, gs, n, gs.pixel(oy, ox), xc, cv);
-          if (a.out_up) {
+          if (a.out_n8 || a.out_up) {
+            const N8Px p = n8_make(xc, cv);
+            if (a.out_n8) n8_put(a.out_n8, gs, n, gs.pixel(oy, ox), p);
+            if (a.out_up) {
 #pragma unroll
-            for (int i = 0; i < 2; ++i)
+              for (int i = 0; i < 2; ++i)
 #pragma unroll
-              for (int j = 0; j < 2; ++j) n8_store(a.out_up, gu, n, gu.pixel(2 * oy + i, 2 * ox + j), xc, cv);
+                for (int j = 0; j < 2; ++j) n8_put(a.out_up, gu, n, gu.pixel(2 * oy + i, 2 * ox + j), p);
+            }
           }
         }
         if (a.out_pool) {
           // the two independent 2x2/2 max-pools (step1.py:62-74), ATen's window order and `(v > m) || isnan(v)` update.
           // The lower row of a window belongs to the next epilogue warp: exchanged through shared memory.
-          float(*px)[16][32] = reinterpret_cast<float(*)[16][32]>(s_px + (size_t)(set * 2 + ((it / NT_ESETS) & 1)) * 4 * 16 * 32);
+          float(*px)[16][32] = reinterpret_cast<float(*)[16][32]>(s_px + (size_t)(set * 2 + ((it / (uint32_t)a.esets) & 1)) * 4 * 16 * 32);
 #pragma unroll
           for (int co = 0; co < 8; ++co) { px[q][co][lane] = yv[co]; px[q][8 + co][lane] = cv[co]; }
           asm volatile("bar.sync %0, 128;" ::"r"(1 + set) : "memory");
@@ -476,18 +508,16 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
               const float y01 = __shfl_down_sync(0xffffffffu, yv[co], 1), c01 = __shfl_down_sync(0xffffffffu, cv[co], 1);
               const float y10 = px[q + 1][co][lane], c10 = px[q + 1][8 + co][lane];
               const float y11 = __shfl_down_sync(0xffffffffu, y10, 1), c11 = __shfl_down_sync(0xffffffffu, c10, 1);
-              float m = -INFINITY;
-              m = pool_max(m, yv[co]); m = pool_max(m, y01); m = pool_max(m, y10); m = pool_max(m, y11);
-              float k = -INFINITY;
-              k = pool_max(k, cv[co]); k = pool_max(k, c01); k = pool_max(k, c10); k = pool_max(k, c11);
-              yp[co] = m; cp[co] = k;
+              // max over the window, NaN if any element is NaN: the value ATen's `(v > m) || isnan(v)` chain leaves
+              yp[co] = max_nan(max_nan(yv[co], y01), max_nan(y10, y11));
+              cp[co] = max_nan(max_nan(cv[co], c01), max_nan(c10, c11));
             }
             const int py = oy >> 1, pxo = ox >> 1;
             if (valid && (lane & 1) == 0 && py < gp.H && pxo < gp.W) {
               float xcp[8];
 #pragma unroll
               for (int co = 0; co < 8; ++co) xcp[co] = yp[co] * cp[co];
-              n8_store(a.out_pool, gp, n, gp.pixel(py, pxo), xcp, cp);
+              n8_put(a.out_pool, gp, n, gp.pixel(py, pxo), n8_make(xcp, cp));
             }
           }
         }
@@ -620,6 +650,12 @@ static int launch_nconv_tc(const nconv_b200_nconv_tc_desc* d, cudaStream_t st) {
   a.tiles_x = (d->W + C::WT - 1) / C::WT; a.tiles_y = (d->H + 4 * TM - 1) / (4 * TM);
   a.ntiles = a.tiles_x * a.tiles_y * d->B;
   a.eps = d->eps;
+  {
+    static const char* ei = getenv("NCONV_B200_NT_ISSUERS");     // A/B measurements and debugging only
+    static const char* es = getenv("NCONV_B200_NT_ESETS");
+    a.issuers = ei && atoi(ei) == 1 ? 1 : NT_ISSUERS;
+    a.esets = es && atoi(es) == 1 ? 1 : NT_ESETS;
+  }
   size_t smem = W_BYTES + NT_PX_BYTES + 2 * (size_t)NSRC * 4 * a.rows_ld * NT_ROW_BYTES;
   if (smem < (size_t)NT_SMEM_MIN) smem = NT_SMEM_MIN;
   // N8 source seen as [planes = 4B][rows = H+4][(W+4)*4 32-bit words]; box [128 words][rows_ld][1]
@@ -649,6 +685,11 @@ static int launch_nconv_tc(const nconv_b200_nconv_tc_desc* d, cudaStream_t st) {
 }  // namespace nconv
 
 using namespace nconv;
+
+extern "C" int nconv_b200_debug_buffer(void* pinned_host_64_bytes) {
+  unsigned int* p = (unsigned int*)pinned_host_64_bytes;
+  return (int)cudaMemcpyToSymbol(g_nt_dbg, &p, sizeof(p));
+}
 
 extern "C" size_t nconv_b200_n8_bytes(int B, int H, int W) {
   if (B <= 0 || H <= 0 || W <= 0) return 0;

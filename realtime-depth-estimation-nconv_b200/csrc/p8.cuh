@@ -73,6 +73,24 @@ __device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
   lo = *reinterpret_cast<uint4*>(l);
 }
 
+// Same result as split8 with packed conversions (cvt.rn.bf16x2.f32: two values per instruction; the bf16 -> fp32
+// back-conversion is a shift / mask): ~3 instructions per value instead of ~5.
+__device__ __forceinline__ void split8_fast(const float* v, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 hp = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    const uint32_t hb = *reinterpret_cast<const uint32_t*>(&hp);
+    const float r0 = v[2 * i] - __uint_as_float(hb << 16);
+    const float r1 = v[2 * i + 1] - __uint_as_float(hb & 0xffff0000u);
+    const __nv_bfloat162 lp = __floats2bfloat162_rn(r0, r1);
+    h[i] = hb;
+    l[i] = *reinterpret_cast<const uint32_t*>(&lp);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
 __device__ __forceinline__ void join8(const uint4& hi, const uint4& lo, float* v) {
   const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&hi);
   const __nv_bfloat16* l = reinterpret_cast<const __nv_bfloat16*>(&lo);

@@ -89,6 +89,7 @@ SIGNATURES = {
     "nconv_b200_dnet_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nconv_b200_dnet_forward": (c_int, [c_void_p, POINTER(c_void_p), c_void_p, c_int, c_int, c_int,
                                         c_void_p, c_size_t, c_void_p]),
+    "nconv_b200_debug_buffer": (c_int, [c_void_p]),
     "nconv_b200_n8_bytes": (c_size_t, [c_int] * 3),
     "nconv_b200_n8_zero_ring": (c_int, [c_void_p] + [c_int] * 3 + [c_void_p]),
     "nconv_b200_n8_pack": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),
