@@ -185,10 +185,10 @@ namespace nconv {
 // ---------------------------------------------------------------------------------------------------------------
 // tcgen05 NConv2d
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int NT_ESETS = 2;                 // epilogue sets of 4 warps; set e drains the M-tiles with (running index) % NT_ESETS == e
+constexpr int NT_ESETS = 3;                 // epilogue sets of 4 warps; set e drains the M-tiles with (running index) % NT_ESETS == e
 constexpr int NT_ISSUERS = 2;               // MMA issuer warps (1, 2): issuer i takes the M-tiles with (running index) % NT_ISSUERS == i
 constexpr int NT_THREADS = 128 + 128 * NT_ESETS;  // warp 0: producer, warps 1-2: MMA issuers, warp 3: idle, then the epilogue warps (TMEM lane quarter = warp % 4)
-constexpr int NT_PX_BYTES = NT_ESETS * 2 * 4 * 16 * 32 * 4;   // pool exchange: [set][parity][staged row in M-tile][y0..7 | c0..7][lane] floats
+constexpr int NT_PX_BYTES = NT_ESETS * 2 * 4 * 8 * 32 * 4;    // pool exchange: [set][parity][staged row in M-tile][4 y | 4 c][lane] floats
 constexpr int NT_P = 32;                    // staged row pitch in pixels: one staged row per epilogue warp
 constexpr int NT_ROW_BYTES = NT_P * 16;     // one staged row of one plane
 constexpr int NT_SMEM_MAX = 227 * 1024 - 4 * 1024;    // dynamic part (static: barriers and per-channel constants)
@@ -212,6 +212,7 @@ struct NtArgs {
   int B, H, W, CI;
   int TM, rows_ld, tiles_x, tiles_y, ntiles;
   int issuers, esets;          // active MMA issuer warps (<= NT_ISSUERS) / epilogue sets (<= NT_ESETS)
+  int dbg;                     // NCONV_B200_NT_DEBUG bits (timing experiments only): 1 no global stores, 2 no pool, 4 no MMAs, 8 no shift-sum
   float eps;
 };
 
@@ -369,6 +370,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
         if ((int)(it % (uint32_t)a.issuers) == issuer) {
           nt_wait(smem_u32(&t_empty[slot]), sphase ^ 1, 4, it);
           tc_fence_after();
+          if (!(a.dbg & 4))
 #pragma unroll
           for (int s = 0; s < 2; ++s) {
             const uint32_t d = tmem_base + slot * C::SLOT_COLS + s * C::NROW;
@@ -449,6 +451,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
         float N[8], D[8];
 #pragma unroll
         for (int co = 0; co < 8; ++co) { N[co] = __uint_as_float(vN[co]); D[co] = __uint_as_float(vD[co]); }
+        if (!(a.dbg & 8))
 #pragma unroll
         for (int dx = 1; dx < K; ++dx)
 #pragma unroll
@@ -457,7 +460,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
             D[co] += __shfl_down_sync(0xffffffffu, __uint_as_float(vD[dx * 8 + co]), dx);
           }
         const int oy = y0 + 4 * t + q, ox = x0 + lane;
-        const bool valid = lane < C::WT && oy < a.H && ox < a.W;
+        const bool valid = lane < C::WT && oy < a.H && ox < a.W && !(a.dbg & 1);
         float yv[8], cv[8];
 #pragma unroll
         for (int co = 0; co < 8; ++co) {
@@ -494,31 +497,40 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
             }
           }
         }
-        if (a.out_pool) {
-          // the two independent 2x2/2 max-pools (step1.py:62-74), ATen's window order and `(v > m) || isnan(v)` update.
-          // The lower row of a window belongs to the next epilogue warp: exchanged through shared memory.
-          float(*px)[16][32] = reinterpret_cast<float(*)[16][32]>(s_px + (size_t)(set * 2 + ((it / (uint32_t)a.esets) & 1)) * 4 * 16 * 32);
+        if (a.out_pool && !(a.dbg & 2)) {
+          // The two independent 2x2/2 max-pools (step1.py:62-74): max over the window, NaN if any element is NaN — the
+          // value ATen's `(v > m) || isnan(v)` chain leaves.  The two rows of a window belong to the warps of quarters
+          // 2j and 2j+1: the even warp pools channels 0-3 and the odd warp channels 4-7, each handing the other its half
+          // of the channels through shared memory (8 floats per lane, one 64-thread barrier per M-tile), and each writes
+          // its 8-byte half of the pooled pixel's four N8 vectors.
+          const int half = q & 1;                                   // channels [4*half, 4*half + 4) are pooled here
+          float(*px)[8][32] = reinterpret_cast<float(*)[8][32]>(s_px + (size_t)(set * 2 + ((it / (uint32_t)a.esets) & 1)) * 4 * 8 * 32);
 #pragma unroll
-          for (int co = 0; co < 8; ++co) { px[q][co][lane] = yv[co]; px[q][8 + co][lane] = cv[co]; }
-          asm volatile("bar.sync %0, 128;" ::"r"(1 + set) : "memory");
-          if ((q & 1) == 0) {
-            float yp[8], cp[8];
+          for (int j = 0; j < 4; ++j) { px[q][j][lane] = half ? yv[j] : yv[4 + j]; px[q][4 + j][lane] = half ? cv[j] : cv[4 + j]; }
+          asm volatile("bar.sync %0, 64;" ::"r"(1 + set * 2 + (q >> 1)) : "memory");
+          float yp[4], cp[4];
 #pragma unroll
-            for (int co = 0; co < 8; ++co) {
-              const float y01 = __shfl_down_sync(0xffffffffu, yv[co], 1), c01 = __shfl_down_sync(0xffffffffu, cv[co], 1);
-              const float y10 = px[q + 1][co][lane], c10 = px[q + 1][8 + co][lane];
-              const float y11 = __shfl_down_sync(0xffffffffu, y10, 1), c11 = __shfl_down_sync(0xffffffffu, c10, 1);
-              // max over the window, NaN if any element is NaN: the value ATen's `(v > m) || isnan(v)` chain leaves
-              yp[co] = max_nan(max_nan(yv[co], y01), max_nan(y10, y11));
-              cp[co] = max_nan(max_nan(cv[co], c01), max_nan(c10, c11));
-            }
-            const int py = oy >> 1, pxo = ox >> 1;
-            if (valid && (lane & 1) == 0 && py < gp.H && pxo < gp.W) {
-              float xcp[8];
+          for (int j = 0; j < 4; ++j) {
+            const float ya = half ? yv[4 + j] : yv[j], ca = half ? cv[4 + j] : cv[j];   // this warp's row
+            const float yb = px[q ^ 1][j][lane], cb = px[q ^ 1][4 + j][lane];  // the partner's row
+            const float ym = max_nan(ya, yb), cm = max_nan(ca, cb);            // vertical, then horizontal with lane + 1
+            yp[j] = max_nan(ym, __shfl_down_sync(0xffffffffu, ym, 1));
+            cp[j] = max_nan(cm, __shfl_down_sync(0xffffffffu, cm, 1));
+          }
+          const int py = oy >> 1, pxo = ox >> 1;
+          if (valid && (lane & 1) == 0 && py < gp.H && pxo < gp.W) {
+            float xcp[4];
 #pragma unroll
-              for (int co = 0; co < 8; ++co) xcp[co] = yp[co] * cp[co];
-              n8_put(a.out_pool, gp, n, gp.pixel(py, pxo), n8_make(xcp, cp));
-            }
+            for (int j = 0; j < 4; ++j) xcp[j] = yp[j] * cp[j];
+            uint2 xh, xl, ch, cl;
+            split4_fast(xcp, xh, xl);
+            split4_fast(cp, ch, cl);
+            __nv_bfloat16* b0 = a.out_pool + gp.plane(n, 0, 0) + gp.pixel(py, pxo) + 4 * half;
+            const size_t pe = gp.plane_elems();
+            *reinterpret_cast<uint2*>(b0) = xh;
+            *reinterpret_cast<uint2*>(b0 + pe) = xl;
+            *reinterpret_cast<uint2*>(b0 + 2 * pe) = ch;
+            *reinterpret_cast<uint2*>(b0 + 3 * pe) = cl;
           }
         }
       }
@@ -655,6 +667,8 @@ static int launch_nconv_tc(const nconv_b200_nconv_tc_desc* d, cudaStream_t st) {
     static const char* es = getenv("NCONV_B200_NT_ESETS");
     a.issuers = ei && atoi(ei) == 1 ? 1 : NT_ISSUERS;
     a.esets = es && atoi(es) == 1 ? 1 : NT_ESETS;
+    static const char* db = getenv("NCONV_B200_NT_DEBUG");
+    a.dbg = db ? atoi(db) : 0;
   }
   size_t smem = W_BYTES + NT_PX_BYTES + 2 * (size_t)NSRC * 4 * a.rows_ld * NT_ROW_BYTES;
   if (smem < (size_t)NT_SMEM_MIN) smem = NT_SMEM_MIN;

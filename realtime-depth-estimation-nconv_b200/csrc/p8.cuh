@@ -91,6 +91,20 @@ __device__ __forceinline__ void split8_fast(const float* v, uint4& hi, uint4& lo
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
+__device__ __forceinline__ void split4_fast(const float* v, uint2& hi, uint2& lo) {
+  uint32_t h[2], l[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const __nv_bfloat162 hp = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    const uint32_t hb = *reinterpret_cast<const uint32_t*>(&hp);
+    const __nv_bfloat162 lp = __floats2bfloat162_rn(v[2 * i] - __uint_as_float(hb << 16), v[2 * i + 1] - __uint_as_float(hb & 0xffff0000u));
+    h[i] = hb;
+    l[i] = *reinterpret_cast<const uint32_t*>(&lp);
+  }
+  hi = make_uint2(h[0], h[1]);
+  lo = make_uint2(l[0], l[1]);
+}
+
 __device__ __forceinline__ void join8(const uint4& hi, const uint4& lo, float* v) {
   const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&hi);
   const __nv_bfloat16* l = reinterpret_cast<const __nv_bfloat16*>(&lo);
