@@ -130,7 +130,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   __shared__ uint32_t s_tmem_base;
   __shared__ float s_scale[N], s_shift[N];
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // shuffle: provably warp-uniform warp index, so the MMA issuer's code compiles to the uniform datapath
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t a_plane_bytes = (uint32_t)a.rows_alloc * a.P * 16;       // one (group, part, j) plane
   const uint32_t a_stage_bytes = (uint32_t)a.G * 4 * a_plane_bytes;
   constexpr uint32_t B_TAP_BYTES = 2 * 2 * N * 16;                        // [j][part][N][16 B]
@@ -224,51 +225,49 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
     // ===================== MMA issuer =====================
     constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
     constexpr uint32_t IDESC2 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((2 * N) >> 3) << 17) | ((128u >> 4) << 24);
+    // Warp-convergent issue: every lane runs the loop on warp-uniform values and one lane is elected inside
+    // umma_bf16_ws, so descriptors stay in uniform registers and UTCHMMAs issue back to back.  (Under `if (lane == 0)`
+    // every MMA cost an R2UR + ELECT + branch sequence, ~100 cycles of the issuing warp: more than an N <= 64 MMA.)
     uint32_t stage = 0, phase = 0, it = 0;
+    constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);       // SBO = 128 B, descriptor version 1
+    constexpr uint32_t B_LBO = (uint32_t)(2 * N * 16 >> 4) << 16, BLO_OFF = (N * 16) >> 4;   // [j][hi|lo][N][16 B]
+    const uint32_t a_lbo = (a_plane_bytes >> 4) << 16, alo_off = (2 * a_plane_bytes) >> 4;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
-      mbar_wait(smem_u32(&s_tempty[buf]), tphase ^ 1);
+      mbar_wait_warp(smem_u32(&s_tempty[buf]), tphase ^ 1);
       tc_fence_after();
       for (int k = 0; k < nk; ++k) {
-        mbar_wait(smem_u32(&s_full[stage]), phase);
+        mbar_wait_warp(smem_u32(&s_full[stage]), phase);
         tc_fence_after();
-        if (lane == 0) {
-          // Descriptor words are built from kernel parameters and compile-time tap tables only, so
-          // they stay in uniform registers (UTCHMMA takes its descriptors from the uniform file).
-          constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);       // SBO = 128 B, descriptor version 1
-          const uint32_t sa16 = (smem_base + stage * stage_bytes) >> 4;
-          const uint32_t sb16 = sa16 + (a_stage_bytes >> 4);
-          const uint32_t a_lbo = (a_plane_bytes >> 4) << 16, alo_off = (2 * a_plane_bytes) >> 4;
-          constexpr uint32_t B_LBO = (uint32_t)(2 * N * 16 >> 4) << 16, BLO_OFF = (N * 16) >> 4;   // [j][hi|lo][N][16 B]
-          for (int t = 0; t < a.T; ++t) {
-            const uint32_t dbase = tmem_base + buf * 256 + t * NACC;
-            const uint32_t at16 = sa16 + (uint32_t)t * 128;
+        const uint32_t sa16 = (smem_base + stage * stage_bytes) >> 4;
+        const uint32_t sb16 = sa16 + (a_stage_bytes >> 4);
+        for (int t = 0; t < a.T; ++t) {
+          const uint32_t dbase = tmem_base + buf * 256 + t * NACC;
+          const uint32_t at16 = sa16 + (uint32_t)t * 128;
 #pragma unroll
-            for (int i = 0; i < TapTable<MODE>::NTAPS; ++i) {
-              if (i >= a.ntaps) break;                                   // S2 without the 1x1 branch
-              const uint32_t ao = TapTable<MODE>::a_off16(i, a.P, a_plane_bytes >> 4);
-              const uint32_t d = dbase + TapTable<MODE>::dgrp(i) * a.T * NACC;
-              const uint64_t a_hi = ((uint64_t)DESC_HI << 32) | ((at16 + ao) | a_lbo);
-              const uint64_t a_lo = ((uint64_t)DESC_HI << 32) | ((at16 + ao + alo_off) | a_lbo);
-              const uint32_t bo = sb16 + TapTable<MODE>::w_idx(i) * (B_TAP_BYTES >> 4);
-              const uint64_t b_hi = ((uint64_t)DESC_HI << 32) | (bo | B_LBO);
-              const uint64_t b_lo = ((uint64_t)DESC_HI << 32) | ((bo + BLO_OFF) | B_LBO);
-              const uint32_t acc = (k > 0 || !TapTable<MODE>::first(i)) ? 1u : 0u;
-              if (a.dbg & 2) continue;
-              if (STACK) {
-                umma_bf16(d, a_hi, b_hi, IDESC2, acc);          // [hi*hi | hi*lo] : b_hi's 2N rows = [W_hi ; W_lo]
-                umma_bf16(d, a_lo, b_hi, IDESC, 1u);            // + lo*hi into the first half
-              } else {
-                umma_bf16(d, a_hi, b_hi, IDESC, acc);
-                umma_bf16(d, a_lo, b_hi, IDESC, 1u);
-                umma_bf16(d, a_hi, b_lo, IDESC, 1u);
-              }
+          for (int i = 0; i < TapTable<MODE>::NTAPS; ++i) {
+            if (i >= a.ntaps) break;                                   // S2 without the 1x1 branch
+            const uint32_t ao = TapTable<MODE>::a_off16(i, a.P, a_plane_bytes >> 4);
+            const uint32_t d = dbase + TapTable<MODE>::dgrp(i) * a.T * NACC;
+            const uint64_t a_hi = ((uint64_t)DESC_HI << 32) | ((at16 + ao) | a_lbo);
+            const uint64_t a_lo = ((uint64_t)DESC_HI << 32) | ((at16 + ao + alo_off) | a_lbo);
+            const uint32_t bo = sb16 + TapTable<MODE>::w_idx(i) * (B_TAP_BYTES >> 4);
+            const uint64_t b_hi = ((uint64_t)DESC_HI << 32) | (bo | B_LBO);
+            const uint64_t b_lo = ((uint64_t)DESC_HI << 32) | ((bo + BLO_OFF) | B_LBO);
+            const uint32_t acc = (k > 0 || !TapTable<MODE>::first(i)) ? 1u : 0u;
+            if (a.dbg & 2) continue;
+            if (STACK) {
+              umma_bf16_ws(d, a_hi, b_hi, IDESC2, acc);          // [hi*hi | hi*lo] : b_hi's 2N rows = [W_hi ; W_lo]
+              umma_bf16_ws(d, a_lo, b_hi, IDESC, 1u);            // + lo*hi into the first half
+            } else {
+              umma_bf16_ws(d, a_hi, b_hi, IDESC, acc);
+              umma_bf16_ws(d, a_lo, b_hi, IDESC, 1u);
+              umma_bf16_ws(d, a_hi, b_lo, IDESC, 1u);
             }
           }
-          umma_commit(smem_u32(&s_empty[stage]));                       // frees the smem slot when the MMAs retire
-          if (k == nk - 1) umma_commit(smem_u32(&s_tfull[buf]));       // accumulators of this tile complete
         }
-        __syncwarp();
+        umma_commit_ws(smem_u32(&s_empty[stage]));                       // frees the smem slot when the MMAs retire
+        if (k == nk - 1) umma_commit_ws(smem_u32(&s_tfull[buf]));       // accumulators of this tile complete
         if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
       }
     }

@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
   __shared__ uint32_t s_tmem_base;
   __shared__ float s_scale[TCX_CO], s_shift[TCX_CO];
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
   const int nk = a.pairs[0] + a.pairs[1];
   const uint32_t plane_bytes = (uint32_t)a.rows_alloc * a.P * 16;    // one (part, j) plane of a stage
   const uint32_t stage_bytes = 4 * plane_bytes;
@@ -146,22 +146,23 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
     constexpr uint32_t DESC_HI = (128u >> 4) | (1u << 14);          // SBO = 128 B, descriptor version 1
     constexpr uint32_t W_LBO = (uint32_t)(TCX_WHALF_BYTES >> 4) << 16;   // lo tile: K-halves 2 KB apart
     // hi tiles: LBO = 0, both K-halves read the SAME 2 KB [W_hi ; W_hi] (against [x_hi ; x_lo])
-    mbar_wait(smem_u32(&s_wfull), 0);
+    // warp-convergent issue (see tc_conv.cu): uniform waits, one lane elected inside umma_bf16_ws
+    mbar_wait_warp(smem_u32(&s_wfull), 0);
     tc_fence_after();
     uint32_t stage = 0, phase = 0, it = 0;
     const uint32_t x_lbo_hl = ((2 * plane_bytes) >> 4) << 16;       // hi plane -> lo plane of the same chunk
     const uint32_t x_lbo_jj = (plane_bytes >> 4) << 16;             // chunk j0 -> j1 (both hi)
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
-      mbar_wait(smem_u32(&s_tempty[buf]), tphase ^ 1);
+      mbar_wait_warp(smem_u32(&s_tempty[buf]), tphase ^ 1);
       tc_fence_after();
       const uint32_t d = tmem_base + buf * TCX_N;
       for (int k = 0; k < nk; ++k) {
-        mbar_wait(smem_u32(&s_full[stage]), phase);
+        mbar_wait_warp(smem_u32(&s_full[stage]), phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t x16 = (ring + stage * stage_bytes) >> 4;
-          const uint32_t w16 = (smem_base + (uint32_t)k * TCX_WSTAGE_BYTES) >> 4;
+        const uint32_t x16 = (ring + stage * stage_bytes) >> 4;
+        const uint32_t w16 = (smem_base + (uint32_t)k * TCX_WSTAGE_BYTES) >> 4;
+        if (!(a.dbg & 2)) {
 #pragma unroll
           for (int dy = 0; dy < 3; ++dy) {
             const uint32_t xs = x16 + (uint32_t)(dy * a.P);
@@ -172,15 +173,13 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
             const uint64_t w_h0 = ((uint64_t)DESC_HI << 32) | ws;
             const uint64_t w_h1 = ((uint64_t)DESC_HI << 32) | (ws + (TCX_WHALF_BYTES >> 4));
             const uint64_t w_lo = ((uint64_t)DESC_HI << 32) | ((ws + 2 * (TCX_WHALF_BYTES >> 4)) | W_LBO);
-            if (a.dbg & 2) continue;
-            umma_bf16(d, w_h0, x_h0, IDESC, (k > 0 || dy > 0) ? 1u : 0u);
-            umma_bf16(d, w_h1, x_h1, IDESC, 1u);
-            umma_bf16(d, w_lo, x_16, IDESC, 1u);
+            umma_bf16_ws(d, w_h0, x_h0, IDESC, (k > 0 || dy > 0) ? 1u : 0u);
+            umma_bf16_ws(d, w_h1, x_h1, IDESC, 1u);
+            umma_bf16_ws(d, w_lo, x_16, IDESC, 1u);
           }
-          umma_commit(smem_u32(&s_empty[stage]));
-          if (k == nk - 1) umma_commit(smem_u32(&s_tfull[buf]));
         }
-        __syncwarp();
+        umma_commit_ws(smem_u32(&s_empty[stage]));
+        if (k == nk - 1) umma_commit_ws(smem_u32(&s_tfull[buf]));
         if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
       }
     }

@@ -33,6 +33,16 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (++spins > (1u << 22)) __trap();
   }
 }
+// Warp-uniform wait: the loop exit is a warp vote, so every lane leaves in the same iteration.  REQUIRED in front of
+// warp-convergent tcgen05 issue code (umma_bf16_ws / umma_commit_ws): with the per-lane exit of mbar_wait the compiler
+// emits no reconvergence point, lanes that see the phase flip first run ahead as their own group, and the uniform-datapath
+// MMAs and commits execute once per group (duplicate barrier arrivals -> deadlock in long runs).
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+    if (++spins > (1u << 22)) __trap();
+  }
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
