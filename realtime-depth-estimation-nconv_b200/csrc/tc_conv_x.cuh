@@ -23,17 +23,21 @@
 //   [W_hi ; W_hi] tiles alias their two K-halves with LBO = 0); only pixel stages stream through the ring,
 //   one TMA tensor copy per staged plane.
 //
-// Warp roles: warp 0 producer (weights once, then 4 tensor copies per K-stage), warp 1 MMA issuer, warps 6-7
-// idle (they keep the epilogue warps' ids aligned with the TMEM lane quarters), warps 2-5 epilogue set 0 and,
-// with ESETS = 2 (layers whose resident weights leave room for a second staging ring), warps 8-11 epilogue
-// set 1: set h handles accumulator columns [128h, 128h+128).  A warp may only read the TMEM lane quarter
-// (warp id % 4).  TMEM: two 256-column accumulators (tile i's epilogue overlaps tile i+1's MMAs).
+// Warp roles (13 warps): warp 0 producer (weights once, then 4 tensor copies per K-stage), warp 1 MMA issuer, three
+// STAGER warps (2, 4, 5: TMEM lane quarters 2, 0, 1 = the three tap groups; a warp may only read quarter warp % 4) and
+// eight EMITTER warps (3, 6..12) in two groups of four.  Stagers drain the accumulator window by window (32 columns)
+// into a 128-row shared-memory ring (one plane per tap group, row = column - tap shift); emitters sum the three planes,
+// apply scale/shift/ReLU, split to hi/lo and store P8 (warp -> 8-channel chunk, lane -> pixel), the two groups taking
+// alternate windows.  Stagers and emitters are decoupled by per-window mbarriers (full: 3 stager arrivals, empty: 4
+// emitter arrivals), three windows may be in flight; round 1's version ran both halves in the same four warps with four
+// 128-thread barriers per two windows and was latency-bound (5 200 cycles of epilogue per tile against 3 000 of MMAs).
+// TMEM: two 256-column accumulators (tile i's epilogue overlaps tile i+1's MMAs).
 #pragma once
 #include <cuda.h>
 
 namespace nconv {
 
-constexpr int TCX_THREADS = 256;                 // + 128 with a second epilogue set
+constexpr int TCX_THREADS = 416;                 // 13 warps
 constexpr int TCX_N = 256;                 // pixels per MMA / TMEM accumulator columns
 constexpr int TCX_OUT = TCX_N - 2;         // output pixels per tile (column shifts 0..2)
 constexpr int TCX_WHALF_BYTES = 128 * 16;              // one K-half of an A tile: [128 rows][8] bf16
@@ -41,7 +45,8 @@ constexpr int TCX_WROW_BYTES = 4 * TCX_WHALF_BYTES;    // per kernel row: hi j0 
 constexpr int TCX_WSTAGE_BYTES = 3 * TCX_WROW_BYTES;   // per K-stage (16 input channels): 24 KB
 constexpr int TCX_MAX_STAGES = 8;
 constexpr int TCX_S_PITCH = 36;                        // floats per staged-output row (32 co + pad: conflict-free 128-bit reads)
-constexpr int TCX_S_PLANE = 64 * TCX_S_PITCH;          // floats per tap-group plane (64-row ring)
+constexpr int TCX_S_ROWS = 128;                        // ring rows = 4 windows
+constexpr int TCX_S_PLANE = TCX_S_ROWS * TCX_S_PITCH;  // floats per tap-group plane
 constexpr int TCX_S_BYTES = (3 * TCX_S_PLANE * 4 + 127) / 128 * 128;   // the ring behind it must stay 128 B aligned
 constexpr int TCX_CO = 32;
 
@@ -60,11 +65,11 @@ struct TcxArgs {
   int dbg;                      // NCONV_B200_TC_DEBUG bits (timing experiments only): 1 no epilogue work, 2 no MMAs, 4 no loads
 };
 
-template <int ESETS>
-__global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_kernel(const __grid_constant__ TcxArgs a, const __grid_constant__ CUtensorMap tm0,
-                                                                                     const __grid_constant__ CUtensorMap tm1) {
+__global__ void __launch_bounds__(TCX_THREADS, 1) conv_tcx_kernel(const __grid_constant__ TcxArgs a, const __grid_constant__ CUtensorMap tm0,
+                                                                 const __grid_constant__ CUtensorMap tm1) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t s_full[TCX_MAX_STAGES], s_empty[TCX_MAX_STAGES], s_tfull[2], s_tempty[2], s_wfull;
+  __shared__ __align__(8) uint64_t s_sfull[4], s_sempty[4];          // staging ring: window slot staged / emitted
   __shared__ uint32_t s_tmem_base;
   __shared__ float s_scale[TCX_CO], s_shift[TCX_CO];
 
@@ -75,7 +80,7 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
   const uint32_t w_bytes = (uint32_t)nk * TCX_WSTAGE_BYTES;
   const uint32_t smem_base = smem_u32(smem);
   const uint32_t s_out = smem_base + w_bytes;                        // epilogue staging (3 planes)
-  const uint32_t ring = s_out + ESETS * TCX_S_BYTES;
+  const uint32_t ring = s_out + TCX_S_BYTES;
 
   if (threadIdx.x < TCX_CO) {
     s_scale[threadIdx.x] = a.scale ? __ldg(a.scale + threadIdx.x) : 1.f;
@@ -83,7 +88,8 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
   }
   if (threadIdx.x == 0) {
     for (int s = 0; s < TCX_MAX_STAGES; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 4 * ESETS); }
+    for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 3); }
+    for (int b = 0; b < 4; ++b) { mbar_init(smem_u32(&s_sfull[b]), 3); mbar_init(smem_u32(&s_sempty[b]), 4); }
     mbar_init(smem_u32(&s_wfull), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -96,9 +102,9 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
 
-  if (warp == 0 || warp == 6 || warp == 7) {
-    // ===================== producers =====================
-    const int pw = (warp == 0) ? 0 : warp - 5;          // 0, 1, 2
+  if (warp == 0) {
+    // ===================== producer =====================
+    const int pw = 0;
     if (pw == 0 && lane == 0) {
       // the layer's packed weights, once per CTA
       const uint32_t wf = smem_u32(&s_wfull);
@@ -183,116 +189,110 @@ __global__ void __launch_bounds__(TCX_THREADS + 128 * (ESETS - 1), 1) conv_tcx_k
         if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
       }
     }
+  } else if (warp == 2 || warp == 4 || warp == 5) {
+    // ===================== stagers: TMEM -> shared-memory ring =====================
+    // TMEM lane 32g + co holds tap-group g of output channel co: the warp of lane quarter g copies its 32x32 block of
+    // every 32-column window into plane g of the ring at row (column - g) (conflict-free 128-byte stores per column).
+    const int q = warp & 3;                                          // TMEM lane quarter = tap group (0, 1, 2)
+    float* S_st = reinterpret_cast<float*>(smem + w_bytes) + q * TCX_S_PLANE + lane;
+    uint32_t it = 0, gw = 0;                                         // tile counter, running window counter
+    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
+      const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
+      const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * TCX_N;
+      mbar_wait(smem_u32(&s_tfull[buf]), tphase);
+      tc_fence_after();
+      uint32_t va[32], vb[32];
+      auto stage_window = [&](const uint32_t* v) {
+        // window gw overwrites the ring rows of window gw - 4, which the emitters of windows gw - 4 and gw - 3 read
+        if (gw >= 4) mbar_wait(smem_u32(&s_sempty[(gw - 4) & 3]), ((gw - 4) >> 2) & 1);
+        if (gw >= 3) mbar_wait(smem_u32(&s_sempty[(gw - 3) & 3]), ((gw - 3) >> 2) & 1);
+        if (!(a.dbg & 8)) {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) S_st[((32 * gw + e - q) & (TCX_S_ROWS - 1)) * TCX_S_PITCH] = __uint_as_float(v[e]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&s_sfull[gw & 3]));
+        ++gw;
+      };
+      if (a.dbg & 1) { gw += TCX_N / 32; }
+      else {
+        tmem_ld32(tcol, va);
+#pragma unroll 1
+        for (int w = 0; w < TCX_N / 32; w += 2) {
+          tmem_ld_wait();
+          tmem_ld32(tcol + (w + 1) * 32, vb);
+          stage_window(va);
+          tmem_ld_wait();
+          if (w + 2 < TCX_N / 32) tmem_ld32(tcol + (w + 2) * 32, va);
+          stage_window(vb);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&s_tempty[buf]));          // the accumulator is drained: tile i+2's MMAs may start
+    }
   } else {
-    // ===================== epilogue (warps 2..5, and 8..11 with ESETS = 2) =====================
-    // TMEM lane 32g + co holds tap-group g of output channel co, so the warp of lane quarter g (< 3) is the
-    // "stager" of group g: per 32-column window it copies its 32x32 block into plane g of a 64-row ring in
-    // shared memory at row (column - g), one conflict-free 128-byte store per column.  After a 128-thread
-    // named barrier all three groups of an output pixel are in place and the four warps of the set emit the
-    // window: thread -> (pixel, 8 channels), summing the three planes, scale/shift/ReLU, hi/lo split,
-    // 16-byte stores.  The TMEM load of the next window is in flight meanwhile.
-    const int q = warp & 3;                                          // TMEM lane quarter = tap group (3: helper, emits only)
-    const int set = (ESETS == 2 && warp >= 8) ? 1 : 0;
-    const int bar_id = 1 + set;
-    constexpr int NWIN = TCX_N / 32 / ESETS;                         // windows per set
-    const int w0 = set * NWIN;
-    float* S = reinterpret_cast<float*>(smem + w_bytes) + set * (TCX_S_BYTES / 4);
-    float* S_st = S + q * TCX_S_PLANE + lane;                        // + row * TCX_S_PITCH   (stagers)
-    const int ep = lane, ech = q;                                    // emit: warp -> 8-channel chunk, lane -> pixel (512 B contiguous stores)
-    const float* S_ld = S + 8 * ech;
+    // ===================== emitters: ring -> P8 =====================
+    // warps 3, 6, 7, 8 (group 0) and 9, 10, 11, 12 (group 1); group g emits the windows with (running index) % 2 == g;
+    // within a group warp -> 8-channel chunk, lane -> pixel (512-byte contiguous stores per plane).
+    const int ei = (warp == 3) ? 0 : warp - 5;                       // 0..7
+    const int grp = ei >> 2, ech = ei & 3, ep = lane;
+    const float* S_ld = reinterpret_cast<const float*>(smem + w_bytes) + 8 * ech;
     const size_t oplane = (size_t)(a.AH + 2) * (a.AW + 2) * 8;
     const P8QGeom qg = P8QGeom::make(a.B, TCX_CO, a.AH, a.AW);
     float sc[8], sh[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) { sc[e] = s_scale[8 * ech + e]; sh[e] = s_shift[8 * ech + e]; }
-    const int m_first = 32 * w0 - 2 + ep;                            // first output position of this thread
-    uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
-      const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
+    uint32_t gw = 0;
+    for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
       const int tx = tile % a.tiles_x, ty = (tile / a.tiles_x) % a.tiles_y, n = tile / (a.tiles_x * a.tiles_y);
-      const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * TCX_N;
       __nv_bfloat16* obase = a.out + ((size_t)n * (TCX_CO / 8) + ech) * 2 * oplane;
       __nv_bfloat16* qbase = a.outq ? a.outq + qg.slab(n, ech, 0) : nullptr;
-      // (row, column) of the output position, advanced by 32 per window without divisions
-      int rr = m_first >= 0 ? m_first / a.P : 0;
-      int cc = m_first - rr * a.P;
-      mbar_wait(smem_u32(&s_tfull[buf]), tphase);
-      tc_fence_after();
-      if (a.dbg & 1) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(smem_u32(&s_tempty[buf])); continue; }
-
-      auto stage_window = [&](const uint32_t* v, int w) {
-        if (a.dbg & 8) return;
+      // (row, column) of this thread's output position in the tile, advanced by 32 per window without divisions
+      int rr = ep >= 2 ? (ep - 2) / a.P : 0;                         // window 0: m = -2 + ep
+      int cc = ep - 2 - rr * a.P;
+      if (a.dbg & 1) { gw += TCX_N / 32; continue; }
+#pragma unroll 1
+      for (int w = 0; w < TCX_N / 32; ++w, ++gw) {
+        if ((int)(gw & 1) == grp) {
+          mbar_wait(smem_u32(&s_sfull[gw & 3]), (gw >> 2) & 1);
+          const int m = 32 * w - 2 + ep;
+          const int ay = ty * a.R + rr, ax = tx * a.Wt + cc;
+          if (m >= 0 && rr < a.R && cc < a.Wt && ay < a.AH && ax < a.AW && !(a.dbg & 16)) {
+            const float* sp = S_ld + ((32 * gw - 2 + ep) & (TCX_S_ROWS - 1)) * TCX_S_PITCH;
+            float f[8];
 #pragma unroll
-        for (int e = 0; e < 32; ++e) S_st[((32 * w + e - q) & 63) * TCX_S_PITCH] = __uint_as_float(v[e]);
-      };
-      auto emit_window = [&](int w) {
-        const int m = 32 * w - 2 + ep;
-        const int ay = ty * a.R + rr, ax = tx * a.Wt + cc;
-        if (m >= 0 && rr < a.R && cc < a.Wt && ay < a.AH && ax < a.AW && !(a.dbg & 16)) {
-          const float* sp = S_ld + (m & 63) * TCX_S_PITCH;
-          float f[8];
+            for (int hv = 0; hv < 2; ++hv) {
+              const float4 v0 = *reinterpret_cast<const float4*>(sp + 4 * hv);
+              const float4 v1 = *reinterpret_cast<const float4*>(sp + 4 * hv + TCX_S_PLANE);
+              const float4 v2 = *reinterpret_cast<const float4*>(sp + 4 * hv + 2 * TCX_S_PLANE);
+              f[4 * hv + 0] = v0.x + v1.x + v2.x; f[4 * hv + 1] = v0.y + v1.y + v2.y;
+              f[4 * hv + 2] = v0.z + v1.z + v2.z; f[4 * hv + 3] = v0.w + v1.w + v2.w;
+            }
 #pragma unroll
-          for (int hv = 0; hv < 2; ++hv) {
-            const float4 v0 = *reinterpret_cast<const float4*>(sp + 4 * hv);
-            const float4 v1 = *reinterpret_cast<const float4*>(sp + 4 * hv + TCX_S_PLANE);
-            const float4 v2 = *reinterpret_cast<const float4*>(sp + 4 * hv + 2 * TCX_S_PLANE);
-            f[4 * hv + 0] = v0.x + v1.x + v2.x; f[4 * hv + 1] = v0.y + v1.y + v2.y;
-            f[4 * hv + 2] = v0.z + v1.z + v2.z; f[4 * hv + 3] = v0.w + v1.w + v2.w;
+            for (int e = 0; e < 8; ++e) {
+              f[e] = fmaf(f[e], sc[e], sh[e]);
+              if (a.relu) f[e] = fmaxf(f[e], 0.f);
+            }
+            uint4 hi, lo;
+            split8_fast(f, hi, lo);
+            __nv_bfloat16* p = obase + ((size_t)(ay + 1) * (a.AW + 2) + (ax + 1)) * 8;
+            if (!((a.dbg & 32) && hi.x != 0x12345678u)) {             // (timing experiment: no global stores)
+              *reinterpret_cast<uint4*>(p) = hi;
+              *reinterpret_cast<uint4*>(p + oplane) = lo;
+              if (qbase) {
+                __nv_bfloat16* pq = qbase + qg.pixel(ay, ax);
+                *reinterpret_cast<uint4*>(pq) = hi;
+                *reinterpret_cast<uint4*>(pq + qg.slab_elems()) = lo;
+              }
+            }
           }
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            f[e] = fmaf(f[e], sc[e], sh[e]);
-            if (a.relu) f[e] = fmaxf(f[e], 0.f);
-          }
-          uint4 hi, lo;
-          split8(f, hi, lo);
-          __nv_bfloat16* p = obase + ((size_t)(ay + 1) * (a.AW + 2) + (ax + 1)) * 8;
-          if ((a.dbg & 32) && hi.x != 0x12345678u) return;             // timing experiment: no global stores
-          *reinterpret_cast<uint4*>(p) = hi;
-          *reinterpret_cast<uint4*>(p + oplane) = lo;
-          if (qbase) {
-            __nv_bfloat16* pq = qbase + qg.pixel(ay, ax);
-            *reinterpret_cast<uint4*>(pq) = hi;
-            *reinterpret_cast<uint4*>(pq + qg.slab_elems()) = lo;
-          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&s_sempty[gw & 3]));
         }
         cc += 32;
         while (cc >= a.P) { cc -= a.P; ++rr; }
-      };
-      auto set_barrier = [&]() { asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory"); };
-
-      uint32_t va[32], vb[32];
-      const bool stager = q < 3;
-      if (ESETS == 2 && set == 1 && stager) {
-        // columns 126, 127 belong to set 0's range but feed this set's first two outputs
-        tmem_ld32(tcol + (uint32_t)((NWIN - 1) * 32), va);
-        tmem_ld_wait();
-#pragma unroll
-        for (int e = 30; e < 32; ++e) S_st[((32 * (NWIN - 1) + e - q) & 63) * TCX_S_PITCH] = __uint_as_float(va[e]);
       }
-      if (stager) tmem_ld32(tcol + w0 * 32, va);
-#pragma unroll 1
-      for (int w = w0; w < w0 + NWIN; w += 2) {
-        if (stager) {
-          tmem_ld_wait();
-          tmem_ld32(tcol + (w + 1) * 32, vb);
-          stage_window(va, w);
-        }
-        set_barrier();
-        emit_window(w);
-        set_barrier();
-        if (stager) {
-          tmem_ld_wait();
-          if (w + 2 < w0 + NWIN) tmem_ld32(tcol + (w + 2) * 32, va);
-          stage_window(vb, w + 1);
-        }
-        set_barrier();
-        emit_window(w + 1);
-        set_barrier();
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&s_tempty[buf]));
     }
   }
 
@@ -328,16 +328,12 @@ __global__ void tcx_pack_weights_kernel(const float* __restrict__ w, __nv_bfloat
   }
 }
 
-struct TcxPlan { int R, Wt, P, rows_alloc, rows_ld, tiles_x, tiles_y, stages, esets; size_t smem; bool ok; };
+struct TcxPlan { int R, Wt, P, rows_alloc, rows_ld, tiles_x, tiles_y, stages; size_t smem; bool ok; };
 
 static TcxPlan tcx_plan(int AH, int AW, int nk) {
   TcxPlan best = {}; best.ok = false;
   double best_cost = 1e300;
-  static const char* force = getenv("NCONV_B200_TCX_ESETS");          // A/B measurements only
-  // a second epilogue set needs a second staging ring: taken when the resident weights leave room for it
-  int esets = ((size_t)nk * TCX_WSTAGE_BYTES + 2 * TCX_S_BYTES + 2 * 26 * 1024 <= (size_t)TC_SMEM_MAX) ? 2 : 1;
-  if (force) esets = atoi(force) == 2 ? esets : 1;
-  const size_t fixed = (size_t)nk * TCX_WSTAGE_BYTES + (size_t)esets * TCX_S_BYTES;
+  const size_t fixed = (size_t)nk * TCX_WSTAGE_BYTES + (size_t)TCX_S_BYTES;
   for (int R = 1; R <= 32; ++R) {
     for (int P = 10; P <= 64; ++P) {                                   // 4P words <= 256 (tensor-map box limit)
       const int Wt = P - 2;
@@ -354,7 +350,7 @@ static TcxPlan tcx_plan(int AH, int AW, int nk) {
       const double cost = (double)tx * ty * (1.0 + 0.15 * (double)((R + 2) * P) / TCX_N);
       if (cost < best_cost) {
         best_cost = cost;
-        best = {R, Wt, P, rows_alloc, R + 2, tx, ty, stages, esets, fixed + (size_t)stages * stage, true};
+        best = {R, Wt, P, rows_alloc, R + 2, tx, ty, stages, fixed + (size_t)stages * stage, true};
       }
     }
   }
@@ -367,8 +363,7 @@ static int launch_tcx(const TcxArgs& a, const TcxPlan& p, cudaStream_t st) {
   int dev = 0, sms = 0;
   NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
   if (dev >= NCONV_MAX_DEVICES || !attr_done[dev]) {
-    NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(conv_tcx_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX));
-    NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(conv_tcx_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX));
+    NCONV_RETURN_IF_ERR(cudaFuncSetAttribute(conv_tcx_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_MAX));
     if (dev < NCONV_MAX_DEVICES) attr_done[dev] = true;
   }
   if (dev < NCONV_MAX_DEVICES) sms = sm_count[dev];
@@ -389,8 +384,7 @@ static int launch_tcx(const TcxArgs& a, const TcxPlan& p, cudaStream_t st) {
   snprintf(label, sizeof(label), "tc_conv3x3 %d->%d @%dx%d", CI, TCX_CO, a.AH, a.AW);
   {
     LaunchScope ls(st, label, 2.0 * CI * TCX_CO * 9.0 * opx, 4.0 * (CI * opx + TCX_CO * opx * (a.outq ? 2.0 : 1.0)));
-    if (p.esets == 2) conv_tcx_kernel<2><<<grid, TCX_THREADS + 128, p.smem, st>>>(a, tm[0], tm[1]);
-    else conv_tcx_kernel<1><<<grid, TCX_THREADS, p.smem, st>>>(a, tm[0], tm[1]);
+    conv_tcx_kernel<<<grid, TCX_THREADS, p.smem, st>>>(a, tm[0], tm[1]);
   }
   return (int)cudaGetLastError();
 }
