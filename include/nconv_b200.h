@@ -104,6 +104,14 @@ int nconv_b200_maxpool2x2_fwd(const float* x, float* y, int planes, int H, int W
 int nconv_b200_maxpool2x2_bwd(const float* gy, const float* x, float* gx, int planes, int H,
                               int W, void* stream);
 
+/* ---- opt-in confidence-argmax pooling (NOT what the reference does, see step1.py:62-74) ----
+ * co = maxpool2x2(c) / 4, xo = x gathered at c's argmax (first maximum in row-major window order, strict >,
+ * NaN wins: F.max_pool2d(return_indices=True)).  bwd scatters (gxo, gco/4) to that argmax. */
+int nconv_b200_pool_conf_argmax_fwd(const float* x, const float* c, float* xo, float* co, int planes,
+                                    int H, int W, void* stream);
+int nconv_b200_pool_conf_argmax_bwd(const float* gxo, const float* gco, const float* c, float* gx,
+                                    float* gc, int planes, int H, int W, void* stream);
+
 /* ---- (a6) nearest upsample + channel concat — step1.py:78-90 --------------------------- */
 int nconv_b200_upcat_fwd(const float* skip, const float* low, float* out, int B, int Cs, int Cl,
                          int H, int W, int HL, int WL, int skip_first, void* stream);
@@ -123,6 +131,14 @@ int nconv_b200_dnet_forward(const float* S, const float* const* params, float* o
  * runs the latter (the frozen step 1 inside a training step uses it, so the training-step numerics stay pure fp32). */
 int nconv_b200_dnet_forward_fp32(const float* S, const float* const* params, float* out, int B,
                                  int H, int W, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- GPU input pipeline: the loaders' per-sample host work after the H2D copy ----------------
+ * rgb:  uint8 [B,H,W,3] (cv2.imread BGR, HWC) -> fp32 [B,3,H,W]           dataset/nyuloader.py:69, kittiloader.py:63
+ * depth: [n] uint8 / uint16 / fp32 (elem_bytes 1/2/4) -> fp32 * scale      kittiloader.py:66-76 (`/ 256.0`)
+ * sparsify: out = raw * (1 + noise) * mask, noise (fp32) and mask (uint8 0/1) optional   nyuloader.py:83-124 */
+int nconv_b200_rgb_u8_to_f32(const uint8_t* hwc, float* chw, int B, int H, int W, void* stream);
+int nconv_b200_depth_decode(const void* raw, int elem_bytes, float* out, long long n, float scale, void* stream);
+int nconv_b200_sparsify(const float* raw, const float* noise, const uint8_t* mask, float* out, long long n, void* stream);
 
 /* Debug aid (no reference counterpart): 64 bytes of pinned, device-mapped host memory in which a tcgen05 NConv kernel
  * records {barrier code, block, warp, tile / M-tile index, parity} when one of its bounded barrier waits gives up. */

@@ -101,6 +101,25 @@ def dnet_forward(S, sd, prefix="d_net.", crop="general", return_all=False):
     return out
 
 
+def pool_conf_argmax(x, c):
+    """Opt-in upstream-nconv pooling (NOT in the reference, which pools independently at step1.py:62-74; SURVEY 8f
+    rank 4): confidence max-pooled with indices, data gathered at those indices, pooled confidence / 4."""
+    co, idx = F.max_pool2d(c, 2, 2, return_indices=True)
+    xo = torch.gather(x.flatten(2), 2, idx.flatten(2)).view_as(co)
+    return xo, co / 4
+
+
+def sparsify(raw, mask=None, noise=None):
+    """dataset/nyuloader.py:83-124 given the random draws: noisy points `d += d * noise` (:107), then `d * mask` (:113)
+    or the zeroed random points (:121-123), which is a 0/1 mask as well."""
+    d = raw
+    if noise is not None:
+        d = d + d * noise
+    if mask is not None:
+        d = d * mask.to(d.dtype)
+    return d
+
+
 def apply_enforce_pos(sd, prefix="d_net."):
     """What one training-mode forward does to the stored NConv weights (step1.py:190-195):
     weight.data <- softplus(weight, beta=10), in place, for all nine layers."""

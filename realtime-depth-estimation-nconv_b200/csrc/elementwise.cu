@@ -343,6 +343,94 @@ extern "C" int nconv_b200_maxpool2x2_bwd(const float* gy, const float* x, float*
   return (int)cudaGetLastError();
 }
 
+// ---- opt-in "confidence-argmax" pooling: what upstream nconv (and BASELINE's north_star text) does and
+// the reference does NOT (it pools data and confidence independently, step1.py:62-74): the confidence is max-pooled, the
+// data is GATHERED at the confidence's argmax, and the pooled confidence is divided by 4.  Same window order and
+// tie-break as F.max_pool2d(return_indices=True): first maximum in row-major order, strict `>`, NaN wins.
+namespace nconv {
+__global__ void pool_conf_argmax_fwd_kernel(const float* __restrict__ x, const float* __restrict__ c, float* __restrict__ xo,
+                                            float* __restrict__ co, int planes, int H, int W, int HP, int WP) {
+  const long long total = (long long)planes * HP * WP;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int px = (int)(idx % WP);
+    const long long r = idx / WP;
+    const int py = (int)(r % HP);
+    const long long base = ((r / HP) * H + 2 * py) * W + 2 * px;
+    const int off[4] = {0, 1, W, W + 1};
+    float m = -INFINITY;
+    int am = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float v = __ldg(c + base + off[k]);
+      if (v > m || v != v) { m = v; am = k; }
+    }
+    co[idx] = m * 0.25f;
+    xo[idx] = __ldg(x + base + off[am]);
+  }
+}
+
+// gx, gc <- scatter of (gxo, gco / 4) to the confidence's argmax; every other window element gets 0.
+__global__ void pool_conf_argmax_bwd_kernel(const float* __restrict__ gxo, const float* __restrict__ gco, const float* __restrict__ c,
+                                            float* __restrict__ gx, float* __restrict__ gc, int planes, int H, int W, int HP, int WP) {
+  const int HC = (H + 1) / 2, WC = (W + 1) / 2;
+  const long long total = (long long)planes * HC * WC;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int cx = (int)(idx % WC);
+    const long long r = idx / WC;
+    const int cy = (int)(r % HC);
+    const long long pl = r / HC;
+    const long long base = (pl * H + 2 * cy) * W + 2 * cx;
+    if (cy < HP && cx < WP) {
+      const int off[4] = {0, 1, W, W + 1};
+      float m = -INFINITY;
+      int am = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float v = __ldg(c + base + off[k]);
+        if (v > m || v != v) { m = v; am = k; }
+      }
+      const long long o = (pl * HP + cy) * WP + cx;
+      const float g1 = gxo ? __ldg(gxo + o) : 0.f, g2 = gco ? 0.25f * __ldg(gco + o) : 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (gx) gx[base + off[k]] = (am == k) ? g1 : 0.f;
+        if (gc) gc[base + off[k]] = (am == k) ? g2 : 0.f;
+      }
+    } else {
+      for (int dy = 0; dy < 2; ++dy)
+        for (int dx = 0; dx < 2; ++dx)
+          if (2 * cy + dy < H && 2 * cx + dx < W) {
+            if (gx) gx[base + dy * W + dx] = 0.f;
+            if (gc) gc[base + dy * W + dx] = 0.f;
+          }
+    }
+  }
+}
+}  // namespace nconv
+
+extern "C" int nconv_b200_pool_conf_argmax_fwd(const float* x, const float* c, float* xo, float* co, int planes, int H, int W,
+                                               void* stream) {
+  if (!x || !c || !xo || !co || planes <= 0 || H < 2 || W < 2) return NCONV_ERR_BAD_ARG;
+  const int HP = H / 2, WP = W / 2;
+  {
+    LaunchScope ls((cudaStream_t)stream, "pool_conf_argmax_fwd", 0.0, 4.0 * planes * (2.0 * H * W + 2.0 * HP * WP));
+    nconv::pool_conf_argmax_fwd_kernel<<<grid_for((long long)planes * HP * WP), 256, 0, (cudaStream_t)stream>>>(x, c, xo, co, planes, H, W, HP, WP);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_pool_conf_argmax_bwd(const float* gxo, const float* gco, const float* c, float* gx, float* gc, int planes,
+                                               int H, int W, void* stream) {
+  if (!c || (!gx && !gc) || planes <= 0 || H < 2 || W < 2) return NCONV_ERR_BAD_ARG;
+  const int HP = H / 2, WP = W / 2;
+  const long long cells = (long long)planes * ((H + 1) / 2) * ((W + 1) / 2);
+  {
+    LaunchScope ls((cudaStream_t)stream, "pool_conf_argmax_bwd", 0.0, 0.0);
+    nconv::pool_conf_argmax_bwd_kernel<<<grid_for(cells), 256, 0, (cudaStream_t)stream>>>(gxo, gco, c, gx, gc, planes, H, W, HP, WP);
+  }
+  return (int)cudaGetLastError();
+}
+
 extern "C" int nconv_b200_upcat_fwd(const float* skip, const float* low, float* out, int B, int Cs,
                                     int Cl, int H, int W, int HL, int WL, int skip_first,
                                     void* stream) {

@@ -23,9 +23,11 @@
 //   [W_hi ; W_hi] tiles alias their two K-halves with LBO = 0); only pixel stages stream through the ring,
 //   one TMA tensor copy per staged plane.
 //
-// Warp roles (13 warps): warp 0 producer (weights once, then 4 tensor copies per K-stage), warp 1 MMA issuer, three
-// STAGER warps (2, 4, 5: TMEM lane quarters 2, 0, 1 = the three tap groups; a warp may only read quarter warp % 4) and
-// eight EMITTER warps (3, 6..12) in two groups of four.  Stagers drain the accumulator window by window (32 columns)
+// Warp roles (16 warps): warp 0 producer (weights once, then 4 tensor copies per K-stage), warp 1 MMA issuer, six
+// STAGER warps in two sets (2, 4, 5 and 6, 8, 9: TMEM lane quarters 2, 0, 1 = the three tap groups; a warp may only read
+// quarter warp % 4; the sets take alternate windows so one set's shared-memory stores overlap the other's tcgen05.ld:
+// draining 3 x 32 KB per tile at the 16 B/clk a lane quarter delivers is the epilogue's floor) and eight EMITTER warps
+// (3, 7, 10..15) in two groups of four.  Stagers drain the accumulator window by window (32 columns)
 // into a 128-row shared-memory ring (one plane per tap group, row = column - tap shift); emitters sum the three planes,
 // apply scale/shift/ReLU, split to hi/lo and store P8 (warp -> 8-channel chunk, lane -> pixel), the two groups taking
 // alternate windows.  Stagers and emitters are decoupled by per-window mbarriers (full: 3 stager arrivals, empty: 4
@@ -37,7 +39,7 @@
 
 namespace nconv {
 
-constexpr int TCX_THREADS = 416;                 // 13 warps
+constexpr int TCX_THREADS = 512;                 // 16 warps
 constexpr int TCX_N = 256;                 // pixels per MMA / TMEM accumulator columns
 constexpr int TCX_OUT = TCX_N - 2;         // output pixels per tile (column shifts 0..2)
 constexpr int TCX_WHALF_BYTES = 128 * 16;              // one K-half of an A tile: [128 rows][8] bf16
@@ -88,7 +90,7 @@ __global__ void __launch_bounds__(TCX_THREADS, 1) conv_tcx_kernel(const __grid_c
   }
   if (threadIdx.x == 0) {
     for (int s = 0; s < TCX_MAX_STAGES; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 3); }
+    for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 6); }
     for (int b = 0; b < 4; ++b) { mbar_init(smem_u32(&s_sfull[b]), 3); mbar_init(smem_u32(&s_sempty[b]), 4); }
     mbar_init(smem_u32(&s_wfull), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -189,20 +191,21 @@ __global__ void __launch_bounds__(TCX_THREADS, 1) conv_tcx_kernel(const __grid_c
         if (++stage == (uint32_t)a.stages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 2 || warp == 4 || warp == 5) {
+  } else if (warp == 2 || warp == 4 || warp == 5 || warp == 6 || warp == 8 || warp == 9) {
     // ===================== stagers: TMEM -> shared-memory ring =====================
     // TMEM lane 32g + co holds tap-group g of output channel co: the warp of lane quarter g copies its 32x32 block of
     // every 32-column window into plane g of the ring at row (column - g) (conflict-free 128-byte stores per column).
     const int q = warp & 3;                                          // TMEM lane quarter = tap group (0, 1, 2)
+    const uint32_t sj = warp >= 6 ? 1u : 0u;                         // stager set: windows with (running index) % 2 == sj
     float* S_st = reinterpret_cast<float*>(smem + w_bytes) + q * TCX_S_PLANE + lane;
-    uint32_t it = 0, gw = 0;                                         // tile counter, running window counter
+    uint32_t it = 0;                                                 // tile counter; running window index gw = 8 it + w
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, ++it) {
       const uint32_t buf = it & 1, tphase = (it >> 1) & 1;
       const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * TCX_N;
       mbar_wait(smem_u32(&s_tfull[buf]), tphase);
       tc_fence_after();
       uint32_t va[32], vb[32];
-      auto stage_window = [&](const uint32_t* v) {
+      auto stage_window = [&](const uint32_t* v, uint32_t gw) {
         // window gw overwrites the ring rows of window gw - 4, which the emitters of windows gw - 4 and gw - 3 read
         if (gw >= 4) mbar_wait(smem_u32(&s_sempty[(gw - 4) & 3]), ((gw - 4) >> 2) & 1);
         if (gw >= 3) mbar_wait(smem_u32(&s_sempty[(gw - 3) & 3]), ((gw - 3) >> 2) & 1);
@@ -212,30 +215,32 @@ __global__ void __launch_bounds__(TCX_THREADS, 1) conv_tcx_kernel(const __grid_c
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&s_sfull[gw & 3]));
-        ++gw;
       };
-      if (a.dbg & 1) { gw += TCX_N / 32; }
-      else {
-        tmem_ld32(tcol, va);
-#pragma unroll 1
-        for (int w = 0; w < TCX_N / 32; w += 2) {
-          tmem_ld_wait();
-          tmem_ld32(tcol + (w + 1) * 32, vb);
-          stage_window(va);
-          tmem_ld_wait();
-          if (w + 2 < TCX_N / 32) tmem_ld32(tcol + (w + 2) * 32, va);
-          stage_window(vb);
-        }
+      if (!(a.dbg & 1)) {
+        // this set's windows of the tile: w = sj, sj + 2, sj + 4, sj + 6 (the running index 8 it + w has w's parity)
+        const uint32_t g0 = 8 * it + sj;
+        tmem_ld32(tcol + sj * 32, va);
+        tmem_ld_wait();
+        tmem_ld32(tcol + (sj + 2) * 32, vb);
+        stage_window(va, g0);
+        tmem_ld_wait();
+        tmem_ld32(tcol + (sj + 4) * 32, va);
+        stage_window(vb, g0 + 2);
+        tmem_ld_wait();
+        tmem_ld32(tcol + (sj + 6) * 32, vb);
+        stage_window(va, g0 + 4);
+        tmem_ld_wait();
+        stage_window(vb, g0 + 6);
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&s_tempty[buf]));          // the accumulator is drained: tile i+2's MMAs may start
+      if (lane == 0) mbar_arrive(smem_u32(&s_tempty[buf]));          // this warp's share of the accumulator is drained
     }
   } else {
     // ===================== emitters: ring -> P8 =====================
-    // warps 3, 6, 7, 8 (group 0) and 9, 10, 11, 12 (group 1); group g emits the windows with (running index) % 2 == g;
+    // warps 3, 7, 10, 11 (group 0) and 12, 13, 14, 15 (group 1); group g emits the windows with (running index) % 2 == g;
     // within a group warp -> 8-channel chunk, lane -> pixel (512-byte contiguous stores per plane).
-    const int ei = (warp == 3) ? 0 : warp - 5;                       // 0..7
+    const int ei = (warp == 3) ? 0 : (warp == 7 ? 1 : warp - 8);     // 0..7
     const int grp = ei >> 2, ech = ei & 3, ep = lane;
     const float* S_ld = reinterpret_cast<const float*>(smem + w_bytes) + 8 * ech;
     const size_t oplane = (size_t)(a.AH + 2) * (a.AW + 2) * 8;
@@ -256,6 +261,8 @@ __global__ void __launch_bounds__(TCX_THREADS, 1) conv_tcx_kernel(const __grid_c
       for (int w = 0; w < TCX_N / 32; ++w, ++gw) {
         if ((int)(gw & 1) == grp) {
           mbar_wait(smem_u32(&s_sfull[gw & 3]), (gw >> 2) & 1);
+          // rows 32 gw - 2 and 32 gw - 1 hold columns of the previous window, staged by the OTHER stager set
+          if (w > 0) mbar_wait(smem_u32(&s_sfull[(gw - 1) & 3]), ((gw - 1) >> 2) & 1);
           const int m = 32 * w - 2 + ep;
           const int ay = ty * a.R + rr, ax = tx * a.Wt + cc;
           if (m >= 0 && rr < a.R && cc < a.Wt && ay < a.AH && ax < a.AW && !(a.dbg & 16)) {

@@ -49,8 +49,14 @@ class DNET(nn.Module):
     _ORDER = ("nconv1", "nconv2", "nconv_down1", "nconv_down2", "nconv_down3",
               "nconv4", "nconv5", "nconv6", "nconv7")
 
-    def __init__(self, out_ch):
+    def __init__(self, out_ch, pool="independent"):
         super().__init__()
+        # pool: "independent" = the reference (two separate F.max_pool2d, step1.py:62-74);
+        # "conf_argmax" = opt-in upstream-nconv behaviour (data gathered at the confidence argmax, pooled confidence / 4):
+        # NOT what the reference computes, never the default
+        if pool not in ("independent", "conf_argmax"):
+            raise ValueError("DNET: pool must be 'independent' or 'conf_argmax'")
+        self.pool = pool
         pos_fn = "softplus"
         nc = 8
         self.nconv1 = NConv2d(1, nc, (5, 5), pos_fn, 'p', padding=(2, 2))
@@ -77,7 +83,7 @@ class DNET(nn.Module):
         if S.dim() != 4 or S.shape[1] != 1:
             raise ValueError("DNET expects a [B,1,H,W] sparse depth map")
         H, W = S.shape[2:]
-        if not return_confidence and self._fusable(S):
+        if not return_confidence and self.pool == "independent" and self._fusable(S):
             # One enqueue of 9 fused kernels.  The EnforcePos pre-hooks still fire (they mutate
             # the stored weights in training mode even when those are frozen, step1.py:190-195).
             for l in self._layers():
@@ -94,9 +100,13 @@ class DNET(nn.Module):
         c0 = _K.confidence_mask(S, 0.01)
         x1, c1 = self.nconv1(S, c0)
         x1, c1 = self.nconv2(x1, c1)
-        x2, c2 = self.nconv_down1(_K.maxpool2x2(x1), _K.maxpool2x2(c1))
-        x3, c3 = self.nconv_down2(_K.maxpool2x2(x2), _K.maxpool2x2(c2))
-        x4, c4 = self.nconv_down3(_K.maxpool2x2(x3), _K.maxpool2x2(c3))
+        if self.pool == "conf_argmax":
+            pool = _K.pool_conf_argmax
+        else:
+            pool = lambda x, c: (_K.maxpool2x2(x), _K.maxpool2x2(c))      # noqa: E731
+        x2, c2 = self.nconv_down1(*pool(x1, c1))
+        x3, c3 = self.nconv_down2(*pool(x2, c2))
+        x4, c4 = self.nconv_down3(*pool(x3, c3))
         x34, c34 = self.nconv4(_K.upcat(x3, x4, True), _K.upcat(c3, c4, True))
         x23, c23 = self.nconv5(_K.upcat(x2, x34, True), _K.upcat(c2, c34, True))
         xo, co = self.nconv6(_K.upcat(x1, x23, False), _K.upcat(c1, c23, False))

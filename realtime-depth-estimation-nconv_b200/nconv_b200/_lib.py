@@ -84,12 +84,17 @@ SIGNATURES = {
     "nconv_b200_confidence_mask": (c_int, [c_void_p, c_void_p, c_longlong, c_float, c_void_p]),
     "nconv_b200_maxpool2x2_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "nconv_b200_maxpool2x2_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "nconv_b200_pool_conf_argmax_fwd": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p]),
+    "nconv_b200_pool_conf_argmax_bwd": (c_int, [c_void_p] * 5 + [c_int] * 3 + [c_void_p]),
     "nconv_b200_upcat_fwd": (c_int, [c_void_p] * 3 + [c_int] * 8 + [c_void_p]),
     "nconv_b200_upcat_bwd": (c_int, [c_void_p] * 3 + [c_int] * 8 + [c_void_p]),
     "nconv_b200_dnet_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nconv_b200_dnet_forward": (c_int, [c_void_p, POINTER(c_void_p), c_void_p, c_int, c_int, c_int,
                                         c_void_p, c_size_t, c_void_p]),
     "nconv_b200_debug_buffer": (c_int, [c_void_p]),
+    "nconv_b200_rgb_u8_to_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "nconv_b200_depth_decode": (c_int, [c_void_p, c_int, c_void_p, c_longlong, c_float, c_void_p]),
+    "nconv_b200_sparsify": (c_int, [c_void_p] * 4 + [c_longlong, c_void_p]),
     "nconv_b200_n8_bytes": (c_size_t, [c_int] * 3),
     "nconv_b200_n8_zero_ring": (c_int, [c_void_p] + [c_int] * 3 + [c_void_p]),
     "nconv_b200_n8_pack": (c_int, [c_void_p] * 3 + [c_int] * 3 + [c_void_p]),

@@ -46,6 +46,12 @@ def maxpool2x2(x):
     return F.max_pool2d(x, 2, 2)                                   # step1.py:62-74
 
 
+def pool_conf_argmax(x, c):
+    co, idx = F.max_pool2d(c, 2, 2, return_indices=True)
+    xo = torch.gather(x.flatten(2), 2, idx.flatten(2)).view_as(co)
+    return xo, co / 4
+
+
 def upcat(skip, low, skip_first: bool):
     up = F.interpolate(low, skip.shape[2:], mode="nearest")        # step1.py:78-89
     return torch.cat((skip, up), 1) if skip_first else torch.cat((up, skip), 1)
@@ -120,6 +126,7 @@ def border_zeroed(x, top: int, bottom: int, left: int):
 # op name -> ATen restatement (what `ops.K.<name>` resolves to while a TorchScript trace is being recorded)
 ATEN = {
     "nconv2d": nconv2d, "confidence_mask": confidence_mask, "maxpool2x2": maxpool2x2, "upcat": upcat,
+    "pool_conf_argmax": pool_conf_argmax,
     "dnet_forward": dnet_forward, "conv2d": conv2d, "convT4x4s2": convT4x4s2, "bilinear_ac": bilinear_ac,
     "bn_fold": bn_fold, "border_zeroed": border_zeroed,
 }

@@ -233,6 +233,42 @@ torch.library.register_autograd(
     setup_context=lambda ctx, inputs, output: ctx.save_for_backward(inputs[0]))
 
 
+def _pool_conf_argmax(x, c):
+    x = _prep(x, "data"); c = _prep(c, "conf")
+    if x.shape != c.shape or x.dim() != 4:
+        raise ValueError("pool_conf_argmax: data and conf must be [B,C,H,W] of the same shape")
+    B, C, H, W = x.shape
+    xo = torch.empty((B, C, H // 2, W // 2), device=x.device, dtype=torch.float32)
+    co = torch.empty_like(xo)
+    if xo.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_pool_conf_argmax_fwd(_p(x), _p(c), _p(xo), _p(co), B * C, H, W, _stream(x)), "pool_conf_argmax_fwd")
+    return xo, co
+
+
+def _pool_conf_argmax_backward(gxo, gco, c):
+    c = _prep(c, "conf"); gxo = _prep_opt(gxo, "gxo"); gco = _prep_opt(gco, "gco")
+    B, C, H, W = c.shape
+    gx = torch.empty_like(c)
+    gc = torch.empty_like(c)
+    if c.numel():
+        with torch.cuda.device(c.device):
+            check(_C.nconv_b200_pool_conf_argmax_bwd(_p(gxo), _p(gco), _p(c), _p(gx), _p(gc), B * C, H, W, _stream(c)),
+                  "pool_conf_argmax_bwd")
+    return gx, gc
+
+
+_define("pool_conf_argmax(Tensor data, Tensor conf) -> (Tensor, Tensor)", _pool_conf_argmax,
+        lambda x, c: (x.new_empty((x.shape[0], x.shape[1], x.shape[2] // 2, x.shape[3] // 2)),
+                      x.new_empty((x.shape[0], x.shape[1], x.shape[2] // 2, x.shape[3] // 2))))
+_define("pool_conf_argmax_backward(Tensor? gxo, Tensor? gco, Tensor conf) -> (Tensor, Tensor)", _pool_conf_argmax_backward,
+        lambda gxo, gco, c: (torch.empty_like(c), torch.empty_like(c)))
+torch.library.register_autograd(
+    "nconv_b200::pool_conf_argmax",
+    lambda ctx, gxo, gco: torch.ops.nconv_b200.pool_conf_argmax_backward(gxo, gco, ctx.saved_tensors[0]),
+    setup_context=lambda ctx, inputs, output: ctx.save_for_backward(inputs[1]))
+
+
 def _upcat(skip, low, skip_first: bool):
     skip = _prep(skip, "skip"); low = _prep(low, "low")
     B, Cs, H, W = skip.shape
@@ -623,6 +659,59 @@ def nconv_tc(a: "N8", b, weight, bias, a_first=True, eps=1e-7, want_n8=False, wa
                         _p(out.get("y")), _p(out.get("cout")), _p(w7), _p(b7), _p(out.get("tail")),
                         a.B, a.H, a.W, K, CB, eps)
         check(_C.nconv_b200_nconv_tc(byref(d), _stream(a.buf)), "nconv_tc")
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# GPU input pipeline (csrc/input_pipeline.cu): the loaders' host work behind the H2D copy
+# --------------------------------------------------------------------------------------
+def _raw_cuda(t, name, dtypes):
+    if not t.is_cuda:
+        raise RuntimeError("nconv_b200: %s must be a CUDA tensor (no CPU path exists)" % name)
+    if t.dtype not in dtypes:
+        raise TypeError("nconv_b200: %s must be one of %s, got %s" % (name, dtypes, t.dtype))
+    return t.contiguous()
+
+
+def decode_rgb(hwc_u8):
+    """cv2.imread -> FloatTensor(...).permute(2, 0, 1) (dataset/nyuloader.py:69): uint8 [B,H,W,3] -> fp32 [B,3,H,W]."""
+    x = _raw_cuda(hwc_u8, "rgb", (torch.uint8,))
+    if x.dim() != 4 or x.shape[3] != 3:
+        raise ValueError("decode_rgb: expected uint8 [B,H,W,3]")
+    B, H, W, _ = x.shape
+    out = torch.empty((B, 3, H, W), device=x.device, dtype=torch.float32)
+    if out.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_rgb_u8_to_f32(_p(x), _p(out), B, H, W, _stream(x)), "rgb_u8_to_f32")
+    return out
+
+
+def decode_depth(raw, scale=1.0):
+    """[B,H,W] or [B,1,H,W] uint8 / uint16 / fp32 -> fp32 [B,1,H,W] * scale (kittiloader.py:66-76: scale = 1/256)."""
+    x = _raw_cuda(raw, "depth", (torch.uint8, torch.uint16, torch.int16, torch.float32))
+    if x.dim() == 3:
+        x = x.unsqueeze(1)
+    if x.dim() != 4 or x.shape[1] != 1:
+        raise ValueError("decode_depth: expected [B,H,W] or [B,1,H,W]")
+    out = torch.empty(x.shape, device=x.device, dtype=torch.float32)
+    if out.numel():
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_depth_decode(_p(x), x.element_size(), _p(out), x.numel(), float(scale), _stream(x)), "depth_decode")
+    return out
+
+
+def sparsify(depth, mask=None, noise=None):
+    """preprocess_depth (dataset/nyuloader.py:83-124) given the caller's random draws: depth + depth*noise on the noisy
+    points (noise: fp32, 0 elsewhere), then the 0/1 mask (uint8)."""
+    d = _prep(depth, "depth")
+    m = None if mask is None else _raw_cuda(mask, "mask", (torch.uint8, torch.bool))
+    z = None if noise is None else _prep(noise, "noise")
+    if (m is not None and m.numel() != d.numel()) or (z is not None and z.numel() != d.numel()):
+        raise ValueError("sparsify: mask / noise must have depth's number of elements")
+    out = torch.empty_like(d)
+    if d.numel():
+        with torch.cuda.device(d.device):
+            check(_C.nconv_b200_sparsify(_p(d), _p(z), _p(m), _p(out), d.numel(), _stream(d)), "sparsify")
     return out
 
 
