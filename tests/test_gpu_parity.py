@@ -497,9 +497,14 @@ def test_conv_train_forward_backward_vs_fp64(cfg):
     bd = bb.to(dev()).requires_grad_(True) if bias else None
     y = ops.conv_train(xd, wd, bd, None, stride, relu)
     (y * G.to(dev())).sum().backward()
-    assert _rel(y, yr) <= 1e-5
+    # 3x3 / stride-1 layers with Ci % 16 == 0 and Co in {32, 64} run forward and data gradient on tcgen05 with split-bf16
+    # operands (ops._tc_train_ok): fp32-class, bounded like the inference kernels (TC_TOL = 2e-5 of the output scale);
+    # the weight gradient is fp32 everywhere
+    tc = ops._tc_train_ok(CI, CO, K, stride)          # data gradient on tcgen05 (forward too with NCONV_B200_TRAIN_TC_FWD=1)
+    report("conv_train_%d_%d_k%d_s%d" % (CI, CO, K, stride), tc=float(tc), y=_rel(y, yr), gw=_rel(wd.grad, wr.grad), gx=_rel(xd.grad, xr.grad))
+    assert _rel(y, yr) <= (2e-5 if tc else 1e-5)
     assert _rel(wd.grad, wr.grad) <= 2e-5
-    assert _rel(xd.grad, xr.grad) <= 2e-5
+    assert _rel(xd.grad, xr.grad) <= (3e-5 if tc else 2e-5)
     if bias:
         assert _rel(bd.grad, br.grad) <= 2e-5
 
@@ -608,7 +613,12 @@ def test_setp2_train_step_vs_reference_golden(golden, tmp_path, monkeypatch):
         noise = ((ref.double() - ref64).abs() / ref64.abs().clamp_min(1e-3)).max().item()
         ours = ((_sub(d).double() - ref64).abs() / ref64.abs().clamp_min(1e-3)).max().item()
         report("setp2_train_step_depth_scale%d" % i, rel_floor0p1=err, rel_vs_fp64_floor1e3=ours, reference_fp32_vs_fp64_floor1e3=noise)
-        assert ours <= max(1e-4, 1.5 * noise), ("depth scale %d at floor 1e-3" % i, ours, noise)
+        # split-bf16 tensor-core convs (forward of the dense 3x3 layers): ~1e-6 of the output scale everywhere, which at
+        # a 1e-3 floor exceeds 1e-4 only where the depth passes through zero; bounded there in absolute terms
+        abs_err = (_sub(d).double() - ref64).abs()
+        over = abs_err / ref64.abs().clamp_min(1e-3) > max(1e-4, 1.5 * noise)
+        assert float(over.double().mean()) <= 1e-3 and (not bool(over.any()) or float(abs_err[over].max()) <= 5e-6), \
+            ("depth scale %d at floor 1e-3" % i, ours, noise)
     names = [str(n) for n in g["grad_names"]]
     params = dict(m.named_parameters())
     assert sorted(names) == sorted(k for k, p in params.items() if p.grad is not None)
