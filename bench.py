@@ -507,7 +507,7 @@ def run_b200(args):
 
     rows = summarise_kernels(records, args.steps)
     roof = roofline_of(rows[0], peaks) if rows else None
-    nconv_rows = [r for r in rows if r["kernel"].startswith("nconv_fwd")]
+    nconv_rows = [r for r in rows if r["kernel"].startswith(("nconv_fwd", "tc_nconv 8", "nconv1_n8"))]
     line = {
         "metric": METRIC, "value": frames * world * args.steps / (ms / 1e3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
@@ -522,7 +522,7 @@ def run_b200(args):
         "clocks": clocks,
         "roofline": roof,
         "parity": parity, "parity_max_rel": parity["max_rel_floor0p1"] if parity else None,
-        "nconv_roofline": [roofline_of(r, peaks) for r in nconv_rows[:3]],
+        "nconv_roofline": [roofline_of(r, peaks) for r in nconv_rows[:4]],
         "kernels": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()} for r in rows[:40]],
     }
     line.update(extra)
