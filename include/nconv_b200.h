@@ -132,6 +132,14 @@ int nconv_b200_dnet_forward(const float* S, const float* const* params, float* o
 int nconv_b200_dnet_forward_fp32(const float* S, const float* const* params, float* out, int B,
                                  int H, int W, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Weight gradient of a 3x3 / stride-1 / pad-1 convolution on tcgen05 (the dL/dW half of train_step2.py:60-66's
+ * backward for step2.py:178-195, 216-236, 290-297): x and g = dL/dy are P8 tensors [B,CI,H,W] / [B,CO,H,W]
+ * (nconv_b200_p8_pack), gw is fp32 [CO][CI][3][3].  CI in {32, 64, 128, 192, 256}, CO in {32, 64}.  Split-bf16
+ * operands with all four partial products, fp32 accumulation in TMEM, deterministic final sum. */
+size_t nconv_b200_conv_wgrad_tc_ws_bytes(int B, int CI, int CO, int H, int W);
+int nconv_b200_conv_wgrad_tc(const void* x_p8, const void* g_p8, float* gw, void* workspace,
+                             size_t workspace_bytes, int B, int CI, int CO, int H, int W, void* stream);
+
 /* ---- GPU input pipeline: the loaders' per-sample host work after the H2D copy ----------------
  * rgb:  uint8 [B,H,W,3] (cv2.imread BGR, HWC) -> fp32 [B,3,H,W]           dataset/nyuloader.py:69, kittiloader.py:63
  * depth: [n] uint8 / uint16 / fp32 (elem_bytes 1/2/4) -> fp32 * scale      kittiloader.py:66-76 (`/ 256.0`)

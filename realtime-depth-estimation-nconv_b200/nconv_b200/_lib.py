@@ -92,6 +92,8 @@ SIGNATURES = {
     "nconv_b200_dnet_forward": (c_int, [c_void_p, POINTER(c_void_p), c_void_p, c_int, c_int, c_int,
                                         c_void_p, c_size_t, c_void_p]),
     "nconv_b200_debug_buffer": (c_int, [c_void_p]),
+    "nconv_b200_conv_wgrad_tc_ws_bytes": (c_size_t, [c_int] * 5),
+    "nconv_b200_conv_wgrad_tc": (c_int, [c_void_p] * 4 + [c_size_t] + [c_int] * 5 + [c_void_p]),
     "nconv_b200_rgb_u8_to_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "nconv_b200_depth_decode": (c_int, [c_void_p, c_int, c_void_p, c_longlong, c_float, c_void_p]),
     "nconv_b200_sparsify": (c_int, [c_void_p] * 4 + [c_longlong, c_void_p]),

@@ -790,11 +790,28 @@ def _conv_wgrad(g, x, K: int, S: int, P: int):
 import os as _os
 _TRAIN_TC = _os.environ.get("NCONV_B200_TRAIN_NO_TC") is None
 _TRAIN_TC_FWD = _TRAIN_TC and _os.environ.get("NCONV_B200_TRAIN_TC_FWD") is not None
+_TRAIN_TC_WGRAD = _os.environ.get("NCONV_B200_TRAIN_NO_TC_WGRAD") is None      # weight gradients on tcgen05 (csrc/wgrad_tc.cu)
 
 
 def _tc_train_ok(ci: int, co: int, K: int, stride: int) -> bool:
     # Co = 32 keeps its packed weights resident in shared memory (24 KB per 16 input channels): Ci <= 64
     return _TRAIN_TC and K == 3 and stride == 1 and ci % 16 == 0 and ((co == 64 and ci <= 256) or (co == 32 and ci <= 64))
+
+
+def _tc_wgrad_ok(ci: int, co: int, K: int, stride: int) -> bool:
+    return _TRAIN_TC and _TRAIN_TC_WGRAD and K == 3 and stride == 1 and co in (32, 64) and (ci == 32 or (ci % 64 == 0 and ci <= 256))
+
+
+def _conv_wgrad_tc(x8: "P8", g8: "P8"):
+    """gw [CO,CI,3,3] from P8 activations / output gradients (csrc/wgrad_tc.cu)."""
+    dev = x8.buf.device
+    gw = torch.empty((g8.C, x8.C, 3, 3), device=dev, dtype=torch.float32)
+    n = int(_C.nconv_b200_conv_wgrad_tc_ws_bytes(x8.B, x8.C, g8.C, x8.H, x8.W))
+    ws = _scratch(dev, n, "wgrad_tc")
+    with torch.cuda.device(dev):
+        check(_C.nconv_b200_conv_wgrad_tc(_p(x8.buf), _p(g8.buf), _p(gw), _p(ws), n, x8.B, x8.C, g8.C, x8.H, x8.W, _stream(gw)),
+              "conv_wgrad_tc")
+    return gw
 
 
 def _tc_conv3x3(x, weight, shift, relu: bool):
@@ -834,7 +851,12 @@ class _ConvTrain(torch.autograd.Function):
             g2, gb = _relu_bias_bwd(gy, y, relu, want_g=relu, want_bias=has_bias and need_b)
             if relu:
                 g = g2
-        gw = _conv_wgrad(g, x, K, stride, K // 2) if need_w else None
+        g8 = None
+        if need_w and _tc_wgrad_ok(CI, CO, K, stride):
+            g8 = P8.pack(g)
+            gw = _conv_wgrad_tc(P8.pack(x), g8)
+        else:
+            gw = _conv_wgrad(g, x, K, stride, K // 2) if need_w else None
         gx = None
         if need_x:
             dev = x.device
@@ -846,7 +868,8 @@ class _ConvTrain(torch.autograd.Function):
                 # cores in blocks of 64 (or 32) "output" channels when the shapes allow
                 blk = 64 if CI % 64 == 0 else (32 if CI == 32 else 0)
                 if blk and _tc_train_ok(CO, blk, K, 1):
-                    g8 = P8.pack(g)
+                    if g8 is None:
+                        g8 = P8.pack(g)
                     parts = []
                     for c0 in range(0, CI, blk):
                         wpk = tc_pack_weights(TC_S1, wf[c0:c0 + blk].contiguous(), CO, 0)

@@ -509,6 +509,31 @@ def test_conv_train_forward_backward_vs_fp64(cfg):
         assert _rel(bd.grad, br.grad) <= 2e-5
 
 
+@pytest.mark.parametrize("cfg", [
+    # CI, CO, B, H, W
+    (64, 64, 2, 16, 64), (32, 32, 1, 9, 13), (128, 64, 2, 30, 40), (64, 32, 3, 37, 101), (32, 64, 1, 60, 80), (64, 64, 16, 60, 80),
+])
+def test_conv_wgrad_tc_vs_fp64(cfg):
+    """csrc/wgrad_tc.cu (tcgen05, MN-major operands over P8, split-bf16 with all four partial products, fp32 accumulation
+    in TMEM over every pixel of a CTA's tiles, deterministic final sum) against the fp64 weight gradient of F.conv2d:
+    ragged sizes (partial tiles in both directions), channel blocks of 32 / 64 / 128, both Co, many tiles per CTA.
+    Tolerance as for the fp32 kernel: 2e-5 of max|gw|."""
+    from nconv_b200 import ops
+    from nconv_b200.ops import P8
+    CI, CO, B, H, W = cfg
+    g = torch.Generator().manual_seed(sum(cfg))
+    x = torch.rand(B, CI, H, W, generator=g) * 4 - 1
+    gy = torch.randn(B, CO, H, W, generator=g)
+    wr = torch.zeros(CO, CI, 3, 3, dtype=torch.float64, requires_grad=True)
+    (F.conv2d(x.double(), wr, padding=1) * gy.double()).sum().backward()
+    gw = ops._conv_wgrad_tc(P8.pack(x.to(dev())), P8.pack(gy.to(dev())))
+    gw2 = ops._conv_wgrad_tc(P8.pack(x.to(dev())), P8.pack(gy.to(dev())))
+    err = _rel(gw, wr.grad)
+    report("conv_wgrad_tc_%d_%d_%dx%dx%d" % cfg, gw=err)
+    assert err <= 2e-5
+    assert torch.equal(gw, gw2)                       # deterministic
+
+
 @pytest.mark.parametrize("cfg", [(65, 64, 2, 15, 20), (33, 32, 1, 9, 13), (9, 16, 2, 5, 6)])
 def test_convT_train_forward_backward_vs_fp64(cfg):
     from nconv_b200 import ops
