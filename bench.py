@@ -229,7 +229,8 @@ def roofline_of(row, peaks, sustained=True):
            "hbm_frac": frac_hbm, "t_hbm_ms": 1e3 * t_hbm}
     if tc:
         mma_factor = 3.0
-        if row["kernel"].startswith("tc_conv3x3 ") and "->32 " in row["kernel"] and not os.environ.get("NCONV_B200_NO_TCX"):
+        ci = int(row["kernel"].split()[1].split("->")[0]) if row["kernel"].startswith("tc_conv3x3 ") else 0
+        if ci >= 64 and "->32 " in row["kernel"] and not os.environ.get("NCONV_B200_NO_TCX"):
             # pixels-as-N kernel (tc_conv_x.cuh): per kernel row and 16 input channels three M128 x N256 x K16 MMAs
             # produce 3 taps x 32 channels x 254 pixels (a quarter of the stacked rows is zero, lo*lo rides along)
             mma_factor = (128.0 * 256.0) / (32.0 * 254.0)

@@ -517,17 +517,20 @@ static void tc_build_taps(TcArgs& a, int mode, bool has_1x1) {
 
 using namespace nconv;
 
-// Co = 32 stride-1 layers run on the pixels-as-N kernel (tc_conv_x.cuh) with its own weight packing;
-// NCONV_B200_NO_TCX=1 keeps them on conv_tc_kernel (A/B measurements only; read once per process, so
-// packing and launch always agree).
-static bool tcx_on(int mode, int CO) {
+// Co = 32 stride-1 layers with >= 64 input channels run on the pixels-as-N kernel (tc_conv_x.cuh) with its own weight
+// packing.  With 32 input channels the pixels-on-M kernel (N-stacked [W_hi | W_lo]) is the faster one since round 2's
+// convergent MMA issue (32->32 @480x640: 0.68 vs 0.79 ms; 64->32: 1.21 vs 1.20).  NCONV_B200_NO_TCX=1 keeps every layer on
+// conv_tc_kernel, NCONV_B200_TCX_ALL=1 sends every Co = 32 layer to conv_tcx (A/B measurements only; read once per
+// process, so packing and launch always agree).
+static bool tcx_on(int mode, int CO, int CI) {
   static const bool off = getenv("NCONV_B200_NO_TCX") != nullptr;
-  return !off && mode == TC_S1 && CO == TCX_CO;
+  static const bool all = getenv("NCONV_B200_TCX_ALL") != nullptr;
+  return !off && mode == TC_S1 && CO == TCX_CO && (all || CI >= 64);
 }
 
 extern "C" size_t nconv_b200_tc_wpack_bytes(int mode, int CO, int CA, int CB, int has_1x1) {
   if (CO <= 0 || CA <= 0 || CB < 0 || mode < 0 || mode > 2) return 0;
-  if (tcx_on(mode, CO)) return (size_t)((CA + CB) / 16) * TCX_WSTAGE_BYTES;
+  if (tcx_on(mode, CO, CA + CB)) return (size_t)((CA + CB) / 16) * TCX_WSTAGE_BYTES;
   return (size_t)tc_nstage(mode, CA, CB) * tc_ntaps_w(mode, has_1x1 != 0) * 2 * 2 * CO * 8 * sizeof(__nv_bfloat16);
 }
 
@@ -537,7 +540,7 @@ extern "C" int nconv_b200_tc_pack_weights(int mode, const float* w, const float*
   const int lead = tc_lead(mode, CA);
   if ((!lead && CA % 16) || CB % 16) return NCONV_ERR_UNSUPPORTED;
   if (w1 && mode != TC_S2) return NCONV_ERR_BAD_ARG;
-  if (tcx_on(mode, CO)) {
+  if (tcx_on(mode, CO, CA + CB)) {
     const int nst = (CA + CB) / 16, tot = nst * 3 * 4 * 128 * 8;
     {
       LaunchScope ls((cudaStream_t)stream, "tc_pack_weights", 0.0, 8.0 * CO * (CA + CB) * 9);
@@ -567,7 +570,7 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   if (d->yq && (mode == TC_T ? 0 : ((mode == TC_S2 ? (d->H / 2) | (d->W / 2) : (d->H | d->W)) & 1))) return NCONV_ERR_UNSUPPORTED;
   const bool has_1x1 = (mode == TC_S2) && d->has_1x1;
   const int AH = (mode == TC_S2) ? d->H / 2 : d->H, AW = (mode == TC_S2) ? d->W / 2 : d->W;
-  if (tcx_on(mode, d->CO)) {
+  if (tcx_on(mode, d->CO, d->CA + d->CB)) {
     const int nk = (d->CA + d->CB) / 16;
     const TcxPlan p = tcx_plan(AH, AW, nk);
     if (!p.ok) return NCONV_ERR_UNSUPPORTED;
