@@ -99,3 +99,44 @@ class StreamedInference:
             retire((i + k) % self.depth)
         results.sort(key=lambda r: r[0])
         return [r for _, r in results]
+
+
+class GraphedInference:
+    """The module's inference forward captured ONCE in a CUDA graph and replayed per call: one `cudaGraphLaunch` instead of
+    ~50 kernel launches plus the Python between them (the step is launch-latency-free, and on an 8-GPU box the eight ranks
+    no longer compete for host cores to enqueue).  Shapes are fixed at capture; `__call__` copies the caller's device
+    tensors into the graph's static input buffers (device-to-device, ~0.05 ms for a 32-frame batch) and returns the
+    graph's static outputs — valid until the next call on this object (copy them if they must outlive it).
+
+    Everything the launchers do lazily (kernel attributes, driver entry points, packed weights, P8 / N8 workspaces, scratch
+    buffers of the capture stream) happens in the warm-up passes, which run on the capture stream before capturing.
+    The captured graph bakes in the parameter pointers AND the packed weights: re-capture (`GraphedInference(...)` again)
+    after the weights change."""
+
+    def __init__(self, model: Callable, example_inputs: Sequence[torch.Tensor], warmup: int = 3):
+        self.model = model
+        self.static_in = [t.detach().clone() for t in example_inputs]
+        dev = self.static_in[0].device
+        self.graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.no_grad(), torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                out = model(*self.static_in)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        with torch.no_grad(), torch.cuda.graph(self.graph, stream=side):
+            out = model(*self.static_in)
+        self.static_out = list(out) if isinstance(out, (tuple, list)) else [out]
+        self._tuple = isinstance(out, (tuple, list))
+
+    def __call__(self, *inputs: torch.Tensor):
+        if len(inputs) != len(self.static_in):
+            raise ValueError("GraphedInference: expected %d inputs" % len(self.static_in))
+        for dst, src in zip(self.static_in, inputs):
+            if src.shape != dst.shape or src.dtype != dst.dtype:
+                raise ValueError("GraphedInference: input shape/dtype differs from the captured one")
+            if src.data_ptr() != dst.data_ptr():
+                dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return tuple(self.static_out) if self._tuple else self.static_out[0]

@@ -287,3 +287,24 @@ def test_streamed_inference_delivers_every_batch():
         assert torch.all(y0 == 2.5 * i) and torch.all(y1 == 0.5 * i)
     seen = StreamedInference(model, dev(), depth=3).run(batches, consume=lambda i, outs: (i, float(outs[0][0, 0])))
     assert seen == [(i, 2.5 * i) for i in range(5)]
+
+
+def test_graphed_inference_matches_eager_and_replays():
+    """pipeline.GraphedInference: the SETP1+SETP2 EXPORT forward captured in a CUDA graph gives bit-identical outputs to the
+    eager call, for the captured inputs and for new inputs of the same shape."""
+    from models.step2 import SETP2_BP_EXPORT
+    from nconv_b200.pipeline import GraphedInference
+    from nconv_b200.synthetic import synthetic_state_dict
+    m = SETP2_BP_EXPORT()
+    m.load_state_dict(synthetic_state_dict(5), strict=False)
+    m = m.eval().to(dev())
+    a = [t.to(dev()) for t in setp2_inputs(2, seed=4, H=128, W=256)]
+    b = [t.to(dev()) for t in setp2_inputs(2, seed=9, H=128, W=256)]
+    with torch.no_grad():
+        ea = [o.clone() for o in m(*a)]
+        eb = [o.clone() for o in m(*b)]
+    g = GraphedInference(m, a)
+    for inp, ref in ((a, ea), (b, eb), (a, ea)):
+        out = g(*inp)
+        torch.cuda.synchronize()
+        assert torch.equal(out[0], ref[0]) and torch.equal(out[1], ref[1])
