@@ -283,6 +283,8 @@ def nconv2d_sweep(dev, peaks, iters=5):
     B = 16
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     rows = []
+    sm_max_mhz = float(peaks.get("sm_max_mhz") or 1965.0)
+    fma_peak = 148 * 128 * 2 * sm_max_mhz / 1e6          # TFLOP/s: 148 SMs x 128 fp32 lanes x 2 at the maximum SM clock (nominal)
 
     def timed(fn):
         fn(); fn()
@@ -311,16 +313,24 @@ def nconv2d_sweep(dev, peaks, iters=5):
         bytes_f = 4.0 * B * (2 * ci + 2 * co) * H * W
         bytes_b = 4.0 * B * (4 * co + 4 * ci) * H * W
         flops_f = 4.0 * ci * co * k * k * B * H * W
+        # the bounding roofline of a layer is max(t_HBM, t_FMA) -- these kernels are fp32 CUDA-core code, and
+        # above Ci*Co = 4 the FMA pipe, not HBM, is the longer of the two (algorithmic flops: fwd 4*Ci*Co*k*k, bwd 8*...)
+        t_hbm_f, t_fma_f = bytes_f / peaks["hbm_gbs"] / 1e6, flops_f / fma_peak / 1e9
+        t_hbm_b, t_fma_b = bytes_b / peaks["hbm_gbs"] / 1e6, 2 * flops_f / fma_peak / 1e9
         rows.append({"shape": "%d->%d k%d" % (ci, co, k), "fwd_ms": round(ms_f, 4), "fwd_gbs": round(bytes_f / ms_f / 1e6, 1),
                      "fwd_hbm_frac": round(bytes_f / ms_f / 1e6 / peaks["hbm_gbs"], 4), "fwd_tflops": round(flops_f / ms_f / 1e9, 2),
+                     "fwd_bound": "fma" if t_fma_f > t_hbm_f else "hbm", "fwd_frac_of_bound": round(max(t_hbm_f, t_fma_f) / ms_f, 4),
                      "bwd_ms": round(ms_b, 4), "bwd_gbs": round(bytes_b / ms_b / 1e6, 1),
                      "bwd_hbm_frac": round(bytes_b / ms_b / 1e6 / peaks["hbm_gbs"], 4),
-                     "bwd_tflops": round(2 * flops_f / ms_b / 1e9, 2)})
+                     "bwd_tflops": round(2 * flops_f / ms_b / 1e9, 2),
+                     "bwd_bound": "fma" if t_fma_b > t_hbm_b else "hbm", "bwd_frac_of_bound": round(max(t_hbm_b, t_fma_b) / ms_b, 4)})
         del x, c, gy, gc, y, co_
     del flush
     return {"workload": "BASELINE config 2: single NConv2d layer, batch 16 at 480x640, fwd and bwd timed separately",
             "protocol": "clean cold L2 (256 MB write + read-back) before every timed launch, median of %d" % iters,
-            "hbm_peak_gbs": peaks["hbm_gbs"], "rows": rows}
+            "hbm_peak_gbs": peaks["hbm_gbs"], "fma_peak_tflops_nominal": round(fma_peak, 1),
+            "bound": "per row: the longer of t_HBM (algorithmic bytes / measured copy bandwidth) and t_FMA (algorithmic flops / "
+                     "nominal fp32 CUDA-core peak at the maximum clock); frac_of_bound = that time / measured time", "rows": rows}
 
 
 def setp1_kitti(dev, rank, world, steps, barrier, max_over_ranks):
