@@ -24,6 +24,7 @@ the analytic forward+backward kernels of csrc/conv_train.cu (`ops.conv_train`, `
 from __future__ import annotations
 
 import math
+import os
 import threading
 from collections import OrderedDict
 
@@ -154,6 +155,8 @@ def _setp2_trunk(m, rgb0, depth0, rgb1, depth1):
 def _tc_eligible(m, rgb) -> bool:
     if _ops.exporting():
         return False          # graph capture records the op-level path (decomposable; P8 workspaces are runtime state)
+    if getattr(m, "fp32_trunk", False) or os.environ.get("NCONV_B200_FP32_TRUNK"):
+        return False          # opt-out: fp32 CUDA-core kernels end to end (5-8x closer to the reference, ~4x slower)
     if torch.is_grad_enabled() and (rgb.requires_grad or any(p.requires_grad for p in m.parameters())):
         return False
     if any(bn.training for bn in _stack_bns(m)):

@@ -51,7 +51,7 @@ def sparse_depth_nyu(B: int, seed: int = 0, H: int = 480, W: int = 640, points: 
     S = torch.zeros(B, 1, H, W)
     for b in range(B):
         idx = torch.randperm(H * W, generator=g)[:points]
-        S[b].view(-1)[idx] = torch.rand(points, generator=g) * 9 + 1
+        S[b].view(-1)[idx] = torch.rand(points, generator=g)[:idx.numel()] * 9 + 1    # a frame of fewer than `points` pixels: all valid
     return S
 
 

@@ -463,6 +463,49 @@ def test_setp2_bench_batch_parity():
     assert res["max_abs_over_max_ref"] <= 1e-5, res
 
 
+@pytest.mark.parametrize("cfg", [(2, 104, 96), (3, 96, 40), (1, 16, 24), (1, 352, 1216), (2, 200, 136)])
+def test_setp2_export_other_shapes_vs_oracle(cfg):
+    """The EXPORT graph at sizes other than the golden's 480x640 (tile geometry, halo handling and the border zeroing
+    of step2.py:122-124 all depend on H, W): KITTI 352x1216, a frame smaller than one tile row, ragged tile counts,
+    a 16x24 frame the zeroed border covers entirely (row 45 of a 96-row frame is the first non-zero one).
+    Both routes -- the fused P8 / tcgen05 trunk (no_grad) and the op-level path (grad mode on an eval model, what a
+    frozen-BatchNorm fine-tune runs) -- against the CPU oracle on the same weights and inputs."""
+    import bench
+    B, H, W = cfg
+    m = bench.build_model(dev())
+    host = setp2_inputs(B, seed=11, H=H, W=W)
+    sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
+    torch.set_num_threads(os.cpu_count() or 1)
+    with torch.no_grad():
+        ref = O.setp2_forward(sd, *host, export=True)
+    ins = [t.to(dev()) for t in host]
+    with torch.no_grad():
+        a0, a1 = m(*ins)
+    fused = torch.cat((a0, a1), 0).cpu()
+    b0, b1 = m(*ins)                       # autograd on: op-level path
+    oplevel = torch.cat((b0, b1), 0).detach().cpu()
+    m.fp32_trunk = True                    # the documented opt-out takes the same kernels under no_grad
+    with torch.no_grad():
+        c0, c1 = m(*ins)
+    m.fp32_trunk = False
+    assert torch.equal(torch.cat((c0, c1), 0).cpu(), oplevel)
+    assert fused.shape == ref.shape == oplevel.shape
+    scale = float(ref.abs().max())
+    for name, out in (("fused", fused), ("oplevel", oplevel)):
+        report("setp2_export_%dx%dx%d_%s" % (B, H, W, name), max_rel_floor0p1=O.max_rel_err(out, ref, floor=SETP2_FLOOR),
+               max_abs_over_max_ref=float((out - ref).abs().max()) / max(scale, 1e-30))
+        if scale > 0:
+            # The bound that holds whatever the input is the scale-relative one: |a-b| <= 1e-5 * max|ref| (the split-bf16
+            # trunk carries 16-17 mantissa bits per stored activation through ~25 layers: measured 1e-6 .. 5e-6).  The
+            # max-rel figure at the 0.1 m floor depends on how close to zero the refined depth of THIS input comes: 1e-4
+            # on the reference golden (test above), up to 1.3e-4 here (KITTI shape); held to 2e-4 for the fused trunk and
+            # to 1e-4 for the fp32 op-level path.
+            assert float((out - ref).abs().max()) / scale <= 1e-5, (name, cfg)
+            assert O.max_rel_err(out, ref, floor=SETP2_FLOOR) <= (2 * REL_TOL if name == "fused" else REL_TOL), (name, cfg)
+        # the zeroed border is exact, whatever it covers at this size
+        assert bool((out[:, :, :45] == 0).all()) and bool((out[:, :, -45:] == 0).all()) and bool((out[..., :20] == 0).all()), (name, cfg)
+
+
 def _rel(a, ref):
     ref = ref.detach().double()
     return float((a.detach().double().cpu() - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
