@@ -235,7 +235,10 @@ def roofline_of(row, peaks, sustained=True):
             # produce 3 taps x 32 channels x 254 pixels (a quarter of the stacked rows is zero, lo*lo rides along)
             mma_factor = (128.0 * 256.0) / (32.0 * 254.0)
         out.update({"tflops": row["tflops"], "frac_tensor_algorithmic": row["tflops"] / tf_peak, "t_tensor_ms": 1e3 * t_tc,
-                    "mma_factor": mma_factor, "frac_tensor_issued": mma_factor * row["tflops"] / tf_peak})
+                    "mma_factor": mma_factor, "frac_tensor_issued": mma_factor * row["tflops"] / tf_peak,
+                    # the split-precision cost alone (3 bf16 MMAs per algorithmic product, no padding counted): the tensor
+                    # time the fp32-level parity bound forces, and the achieved fraction of max(that, HBM time)
+                    "t_tensor_bf16x3_ms": 3e3 * t_tc, "frac_of_max_hbm_bf16x3": max(t_hbm, 3.0 * t_tc) / (row["avg_ms"] * 1e-3)})
     if t_hbm >= t_tc:
         out.update({"bound": "hbm", "achieved": row["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": frac_hbm})
         if not tc and row["bytes"] > 0 and row["flops"] / row["bytes"] > 11.0:

@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
       tc_fence_after();
       const uint32_t st16 = (ring + stage * stage_bytes) >> 4;
       for (int t = 0; t < tmv; ++t) {
-        if ((int)(it % (uint32_t)a.issuers) == issuer) {
+        if ((int)(it & (uint32_t)(a.issuers - 1)) == issuer) {       // issuers is 1 or 2
           nt_wait(smem_u32(&t_empty[slot]), sphase ^ 1, 4, it);
           tc_fence_after();
           if (!(a.dbg & 4))
@@ -429,13 +429,16 @@ __global__ void __launch_bounds__(NT_THREADS, 1) nconv_tc_kernel(const __grid_co
     const N8Geom gu = N8Geom::make(a.B, 2 * a.H, 2 * a.W);
     const float b7 = a.b_tail ? __ldg(a.b_tail) : 0.f;
     uint32_t it = 0;
+    int erot = 0;
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
       const int tx = tile % a.tiles_x, ty = (tile / a.tiles_x) % a.tiles_y, n = tile / (a.tiles_x * a.tiles_y);
       const int y0 = ty * rows_tile, x0 = tx * C::WT;
       const int rows_left = a.H - y0;
       const int tmv = rows_left >= rows_tile ? a.TM : (rows_left + 3) / 4;
       for (int t = 0; t < tmv; ++t, ++it) {
-        if ((int)(it % (uint32_t)a.esets) != set) continue;
+        const bool mine = (erot == set);                         // it % esets == set, without the integer division
+        if (++erot == a.esets) erot = 0;
+        if (!mine) continue;
         const uint32_t slot = it % C::NSLOT, sphase = (it / C::NSLOT) & 1;
         nt_wait(smem_u32(&t_full[slot]), sphase, 5, it);
         tc_fence_after();

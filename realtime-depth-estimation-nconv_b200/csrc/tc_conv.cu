@@ -109,6 +109,7 @@ struct TcArgs {
   __nv_bfloat16* outq;          // optional P8Q copy of the output
   int B, AH, AW, OH, OW;        // anchor grid and output size
   int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, ntaps, ntaps_w;
+  uint32_t P_magic;             // ceil(2^32 / P): m / P == __umulhi(m, P_magic) for m * P < 2^32 (no integer division in the epilogue)
   int tiles_x, tiles_y, ntiles;
   int relu, mode, stages;
   int dbg;                      // NCONV_B200_TC_DEBUG bits (timing experiments only): 1 no stores, 2 no MMAs, 4 no loads
@@ -285,7 +286,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       tc_fence_after();
       for (int t = 0; t < a.T; ++t) {
         const int m = t * 128 + q * 32 + lane;                 // flat staged position of this thread's anchor
-        const int r = m / a.P, c = m - r * a.P;
+        const int r = (int)__umulhi((uint32_t)m, a.P_magic), c = m - r * a.P;
         const int ay = ty * a.R + r, ax = tx * a.Wt + c;
         const bool valid = (r < a.R) && (c < a.Wt) && (ay < a.AH) && (ax < a.AW);
         for (int ph = 0; ph < nphase; ++ph) {
@@ -609,6 +610,7 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   a.B = d->B; a.AH = AH; a.AW = AW;
   a.OH = (mode == TC_T) ? 2 * d->H : AH; a.OW = (mode == TC_T) ? 2 * d->W : AW;
   a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.T = p.T; a.rows_alloc = p.rows_alloc; a.rows_ld = p.rows_ld;
+  a.P_magic = (uint32_t)(((1ull << 32) + (uint64_t)p.P - 1) / (uint64_t)p.P);
   a.G = p.G; a.ngrp = ngrp; a.ntaps_w = ntw;
   a.tiles_x = p.tiles_x; a.tiles_y = p.tiles_y; a.ntiles = p.tiles_x * p.tiles_y * d->B;
   a.relu = d->relu; a.mode = mode; a.stages = p.stages;

@@ -14,6 +14,8 @@ Differences from the reference, all conscious:
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -94,7 +96,8 @@ class DNET(nn.Module):
                 params += [l.weight, l.bias]
             # inference (no_grad) takes the tensor-core pipeline where the shape allows; a frozen step 1 inside a
             # recording (training) step stays on the fp32 CUDA-core pipeline
-            return _K.dnet_forward(S, params, torch.is_grad_enabled())
+            fp32 = torch.is_grad_enabled() or bool(getattr(self, "fp32_only", False)) or bool(os.environ.get("NCONV_B200_FP32_TRUNK"))
+            return _K.dnet_forward(S, params, fp32)
 
         # Staged graph (training): every stage is a custom op with an analytic backward.
         c0 = _K.confidence_mask(S, 0.01)

@@ -130,6 +130,7 @@ class SETP2_BP_EXPORT(nn.Module):
 def _setp2_trunk(m, rgb0, depth0, rgb1, depth1):
     """Shared body of step2.py:60-75 / :105-120."""
     B = rgb0.shape[0]
+    m.step1.d_net.fp32_only = bool(getattr(m, "fp32_trunk", False))      # the opt-out covers step 1's tensor-core pipeline too
     sparse = m.step1(depth0, depth1)
     rgb = torch.cat((rgb0, rgb1), dim=0)
     if _tc_eligible(m, rgb):

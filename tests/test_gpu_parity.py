@@ -484,14 +484,14 @@ def test_setp2_export_other_shapes_vs_oracle(cfg):
     fused = torch.cat((a0, a1), 0).cpu()
     b0, b1 = m(*ins)                       # autograd on: op-level path
     oplevel = torch.cat((b0, b1), 0).detach().cpu()
-    m.fp32_trunk = True                    # the documented opt-out takes the same kernels under no_grad
+    m.fp32_trunk = True                    # the documented opt-out: fp32 CUDA-core kernels under no_grad, step 1 included
     with torch.no_grad():
         c0, c1 = m(*ins)
     m.fp32_trunk = False
-    assert torch.equal(torch.cat((c0, c1), 0).cpu(), oplevel)
+    fp32 = torch.cat((c0, c1), 0).cpu()
     assert fused.shape == ref.shape == oplevel.shape
     scale = float(ref.abs().max())
-    for name, out in (("fused", fused), ("oplevel", oplevel)):
+    for name, out in (("fused", fused), ("oplevel", oplevel), ("fp32_trunk", fp32)):
         report("setp2_export_%dx%dx%d_%s" % (B, H, W, name), max_rel_floor0p1=O.max_rel_err(out, ref, floor=SETP2_FLOOR),
                max_abs_over_max_ref=float((out - ref).abs().max()) / max(scale, 1e-30))
         if scale > 0:
