@@ -15,7 +15,7 @@
 // fp32-class results (parity bound 1e-4, measured in tests/test_gpu_parity.py) at 1/3 of the bf16
 // tensor rate.
 //
-// Structure (one persistent CTA per SM, 192 threads, warp-specialised):
+// Structure (one persistent CTA per SM, 352 threads, warp-specialised):
 //   warp 0     producer: per K-stage (16 input channels) bulk-copies (cp.async.bulk on the TMA
 //              engine, mbarrier complete_tx) the halo rows of the staged planes and the stage's
 //              packed weights into a 2-deep shared-memory ring
@@ -25,9 +25,11 @@
 //              K-major no-swizzle A tile and a tap is "descriptor start address + shift*16 B"
 //              (implicit im2col; for S2 the shift is taken inside one of the four phase planes).
 //              Halo columns yield garbage rows that the epilogue drops (2/P of the MMA rows).
-//   warps 2-5  epilogue: tcgen05.ld the fp32 accumulators (double-buffered in TMEM so the next
-//              tile's MMAs overlap), scale/shift/ReLU (+ residual accumulator), split to hi/lo
-//              bf16, 16-byte stores into the P8 output (and its P8Q copy for a stride-2 consumer).
+//   warps 2-5, 7-10  epilogue, one (Co = 64) or two (Co = 32) sets of four warps (one per TMEM lane quarter): tcgen05.ld the fp32
+//              accumulators (double-buffered in TMEM so the next tile's MMAs overlap), scale/shift/ReLU
+//              (+ residual accumulator), split to hi/lo bf16, 16-byte stores into the P8 output (and its
+//              P8Q copy for a stride-2 consumer).  The (M-tile, phase, 32-channel block) work items of a
+//              buffer alternate between the sets (TcEsets below).
 #include "common.cuh"
 #include "launch_count.h"
 #include "nconv_b200.h"
@@ -41,7 +43,11 @@
 
 namespace nconv {
 
-constexpr int TC_THREADS = 224;      // warp 0, 6: producers; warp 1: MMA issuer; warps 2-5: epilogue
+constexpr int TC_THREADS = 352;      // warp 0, 6: producers; warp 1: MMA issuer; warps 2-5 and (Co = 32) 7-10: the epilogue sets
+// Epilogue sets per output width.  Measured A/B in one process (bench, B = 32): a second set makes the Co = 32 kernels
+// 6 % faster (32->32 @480x640 0.748 -> 0.700 ms, transposed 48->32 -2 %); with Co = 64 the MMAs are the longer side and the
+// extra warps only cost (+1 %, stride-2 +3 %), so those launch without them.
+template <int N> struct TcEsets { static constexpr int value = (N == 32) ? 2 : 1; };
 constexpr int TC_MAX_STAGES = 3;
 constexpr int TC_SMEM_MAX = 227 * 1024 - 1024;   // dynamic part; static barriers etc. take the rest
 constexpr int TC_MAX_TAPS = 17;
@@ -112,7 +118,7 @@ struct TcArgs {
   uint32_t P_magic;             // ceil(2^32 / P): m / P == __umulhi(m, P_magic) for m * P < 2^32 (no integer division in the epilogue)
   int tiles_x, tiles_y, ntiles;
   int relu, mode, stages;
-  int dbg;                      // NCONV_B200_TC_DEBUG bits (timing experiments only): 1 no stores, 2 no MMAs, 4 no loads
+  int dbg;                      // NCONV_B200_TC_DEBUG bits (timing experiments only): 1 no stores, 2 no MMAs, 4 no loads, 64 one epilogue set
   int use_tmap;                 // halo planes by TMA tensor copies (one box per staged plane) instead of per-row bulk copies
   TcTap taps[TC_MAX_TAPS];
 };
@@ -147,7 +153,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   }
   if (threadIdx.x == 0) {
     for (int s = 0; s < TC_MAX_STAGES; ++s) { mbar_init(smem_u32(&s_full[s]), 1); mbar_init(smem_u32(&s_empty[s]), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(smem_u32(&s_tfull[b]), 1); mbar_init(smem_u32(&s_tempty[b]), 4 * TcEsets<N>::value); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -273,8 +279,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2..5 = set 0, 7..10 = set 1) =====================
     const int q = warp & 3;                                    // TMEM lane quarter this warp may access
+    const int eset = warp >= 7 ? 1 : 0;
+    const int esplit = (TcEsets<N>::value == 1 || (a.dbg & 64)) ? 0 : 1;   // 0: everything goes to set 0
     uint32_t it = 0;
     const size_t oplane = (size_t)(a.OH + 2) * (a.OW + 2) * 8;
     const P8QGeom qg = P8QGeom::make(a.B, N, a.OH, a.OW);
@@ -290,12 +298,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         const int ay = ty * a.R + r, ax = tx * a.Wt + c;
         const bool valid = (r < a.R) && (c < a.Wt) && (ay < a.AH) && (ax < a.AW);
         for (int ph = 0; ph < nphase; ++ph) {
+          if ((N / 32) % 2 == 1 && ((((t * nphase + ph) & 1) & esplit) != eset)) continue;   // odd block count: whole (t, ph) items alternate
           const int oy = (MODE == TC_T) ? 2 * ay + (ph >> 1) : ay;
           const int ox = (MODE == TC_T) ? 2 * ax + (ph & 1) : ax;
           __nv_bfloat16* obase = a.out + ((size_t)n * (N / 8) * 2) * oplane + ((size_t)(oy + 1) * (a.OW + 2) + (ox + 1)) * 8;
           const uint32_t tcol = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256;
 #pragma unroll
           for (int cb = 0; cb < N / 32; ++cb) {
+            if ((N / 32) % 2 == 0 && (((cb & 1) & esplit) != eset)) continue;           // even block count: the blocks alternate
             uint32_t v[32], w[32];
             tmem_ld32(tcol + (ph * a.T + t) * NACC + cb * 32, v);
             if (MODE == TC_S2 && a.ngrp == 2) tmem_ld32(tcol + (a.T + t) * NACC + cb * 32, w);   // S2 residual branch
@@ -467,7 +477,7 @@ static int launch_tc(const TcArgs& a, const TcPlan& p, cudaStream_t st) {
   {
     // algorithmic bytes: fp32-equivalent activations in and out (P8 holds the same 4 B per value)
     LaunchScope ls(st, label, 2.0 * CI * N * taps_per_out * opx, 4.0 * (CI * ipx + N * opx * (a.outq ? 2.0 : 1.0)));
-    kern<<<grid, TC_THREADS, p.smem, st>>>(a, tm[0], tm[1]);
+    kern<<<grid, 224 + 128 * (TcEsets<N>::value - 1), p.smem, st>>>(a, tm[0], tm[1]);
   }
   return (int)cudaGetLastError();
 }
