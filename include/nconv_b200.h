@@ -282,7 +282,15 @@ int nconv_b200_bn_fold(const float* gamma, const float* beta, const float* mean,
 size_t nconv_b200_p8_bytes(int B, int C, int H, int W);
 int nconv_b200_p8_pack(const float* x, void* p8, int B, int C, int H, int W, void* stream);
 int nconv_b200_p8_unpack(const void* p8, float* x, int B, int C, int H, int W, void* stream);
+/* unpack into channels [c0, c0+C) of a contiguous fp32 [B, Ctot, H, W] tensor (the data gradient of a wide layer is computed
+ * in blocks of 64 input channels: no concatenation pass afterwards) */
+int nconv_b200_p8_unpack_into(const void* p8, float* x, int B, int C, int H, int W, int Ctot, int c0, void* stream);
 int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream);
+/* Backward of ReLU(conv + bias) (step2.py:290-297 under train_step2.py:62-64) written straight into P8 for the tcgen05
+ * data / weight gradient kernels: p8 = P8(gy * [y > 0]) (y null: no mask), gbias[c] = per-channel sum of the masked
+ * gradient (null: not wanted).  ws: C doubles of scratch when gbias is given.  gy, y: fp32 NCHW [B,C,H,W]. */
+int nconv_b200_relu_bias_bwd_p8(const float* gy, const float* y, void* p8, float* gbias, void* ws, int B, int C, int H,
+                                int W, void* stream);
 
 /* P8Q: the four spatial phases of an activation, for stride-2 consumers (csrc/p8.cuh). */
 size_t nconv_b200_p8q_bytes(int B, int C, int H, int W);

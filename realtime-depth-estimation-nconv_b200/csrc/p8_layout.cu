@@ -7,39 +7,78 @@
 
 namespace nconv {
 
-__global__ void p8_pack_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ p8, int B, int C, int H, int W) {
+// fp32 NCHW -> P8.  One thread = one ring-padded pixel x the 8 channels of a chunk; grid (columns / 128, row groups, B * C8)
+// so no index needs a division.  Optional fusions for the training backward (ops.py::_ConvTrain.backward):
+//   mask  g = x * [mask > 0]      (ReLU backward: x is the output gradient, mask the saved activation)
+//   acc   acc[c] += sum over pixels of the packed value (bias gradient), fp32 partials per CTA, fp64 atomics.
+constexpr int PK_THREADS = 128, PK_ROWS = 8;
+
+template <bool MASK>
+__global__ void __launch_bounds__(PK_THREADS) p8_pack_kernel(const float* __restrict__ x, const float* __restrict__ mask,
+                                                             __nv_bfloat16* __restrict__ p8, double* __restrict__ acc,
+                                                             int B, int C, int H, int W) {
   const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * g.Hp * g.Wp;
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    int xx = (int)(idx % g.Wp);
-    size_t r = idx / g.Wp;
-    int yy = (int)(r % g.Hp); r /= g.Hp;
-    int ch = (int)(r % g.C8);
-    int n = (int)(r / g.C8);
-    float f[8];
-    const bool inside = yy >= 1 && yy <= H && xx >= 1 && xx <= W;
+  const int xx = blockIdx.x * PK_THREADS + threadIdx.x;          // padded column
+  const int ch = blockIdx.z % g.C8, n = blockIdx.z / g.C8;
+  const int y0 = blockIdx.y * PK_ROWS;
+  float sum[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) sum[e] = 0.f;
+  if (xx < g.Wp) {
+#pragma unroll 2
+    for (int yy = y0; yy < y0 + PK_ROWS && yy < g.Hp; ++yy) {
+      float f[8], m[8];
+      const bool inside = yy >= 1 && yy <= H && xx >= 1 && xx <= W;
+      // all loads of the pixel first (independent, issued back to back), then the mask
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int c = ch * 8 + e;
+        const bool ok = inside && c < C;
+        const size_t i = ok ? (((size_t)n * C + c) * H + (yy - 1)) * W + (xx - 1) : 0;
+        f[e] = ok ? __ldg(x + i) : 0.f;
+        m[e] = (MASK && ok) ? __ldg(mask + i) : 1.f;
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        if (MASK && !(m[e] > 0.f)) f[e] = 0.f;
+        sum[e] += f[e];
+      }
+      uint4 hi, lo;
+      split8_fast(f, hi, lo);
+      const size_t off = ((size_t)yy * g.Wp + xx) * 8;
+      *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 0) + off) = hi;
+      *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 1) + off) = lo;
+    }
+  }
+  if (acc) {
+    __shared__ float sh[PK_THREADS / 32][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int c = ch * 8 + e;
-      f[e] = (inside && c < C) ? __ldg(x + (((size_t)n * C + c) * H + (yy - 1)) * W + (xx - 1)) : 0.f;
+      float v = sum[e];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+      if (lane == 0) sh[warp][e] = v;
     }
-    uint4 hi, lo;
-    split8(f, hi, lo);
-    const size_t off = ((size_t)yy * g.Wp + xx) * 8;
-    *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 0) + off) = hi;
-    *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 1) + off) = lo;
+    __syncthreads();
+    if (threadIdx.x < 8 && ch * 8 + threadIdx.x < C) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < PK_THREADS / 32; ++w) t += (double)sh[w][threadIdx.x];
+      atomicAdd(acc + ch * 8 + threadIdx.x, t);
+    }
   }
 }
 
-__global__ void p8_unpack_kernel(const __nv_bfloat16* __restrict__ p8, float* __restrict__ x, int B, int C, int H, int W) {
+// P8 -> fp32 NCHW; the C channels land at channel offset c0 of a [B, Ctot, H, W] tensor (Ctot = C, c0 = 0: a plain unpack)
+__global__ void __launch_bounds__(PK_THREADS) p8_unpack_kernel(const __nv_bfloat16* __restrict__ p8, float* __restrict__ x, int B, int C,
+                                                               int H, int W, int Ctot, int c0) {
   const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * H * W;
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    int xx = (int)(idx % W);
-    size_t r = idx / W;
-    int yy = (int)(r % H); r /= H;
-    int ch = (int)(r % g.C8);
-    int n = (int)(r / g.C8);
+  const int xx = blockIdx.x * PK_THREADS + threadIdx.x;          // interior column
+  const int ch = blockIdx.z % g.C8, n = blockIdx.z / g.C8;
+  if (xx >= W) return;
+  const int y0 = blockIdx.y * PK_ROWS;
+  for (int yy = y0; yy < y0 + PK_ROWS && yy < H; ++yy) {
     const size_t off = g.pixel(yy, xx);
     const uint4 hi = *reinterpret_cast<const uint4*>(p8 + g.plane(n, ch, 0) + off);
     const uint4 lo = *reinterpret_cast<const uint4*>(p8 + g.plane(n, ch, 1) + off);
@@ -48,7 +87,7 @@ __global__ void p8_unpack_kernel(const __nv_bfloat16* __restrict__ p8, float* __
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int c = ch * 8 + e;
-      if (c < C) x[(((size_t)n * C + c) * H + yy) * W + xx] = f[e];
+      if (c < C) x[(((size_t)n * Ctot + c0 + c) * H + yy) * W + xx] = f[e];
     }
   }
 }
@@ -78,28 +117,61 @@ extern "C" size_t nconv_b200_p8_bytes(int B, int C, int H, int W) {
   return P8Geom::make(B, C, H, W).total_elems() * sizeof(__nv_bfloat16) + P8_TAIL_SLACK_BYTES;
 }
 
+static int p8_pack_launch(const float* x, const float* mask, void* p8, double* acc, int B, int C, int H, int W, const char* label,
+                          cudaStream_t st) {
+  const P8Geom g = P8Geom::make(B, C, H, W);
+  if ((long long)B * g.C8 > 65535) return NCONV_ERR_UNSUPPORTED;
+  dim3 grid((g.Wp + PK_THREADS - 1) / PK_THREADS, (g.Hp + PK_ROWS - 1) / PK_ROWS, B * g.C8);
+  const double n = (double)B * C * H * W;
+  {
+    LaunchScope ls(st, label, 0.0, (mask ? 12.0 : 8.0) * n);
+    if (mask) p8_pack_kernel<true><<<grid, PK_THREADS, 0, st>>>(x, mask, (__nv_bfloat16*)p8, acc, B, C, H, W);
+    else p8_pack_kernel<false><<<grid, PK_THREADS, 0, st>>>(x, mask, (__nv_bfloat16*)p8, acc, B, C, H, W);
+  }
+  return (int)cudaGetLastError();
+}
+
 extern "C" int nconv_b200_p8_pack(const float* x, void* p8, int B, int C, int H, int W, void* stream) {
   if (!x || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  return p8_pack_launch(x, nullptr, p8, nullptr, B, C, H, W, "p8_pack", (cudaStream_t)stream);
+}
+
+namespace nconv { __global__ void p8_sums_out_kernel(const double* __restrict__ a, float* __restrict__ o, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) o[i] = (float)a[i];
+} }
+
+// ReLU(conv + bias) backward straight into the tensor-core layout: p8 = P8(gy * [y > 0]) (y null: no mask), gbias[c] = the
+// per-channel sum of the masked gradient (null: not wanted).  ws: C doubles of scratch.  Replaces relu_bias_bwd + p8_pack
+// where both consumers of the masked gradient (data and weight gradient) run on tcgen05 (train_step2.py:62-64).
+extern "C" int nconv_b200_relu_bias_bwd_p8(const float* gy, const float* y, void* p8, float* gbias, void* ws, int B, int C, int H,
+                                           int W, void* stream) {
+  if (!gy || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0 || (gbias && !ws)) return NCONV_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (gbias) NCONV_RETURN_IF_ERR(cudaMemsetAsync(ws, 0, sizeof(double) * C, st));
+  const int rc = p8_pack_launch(gy, y, p8, gbias ? (double*)ws : nullptr, B, C, H, W, "relu_bias_bwd_p8", st);
+  if (rc) return rc;
+  if (gbias) {
+    LaunchScope ls(st, "channel_sum_out", 0.0, 0.0);
+    p8_sums_out_kernel<<<(C + 127) / 128, 128, 0, st>>>((const double*)ws, gbias, C);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_p8_unpack_into(const void* p8, float* x, int B, int C, int H, int W, int Ctot, int c0, void* stream) {
+  if (!x || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0 || c0 < 0 || c0 + C > Ctot) return NCONV_ERR_BAD_ARG;
   const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * g.Hp * g.Wp;
-  int blocks = (int)((total + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
+  if ((long long)B * g.C8 > 65535) return NCONV_ERR_UNSUPPORTED;
+  dim3 grid((W + PK_THREADS - 1) / PK_THREADS, (H + PK_ROWS - 1) / PK_ROWS, B * g.C8);
   {
-    LaunchScope ls((cudaStream_t)stream, "p8_pack", 0.0, 8.0 * B * C * H * W);
-    p8_pack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)p8, B, C, H, W);
+    LaunchScope ls((cudaStream_t)stream, "p8_unpack", 0.0, 8.0 * B * C * H * W);
+    p8_unpack_kernel<<<grid, PK_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)p8, x, B, C, H, W, Ctot, c0);
   }
   return (int)cudaGetLastError();
 }
 
 extern "C" int nconv_b200_p8_unpack(const void* p8, float* x, int B, int C, int H, int W, void* stream) {
-  if (!x || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
-  const P8Geom g = P8Geom::make(B, C, H, W);
-  const size_t total = (size_t)B * g.C8 * H * W;
-  int blocks = (int)((total + 255) / 256); if (blocks > 148 * 16) blocks = 148 * 16;
-  {
-    LaunchScope ls((cudaStream_t)stream, "p8_unpack", 0.0, 8.0 * B * C * H * W);
-    p8_unpack_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)p8, x, B, C, H, W);
-  }
-  return (int)cudaGetLastError();
+  return nconv_b200_p8_unpack_into(p8, x, B, C, H, W, C, 0, stream);
 }
 
 extern "C" int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream) {

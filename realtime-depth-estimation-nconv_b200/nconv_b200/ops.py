@@ -506,6 +506,15 @@ class P8:
                 check(_C.nconv_b200_p8q_pack(_p(x), _p(t.qbuf), B, C, H, W, _stream(x)), "p8q_pack")
         return t
 
+    def unpack_into(self, x, c0: int):
+        """Write the C channels at channel offset c0 of the contiguous fp32 tensor x [B, Ctot, H, W]."""
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.shape[0] != self.B or tuple(x.shape[2:]) != (self.H, self.W):
+            raise ValueError("unpack_into: x must be contiguous fp32 [B, Ctot, H, W] of this tensor's B, H, W")
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_p8_unpack_into(_p(self.buf), _p(x), self.B, self.C, self.H, self.W, int(x.shape[1]), int(c0),
+                                               _stream(x)), "p8_unpack_into")
+        return x
+
     def unpack(self):
         x = torch.empty((self.B, self.C, self.H, self.W), device=self.buf.device, dtype=torch.float32)
         with torch.cuda.device(x.device):
@@ -763,6 +772,18 @@ def _relu_bias_bwd(gy, y, relu: bool, want_g: bool, want_bias: bool):
     return g, gb
 
 
+def _relu_bias_bwd_p8(gy, y, want_bias: bool):
+    """P8(gy * [y > 0]) (y None: no mask) and the per-channel sum of it, one pass (csrc/p8_layout.cu)."""
+    B, C, H, W = gy.shape
+    out = P8.empty(B, C, H, W, gy.device, zero_ring=False)           # the kernel writes ring and padding channels itself
+    gb = torch.empty(C, device=gy.device, dtype=torch.float32) if want_bias else None
+    ws = _scratch(gy.device, int(_C.nconv_b200_train_ws_bytes(C))) if want_bias else None
+    with torch.cuda.device(gy.device):
+        check(_C.nconv_b200_relu_bias_bwd_p8(_p(gy), _p(y), _p(out.buf), _p(gb), _p(ws), B, C, H, W, _stream(gy)),
+              "relu_bias_bwd_p8")
+    return out, gb
+
+
 def _conv_wgrad(g, x, K: int, S: int, P: int):
     """gw[CO][CI][K][K] for g [B,CO,HO,WO], x [B,CI,H,W]."""
     B, CI, H, W = x.shape
@@ -847,13 +868,21 @@ class _ConvTrain(torch.autograd.Function):
         gy = _prep(gy, "gy")
         CO, CI, K, _ = weight.shape
         g, gb = gy, None
-        if relu or (has_bias and need_b):
+        blk = 64 if CI % 64 == 0 else (32 if CI == 32 else 0)
+        tc_w = need_w and _tc_wgrad_ok(CI, CO, K, stride)
+        tc_x = need_x and stride == 1 and blk != 0 and _tc_train_ok(CO, blk, K, 1)
+        g8 = None
+        if (relu or (has_bias and need_b)) and (tc_w or not need_w) and (tc_x or not need_x) and (tc_w or tc_x):
+            # every consumer of the masked gradient runs on tcgen05: mask, bias sum and P8 split in one pass (no fp32 copy)
+            g8, gb = _relu_bias_bwd_p8(gy, y if relu else None, want_bias=has_bias and need_b)
+            g = None
+        elif relu or (has_bias and need_b):
             g2, gb = _relu_bias_bwd(gy, y, relu, want_g=relu, want_bias=has_bias and need_b)
             if relu:
                 g = g2
-        g8 = None
-        if need_w and _tc_wgrad_ok(CI, CO, K, stride):
-            g8 = P8.pack(g)
+        if tc_w:
+            if g8 is None:
+                g8 = P8.pack(g)
             gw = _conv_wgrad_tc(P8.pack(x), g8)
         else:
             gw = _conv_wgrad(g, x, K, stride, K // 2) if need_w else None
@@ -866,15 +895,13 @@ class _ConvTrain(torch.autograd.Function):
                     check(_C.nconv_b200_wflip(_p(weight), _p(wf), CO, CI, K, _stream(x)), "wflip")
                 # data gradient = the forward conv of g with the flipped / transposed weights [CI, CO, K, K]; on the tensor
                 # cores in blocks of 64 (or 32) "output" channels when the shapes allow
-                blk = 64 if CI % 64 == 0 else (32 if CI == 32 else 0)
-                if blk and _tc_train_ok(CO, blk, K, 1):
+                if tc_x:
                     if g8 is None:
                         g8 = P8.pack(g)
-                    parts = []
+                    gx = torch.empty_like(x)
                     for c0 in range(0, CI, blk):
                         wpk = tc_pack_weights(TC_S1, wf[c0:c0 + blk].contiguous(), CO, 0)
-                        parts.append(conv_tc(TC_S1, g8, None, wpk, blk, None, None, False).unpack())
-                    gx = parts[0] if len(parts) == 1 else torch.cat(parts, 1)
+                        conv_tc(TC_S1, g8, None, wpk, blk, None, None, False).unpack_into(gx, c0)
                 else:
                     gx = _conv_fwd_raw(g, wf, None, None, 1, False)
             else:

@@ -723,6 +723,32 @@ def test_setp2_train_step_vs_reference_golden(golden, tmp_path, monkeypatch):
 # ---------------------------------------------------------------------------------------------
 # tensor-core path: P8 layout round trip and the tcgen05 bf16x3 conv3x3 vs fp64 F.conv2d
 # ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(2, 5, 7, 9), (1, 32, 16, 24), (2, 64, 33, 300), (3, 12, 130, 131)])
+@pytest.mark.parametrize("relu", [True, False])
+def test_relu_bias_bwd_p8_and_unpack_into(shape, relu):
+    """The fused backward of ReLU(conv + bias) into the tensor-core layout (mask, per-channel sum, split in one pass)
+    against torch, and P8 -> a channel slice of a wider fp32 tensor."""
+    from nconv_b200 import ops
+    torch.manual_seed(4)
+    gy = torch.randn(*shape).to(dev())
+    y = torch.relu(torch.randn(*shape)).to(dev())
+    g8, gb = ops._relu_bias_bwd_p8(gy, y if relu else None, want_bias=True)
+    ref = gy * (y > 0) if relu else gy
+    assert O.max_rel_err(g8.unpack(), ref, floor=1e-6) <= 2.0 ** -16
+    assert float((gb.double() - ref.double().sum((0, 2, 3))).abs().max()) <= 1e-5 * float(ref.abs().sum((0, 2, 3)).max())
+    wide = torch.full((shape[0], shape[1] + 11, shape[2], shape[3]), 7.0, device=dev())
+    g8.unpack_into(wide, 5)
+    assert torch.equal(wide[:, 5:5 + shape[1]], g8.unpack())
+    assert bool((wide[:, :5] == 7).all()) and bool((wide[:, 5 + shape[1]:] == 7).all())
+    # ring and padding channels of the packed tensor are zero (the tcgen05 kernels read them as the conv's zero padding)
+    raw = g8.buf[:2 * shape[0] * ((shape[1] + 7) // 8) * 2 * (shape[2] + 2) * (shape[3] + 2) * 8].view(torch.bfloat16)
+    planes = raw.view(shape[0], (shape[1] + 7) // 8, 2, shape[2] + 2, shape[3] + 2, 8)
+    assert bool((planes[:, :, :, 0] == 0).all()) and bool((planes[:, :, :, -1] == 0).all())
+    assert bool((planes[:, :, :, :, 0] == 0).all()) and bool((planes[:, :, :, :, -1] == 0).all())
+    if shape[1] % 8:
+        assert bool((planes[:, -1, :, :, :, shape[1] % 8:] == 0).all())
+
+
 @pytest.mark.parametrize("shape", [(2, 5, 7, 9), (1, 32, 16, 24), (2, 64, 33, 70)])
 def test_p8_roundtrip(shape):
     from nconv_b200.ops import P8
