@@ -56,6 +56,8 @@ __global__ void __launch_bounds__(RED_THREADS) bn_stats_kernel(const float* __re
   const float pivot = __ldg(x + (size_t)c * HW);
   const float* p = x + ((size_t)b * C + c) * HW;
   double s1 = 0.0, s2 = 0.0;
+  // (scalar, strided order kept on purpose: the batch statistics feed the forward activations, and a training step of this
+  //  stack is chaotic at the 1e-3 level -- a different summation order here re-rolls every ReLU mask decision near zero)
   const int per = (HW + gridDim.x - 1) / gridDim.x;
   const int lo = blockIdx.x * per, hi = min(HW, lo + per);
   for (int i0 = lo + threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
@@ -99,17 +101,47 @@ __global__ void bn_finalize_kernel(const double* __restrict__ acc, const float* 
   }
 }
 
-// y = act(x * scale[c] + shift[c]) (+ residual); in place allowed (y == x).
+// y = act(x * scale[c] + shift[c]) (+ residual); in place allowed (y == x).  grid (chunks, C, B): a CTA streams one slice of
+// one (b, c) plane, so the channel constants are registers and there is no per-element index arithmetic; 128-bit
+// accesses when the plane size allows (VEC = 4).
+template <int VEC>
 __global__ void __launch_bounds__(256) affine_act_kernel(const float* __restrict__ x, const float* __restrict__ scale,
                                                          const float* __restrict__ shift, const float* __restrict__ residual,
-                                                         float* __restrict__ y, int C, int HW, long long total, int relu) {
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += 256ll * gridDim.x) {
-    const int c = (int)((i / HW) % C);
-    float v = fmaf(x[i], __ldg(scale + c), __ldg(shift + c));
-    if (relu) v = fmaxf(v, 0.f);
-    if (residual) v += __ldg(residual + i);
-    y[i] = v;
+                                                         float* __restrict__ y, int C, int HW, int per, int relu) {
+  const int c = blockIdx.y, b = blockIdx.z;
+  const float sc = __ldg(scale + c), sf = __ldg(shift + c);
+  const size_t base = ((size_t)b * C + c) * HW;
+  const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  for (int i = lo + VEC * threadIdx.x; i < hi; i += VEC * 256) {
+    float v[VEC], r[VEC];
+    if (VEC == 4) {
+      *reinterpret_cast<float4*>(v) = *reinterpret_cast<const float4*>(x + base + i);
+      if (residual) *reinterpret_cast<float4*>(r) = __ldg(reinterpret_cast<const float4*>(residual + base + i));
+    } else {
+      v[0] = x[base + i];
+      if (residual) r[0] = __ldg(residual + base + i);
+    }
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      v[k] = fmaf(v[k], sc, sf);
+      if (relu) v[k] = fmaxf(v[k], 0.f);
+      if (residual) v[k] += r[k];
+    }
+    if (VEC == 4) *reinterpret_cast<float4*>(y + base + i) = *reinterpret_cast<float4*>(v);
+    else y[base + i] = v[0];
   }
+}
+
+// slices per plane for the streaming (non-reducing) kernels: >= 4 CTAs per SM in flight, a slice a multiple of 4 elements
+static inline int stream_chunks(int HW, int C, int B, int* per) {
+  int want = (148 * 8 + C * B - 1) / (C * B);
+  const int maxc = (HW + 4095) / 4096;
+  if (want > maxc) want = maxc;
+  if (want < 1) want = 1;
+  int p = (HW + want - 1) / want;
+  p = (p + 3) / 4 * 4;
+  *per = p;
+  return (HW + p - 1) / p;
 }
 
 // ---- BatchNorm (+ReLU) backward ---------------------------------------------------------------------
@@ -124,8 +156,32 @@ __global__ void __launch_bounds__(RED_THREADS) bn_bwd_reduce_kernel(const float*
   const float sc = scale[c], sf = shift[c], mu = mean[c], rs = rstd[c];
   const size_t base = ((size_t)b * C + c) * HW;
   double s1 = 0.0, s2 = 0.0;
-  const int per = (HW + gridDim.x - 1) / gridDim.x;
+  const int per = ((HW + gridDim.x - 1) / gridDim.x + 3) & ~3;
   const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  if ((HW & 3) == 0) {
+    // 128-bit loads; fp32 partials over 8 iterations (32 values per thread), then into the fp64 sums
+    for (int i0 = lo + 4 * threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
+      float f1 = 0.f, f2 = 0.f;
+#pragma unroll 4
+      for (int k = 0; k < 8; ++k) {
+        const int i = i0 + k * RED_THREADS * 4;
+        if (i < hi) {
+          const float4 zv = __ldg(reinterpret_cast<const float4*>(z + base + i));
+          float4 g = __ldg(reinterpret_cast<const float4*>(gy + base + i));
+          if (relu) {
+            if (!(fmaf(zv.x, sc, sf) > 0.f)) g.x = 0.f;
+            if (!(fmaf(zv.y, sc, sf) > 0.f)) g.y = 0.f;
+            if (!(fmaf(zv.z, sc, sf) > 0.f)) g.z = 0.f;
+            if (!(fmaf(zv.w, sc, sf) > 0.f)) g.w = 0.f;
+          }
+          f1 += (g.x + g.y) + (g.z + g.w);
+          f2 = fmaf(g.x, (zv.x - mu) * rs, f2); f2 = fmaf(g.y, (zv.y - mu) * rs, f2);
+          f2 = fmaf(g.z, (zv.z - mu) * rs, f2); f2 = fmaf(g.w, (zv.w - mu) * rs, f2);
+        }
+      }
+      s1 += f1; s2 += f2;
+    }
+  } else
   for (int i0 = lo + threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
     float f1 = 0.f, f2 = 0.f;
 #pragma unroll 4
@@ -146,29 +202,41 @@ __global__ void __launch_bounds__(RED_THREADS) bn_bwd_reduce_kernel(const float*
 }
 
 // gz = gamma*rstd * (g - sum_g/n - xhat * sum_gxhat/n); also emits ggamma = sum_gxhat, gbeta = sum_g once.
+// grid (chunks, C, B) as affine_act_kernel: the per-channel constants (two fp64 divisions among them) once per CTA.
+template <int VEC>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ gy, const float* __restrict__ z,
                                                            const float* __restrict__ scale, const float* __restrict__ shift,
                                                            const float* __restrict__ mean, const float* __restrict__ rstd,
                                                            const float* __restrict__ gamma, const double* __restrict__ acc,
                                                            float* __restrict__ gz, float* __restrict__ ggamma,
-                                                           float* __restrict__ gbeta, int C, int HW, long long total, double n,
+                                                           float* __restrict__ gbeta, int C, int HW, int per, double n,
                                                            int relu) {
-  if (blockIdx.x == 0) {
-    for (int c = threadIdx.x; c < C; c += 256) {
-      if (gbeta) gbeta[c] = (float)acc[2 * c];
-      if (ggamma) ggamma[c] = (float)acc[2 * c + 1];
-    }
+  const int c = blockIdx.y, b = blockIdx.z;
+  if (blockIdx.x == 0 && b == 0 && threadIdx.x == 0) {
+    if (gbeta) gbeta[c] = (float)acc[2 * c];
+    if (ggamma) ggamma[c] = (float)acc[2 * c + 1];
   }
-  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += 256ll * gridDim.x) {
-    const int c = (int)((i / HW) % C);
-    const float sc = scale[c], sf = shift[c], mu = mean[c], rs = rstd[c];
-    const float zv = z[i];
-    float g = gy[i];
-    if (relu && !(fmaf(zv, sc, sf) > 0.f)) g = 0.f;
-    const float xh = (zv - mu) * rs;
-    const float m1 = (float)(acc[2 * c] / n), m2 = (float)(acc[2 * c + 1] / n);
-    const float gm = gamma ? gamma[c] : 1.f;
-    gz[i] = gm * rs * (g - m1 - xh * m2);
+  const float sc = __ldg(scale + c), sf = __ldg(shift + c), mu = __ldg(mean + c), rs = __ldg(rstd + c);
+  const float m1 = (float)(acc[2 * c] / n), m2 = (float)(acc[2 * c + 1] / n);
+  const float k = (gamma ? __ldg(gamma + c) : 1.f) * rs;
+  const size_t base = ((size_t)b * C + c) * HW;
+  const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  for (int i = lo + VEC * threadIdx.x; i < hi; i += VEC * 256) {
+    float zv[VEC], g[VEC];
+    if (VEC == 4) {
+      *reinterpret_cast<float4*>(zv) = __ldg(reinterpret_cast<const float4*>(z + base + i));
+      *reinterpret_cast<float4*>(g) = __ldg(reinterpret_cast<const float4*>(gy + base + i));
+    } else {
+      zv[0] = __ldg(z + base + i); g[0] = __ldg(gy + base + i);
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      if (relu && !(fmaf(zv[e], sc, sf) > 0.f)) g[e] = 0.f;
+      const float xh = (zv[e] - mu) * rs;
+      g[e] = k * (g[e] - m1 - xh * m2);
+    }
+    if (VEC == 4) *reinterpret_cast<float4*>(gz + base + i) = *reinterpret_cast<float4*>(g);
+    else gz[base + i] = g[0];
   }
 }
 
@@ -180,8 +248,30 @@ __global__ void __launch_bounds__(RED_THREADS) relu_bias_bwd_kernel(const float*
   const int c = blockIdx.y, b = blockIdx.z;
   const size_t base = ((size_t)b * C + c) * HW;
   double s1 = 0.0;
-  const int per = (HW + gridDim.x - 1) / gridDim.x;
+  const int per = ((HW + gridDim.x - 1) / gridDim.x + 3) & ~3;
   const int lo = blockIdx.x * per, hi = min(HW, lo + per);
+  if ((HW & 3) == 0) {
+    for (int i0 = lo + 4 * threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
+      float f1 = 0.f;
+#pragma unroll 4
+      for (int k = 0; k < 8; ++k) {
+        const int i = i0 + k * RED_THREADS * 4;
+        if (i < hi) {
+          float4 v = __ldg(reinterpret_cast<const float4*>(gy + base + i));
+          if (relu) {
+            const float4 yv = __ldg(reinterpret_cast<const float4*>(y + base + i));
+            if (!(yv.x > 0.f)) v.x = 0.f;
+            if (!(yv.y > 0.f)) v.y = 0.f;
+            if (!(yv.z > 0.f)) v.z = 0.f;
+            if (!(yv.w > 0.f)) v.w = 0.f;
+          }
+          if (g) *reinterpret_cast<float4*>(g + base + i) = v;
+          f1 += (v.x + v.y) + (v.z + v.w);
+        }
+      }
+      s1 += f1;
+    }
+  } else
   for (int i0 = lo + threadIdx.x; i0 < hi; i0 += RED_THREADS * 32) {
     float f1 = 0.f;
 #pragma unroll 4
@@ -242,8 +332,10 @@ extern "C" int nconv_b200_bn_train_fwd(const float* x, const float* gamma, const
   }
   {
     LaunchScope ls(st, "bn_train_apply", 2.0 * total, 4.0 * total * (residual ? 3.0 : 2.0));
-    const int blocks = (int)((total + 256 * 8 - 1) / (256 * 8) < 148 * 16 ? (total + 256 * 8 - 1) / (256 * 8) : 148 * 16);
-    affine_act_kernel<<<blocks < 1 ? 1 : blocks, 256, 0, st>>>(x, scale, shift, residual, y, C, HW, total, relu);
+    int per = 0;
+    const int chunks = stream_chunks(HW, C, B, &per);
+    if (HW % 4 == 0) affine_act_kernel<4><<<dim3(chunks, C, B), 256, 0, st>>>(x, scale, shift, residual, y, C, HW, per, relu);
+    else affine_act_kernel<1><<<dim3(chunks, C, B), 256, 0, st>>>(x, scale, shift, residual, y, C, HW, per, relu);
   }
   return (int)cudaGetLastError();
 }
@@ -265,11 +357,14 @@ extern "C" int nconv_b200_bn_train_bwd(const float* gy, const float* z, const fl
   }
   {
     LaunchScope ls(st, "bn_bwd_apply", 8.0 * total, 12.0 * total);
-    long long blocks = (total + 256 * 8 - 1) / (256 * 8);
-    if (blocks > 148 * 16) blocks = 148 * 16;
-    bn_bwd_apply_kernel<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, st>>>(gy, z, scale, shift, mean, rstd, gamma,
-                                                                        (const double*)ws, gz, ggamma, gbeta, C, HW, total,
-                                                                        (double)B * HW, relu);
+    int per = 0;
+    const int chunks = stream_chunks(HW, C, B, &per);
+    if (HW % 4 == 0)
+      bn_bwd_apply_kernel<4><<<dim3(chunks, C, B), 256, 0, st>>>(gy, z, scale, shift, mean, rstd, gamma, (const double*)ws, gz,
+                                                                 ggamma, gbeta, C, HW, per, (double)B * HW, relu);
+    else
+      bn_bwd_apply_kernel<1><<<dim3(chunks, C, B), 256, 0, st>>>(gy, z, scale, shift, mean, rstd, gamma, (const double*)ws, gz,
+                                                                 ggamma, gbeta, C, HW, per, (double)B * HW, relu);
   }
   return (int)cudaGetLastError();
 }
