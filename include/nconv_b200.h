@@ -322,6 +322,10 @@ typedef struct {
   void* y;
   void* yq;             /* or NULL                                             */
   int B, CA, CB, CO, H, W, relu, mode, has_1x1;
+  float* y_f32;         /* mode S1 only, or NULL: write fp32 NCHW instead of y, into channels [y_c0, y_c0+CO) of a
+                           contiguous [B][y_ctot][H][W] tensor (the data gradient of train_step2.py:62-64's backward);
+                           NCONV_B200_ERR_UNSUPPORTED for CO = 32 with CA+CB >= 64 (that shape's kernel writes P8 only) */
+  int y_ctot, y_c0;
 } nconv_b200_tc_desc;
 int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream);
 

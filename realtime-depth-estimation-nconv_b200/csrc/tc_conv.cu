@@ -113,6 +113,8 @@ struct TcArgs {
   const float* shift;           // [CO] or null
   __nv_bfloat16* out;           // P8 [B][CO/8][2][OH+2][OW+2][8]
   __nv_bfloat16* outq;          // optional P8Q copy of the output
+  float* out32;                 // S1 only: fp32 NCHW output instead of `out` (channels [o32_c0, o32_c0+CO) of a [B][o32_ctot][OH][OW] tensor)
+  int o32_ctot, o32_c0;
   int B, AH, AW, OH, OW;        // anchor grid and output size
   int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, ntaps, ntaps_w;
   uint32_t P_magic;             // ceil(2^32 / P): m / P == __umulhi(m, P_magic) for m * P < 2^32 (no integer division in the epilogue)
@@ -315,7 +317,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
               for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
             }
-            if (valid && !(a.dbg & 1)) {
+            if (MODE == TC_S1 && a.out32) {
+              // fp32 NCHW epilogue (the training data gradient, ops.py::_ConvTrain.backward): a lane owns one pixel, so every
+              // channel's store is a 128-byte run across the warp; no P8 round trip through HBM
+              if (valid && !(a.dbg & 1)) {
+                const size_t cs = (size_t)a.OH * a.OW;
+                float* ob = a.out32 + ((size_t)n * a.o32_ctot + a.o32_c0 + cb * 32) * cs + (size_t)oy * a.OW + ox;
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                  const int o = cb * 32 + e;
+                  float x = fmaf(__uint_as_float(v[e]), s_scale[o], s_shift[o]);
+                  if (a.relu) x = fmaxf(x, 0.f);
+                  ob[e * cs] = x;
+                }
+              }
+            } else if (valid && !(a.dbg & 1)) {
 #pragma unroll
               for (int ch = 0; ch < 4; ++ch) {
                 float f[8];
@@ -570,9 +586,13 @@ extern "C" int nconv_b200_tc_pack_weights(int mode, const float* w, const float*
 }
 
 extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
-  if (!d || !d->a || !d->wpack || !d->y) return NCONV_ERR_BAD_ARG;
+  if (!d || !d->a || !d->wpack || (!d->y && !d->y_f32)) return NCONV_ERR_BAD_ARG;
   if (d->B <= 0 || d->H <= 0 || d->W <= 0 || d->CA <= 0 || d->CB < 0) return NCONV_ERR_BAD_ARG;
   if (d->mode < 0 || d->mode > 2) return NCONV_ERR_BAD_ARG;
+  if (d->y_f32) {
+    if (d->mode != TC_S1 || d->yq || d->y_c0 < 0 || d->y_c0 + d->CO > d->y_ctot) return NCONV_ERR_BAD_ARG;
+    if (tcx_on(d->mode, d->CO, d->CA + d->CB)) return NCONV_ERR_UNSUPPORTED;       // the pixels-on-N kernel writes P8 only
+  }
   const int mode = d->mode;
   const int lead = tc_lead(mode, d->CA);
   if ((!lead && d->CA % 16) || d->CB % 16 || (d->CB > 0 && !d->b)) return NCONV_ERR_UNSUPPORTED;
@@ -617,6 +637,7 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   }
   a.wpack = (const __nv_bfloat16*)d->wpack; a.scale = d->scale; a.shift = d->shift;
   a.out = (__nv_bfloat16*)d->y; a.outq = (__nv_bfloat16*)d->yq;
+  a.out32 = d->y_f32; a.o32_ctot = d->y_ctot; a.o32_c0 = d->y_c0;
   a.B = d->B; a.AH = AH; a.AW = AW;
   a.OH = (mode == TC_T) ? 2 * d->H : AH; a.OW = (mode == TC_T) ? 2 * d->W : AW;
   a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.T = p.T; a.rows_alloc = p.rows_alloc; a.rows_ld = p.rows_ld;

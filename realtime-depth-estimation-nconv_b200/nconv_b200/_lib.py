@@ -45,6 +45,7 @@ class TcDesc(Structure):
         ("y", c_void_p), ("yq", c_void_p),
         ("B", c_int), ("CA", c_int), ("CB", c_int), ("CO", c_int), ("H", c_int), ("W", c_int), ("relu", c_int),
         ("mode", c_int), ("has_1x1", c_int),
+        ("y_f32", c_void_p), ("y_ctot", c_int), ("y_c0", c_int),
     ]
 
 

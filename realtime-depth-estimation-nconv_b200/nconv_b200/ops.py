@@ -553,10 +553,27 @@ def conv_tc(mode: int, a: "P8", b, wpack, CO: int, scale, shift, relu: bool, has
     else:
         pa, pb = _p(a.buf), None if b is None else _p(b.buf)
     d = TcDesc(pa, pb, _p(wpack), _p(scale), _p(shift), _p(y.buf), _p(y.qbuf), a.B, a.C, CB, CO, a.H, a.W,
-               int(relu), mode, int(has_1x1))
+               int(relu), mode, int(has_1x1), None, 0, 0)
     with torch.cuda.device(a.buf.device):
         check(_C.nconv_b200_conv_tc(byref(d), _stream(a.buf)), "conv_tc")
     return y
+
+
+def conv_tc_f32(a: "P8", wpack, CO: int, out, c0: int = 0, shift=None, relu: bool = False):
+    """3x3 / stride-1 conv of the P8 tensor `a` on tcgen05, written as fp32 into channels [c0, c0+CO) of the contiguous
+    NCHW tensor `out` [B, Ctot, H, W] (no P8 round trip).  Returns False when the shape's kernel cannot (CO = 32 with >= 64
+    input channels): the caller takes conv_tc(...).unpack_into(out, c0)."""
+    if out.dtype != torch.float32 or not out.is_contiguous() or out.shape[0] != a.B or tuple(out.shape[2:]) != (a.H, a.W):
+        raise ValueError("conv_tc_f32: out must be contiguous fp32 [B, Ctot, H, W] of the source's B, H, W")
+    shift = _prep_opt(shift, "shift")
+    d = TcDesc(_p(a.buf), None, _p(wpack), None, _p(shift), None, None, a.B, a.C, 0, CO, a.H, a.W, int(relu), TC_S1, 0,
+               _p(out), int(out.shape[1]), int(c0))
+    with torch.cuda.device(a.buf.device):
+        rc = _C.nconv_b200_conv_tc(byref(d), _stream(a.buf))
+    if rc == 100002:          # NCONV_B200_ERR_UNSUPPORTED
+        return False
+    check(rc, "conv_tc_f32")
+    return True
 
 
 def conv_small_p8(x, weight, w1, scale, shift, relu: bool, out=None, with_q=False) -> "P8":
@@ -839,7 +856,11 @@ def _tc_conv3x3(x, weight, shift, relu: bool):
     """act(conv3x3_p1(x, weight) + shift) on the tcgen05 path, fp32 NCHW in and out."""
     CO, CI = weight.shape[0], weight.shape[1]
     wp = tc_pack_weights(TC_S1, weight, CI, 0)
-    return conv_tc(TC_S1, P8.pack(x), None, wp, CO, None, shift, relu).unpack()
+    x8 = P8.pack(x)
+    y = torch.empty((x.shape[0], CO, x.shape[2], x.shape[3]), device=x.device, dtype=torch.float32)
+    if not conv_tc_f32(x8, wp, CO, y, 0, shift=shift, relu=relu):
+        conv_tc(TC_S1, x8, None, wp, CO, None, shift, relu).unpack_into(y, 0)
+    return y
 
 
 class _ConvTrain(torch.autograd.Function):
@@ -901,7 +922,8 @@ class _ConvTrain(torch.autograd.Function):
                     gx = torch.empty_like(x)
                     for c0 in range(0, CI, blk):
                         wpk = tc_pack_weights(TC_S1, wf[c0:c0 + blk].contiguous(), CO, 0)
-                        conv_tc(TC_S1, g8, None, wpk, blk, None, None, False).unpack_into(gx, c0)
+                        if not conv_tc_f32(g8, wpk, blk, gx, c0):
+                            conv_tc(TC_S1, g8, None, wpk, blk, None, None, False).unpack_into(gx, c0)
                 else:
                     gx = _conv_fwd_raw(g, wf, None, None, 1, False)
             else:

@@ -917,3 +917,28 @@ def test_head_p8(cfg):
     assert grad_err(y, ref) <= 1e-5
     assert grad_err(y8.unpack(), ref) <= 1e-5
     assert _ring_intact(y8)
+
+
+@pytest.mark.parametrize("cfg", [(2, 32, 64, 33, 70), (1, 64, 64, 40, 48), (2, 32, 32, 17, 130), (1, 128, 64, 24, 40)])
+def test_conv3x3_tc_fp32_output(cfg):
+    """The fp32 NCHW epilogue of the tcgen05 3x3 conv (training data gradient: no P8 round trip): channels land at an
+    offset of a wider tensor, everything else untouched; against the P8 epilogue (same accumulators: equal to the
+    16-bit-mantissa split the P8 store applies) and fp64."""
+    from nconv_b200 import ops
+    from nconv_b200.ops import P8, TC_S1
+    B, CI, CO, H, W = cfg
+    torch.manual_seed(21)
+    x = torch.randn(B, CI, H, W)
+    w = torch.randn(CO, CI, 3, 3) * 0.1
+    shift = torch.randn(CO)
+    ref = F.conv2d(x.double(), w.double(), shift.double(), padding=1)
+    x8 = P8.pack(x.to(dev()))
+    wp = ops.tc_pack_weights(TC_S1, w.to(dev()), CI, 0)
+    out = torch.full((B, CO + 24, H, W), -3.0, device=dev())
+    ok = ops.conv_tc_f32(x8, wp, CO, out, 8, shift=shift.to(dev()))
+    assert ok
+    got = out[:, 8:8 + CO]
+    assert _rel(got, ref) <= 2e-5
+    assert bool((out[:, :8] == -3).all()) and bool((out[:, 8 + CO:] == -3).all())
+    via_p8 = ops.conv_tc(TC_S1, x8, None, wp, CO, None, shift.to(dev()), False).unpack()
+    assert O.max_rel_err(via_p8, got, floor=1e-6) <= 2.0 ** -16
