@@ -26,6 +26,7 @@ extern "C" {
 #define NCONV_B200_ERR_BAD_ARG 100001
 #define NCONV_B200_ERR_UNSUPPORTED 100002
 #define NCONV_B200_ERR_WORKSPACE 100003
+#define NCONV_B200_ERR_STATIC_SCRATCH 100004 /* size beyond the static scratch of a *_noalloc entry point */
 
 /* flags of nconv_b200_fwd_desc */
 #define NCONV_B200_F_THRESH 1 /* conf = (xa > thr), xa used raw  (step1.py:53-54)            */
@@ -241,6 +242,18 @@ int nconv_b200_bn_train_bwd(const float* gy, const float* z, const float* scale,
  * gbias[c] = sum g; relu=0 gives the plain per-channel sum of gy. */
 int nconv_b200_relu_bias_bwd(const float* gy, const float* y, float* g, float* gbias, void* ws, int B,
                              int C, int H, int W, int relu, void* stream);
+
+/* No counterpart in the reference: added for callers that cannot allocate device
+ * memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same operation and
+ * results as nconv_b200_relu_bias_bwd, without the `ws` argument: the per-channel fp64 sums go to a static device array
+ * inside the library (2 doubles per channel, NCONV_B200_NOALLOC_MAX_C channels = 16 KB per GPU, held until the process
+ * exits).  C > NCONV_B200_NOALLOC_MAX_C returns NCONV_B200_ERR_STATIC_SCRATCH.  The call makes no cudaMalloc / cudaFree
+ * and calls no allocating library routine; it enqueues a memset of the array, the kernel and (gbias != NULL) the
+ * read-out on `stream`.  Every call on a GPU shares the one array: calls that overlap on the GPU (different streams with
+ * no dependency between them) race; calls ordered on one stream, or by events, do not. */
+#define NCONV_B200_NOALLOC_MAX_C 1024
+int nconv_b200_relu_bias_bwd_noalloc(const float* gy, const float* y, float* g, float* gbias, int B, int C, int H,
+                                     int W, int relu, void* stream);
 
 /* weight gradient gw[CO][CI][K][K] = sum_{b,oy,ox} g[b,co,oy,ox]*x[b,ci,oy*S-P+u,ox*S-P+v] of
  * Conv2d (K,S,P) in {(1,1,0),(1,2,0),(3,1,1),(3,2,1)}; (4,2,1) with g and x swapped is

@@ -13,7 +13,7 @@
   } while (0)
 
 // Error codes above the CUDA range for argument problems detected by a launcher.
-enum { NCONV_ERR_BAD_ARG = 100001, NCONV_ERR_UNSUPPORTED = 100002, NCONV_ERR_WORKSPACE = 100003 };
+enum { NCONV_ERR_BAD_ARG = 100001, NCONV_ERR_UNSUPPORTED = 100002, NCONV_ERR_WORKSPACE = 100003, NCONV_ERR_STATIC_SCRATCH = 100004 };
 
 namespace nconv {
 

@@ -18,6 +18,7 @@
 // Per-channel reductions accumulate in double (per-thread fp32 partials over <= 64 values, combined in
 // fp64 through shared memory and one atomicAdd(double) per CTA), so BatchNorm statistics of the
 // un-normalised RGB activations (mean >> std) do not lose digits and results do not depend on the grid.
+#include <mutex>
 #include "common.cuh"
 #include <cstdint>
 #include <type_traits>
@@ -385,6 +386,55 @@ extern "C" int nconv_b200_relu_bias_bwd(const float* gy, const float* y, float* 
   if (gbias) {
     LaunchScope ls(st, "channel_sum_out", 0.0, 0.0);
     double_to_float_kernel<<<(C + 127) / 128, 128, 0, st>>>((const double*)ws, gbias, C, 1);
+  }
+  return (int)cudaGetLastError();
+}
+
+// ---- the same operation for callers that must not allocate ----------------------------------------------------------
+// (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc.)  The per-channel fp64 sums live in a file-scope
+// device array instead of a caller workspace: 2 doubles per channel, NCONV_B200_NOALLOC_MAX_C channels = 16 KB, held by
+// every GPU that loads the library until the process exits.  In HOST code `g_noalloc_sums` is only a stand-in for the
+// symbol, not a device address: its address is taken once per device with cudaGetSymbolAddress (that device current)
+// and that pointer is what the kernels get.  All calls share the array and it keeps the previous call's sums: it is
+// cleared (memset on the caller's stream, no allocation) at the start of every call; two calls that overlap on the GPU
+// (different streams, no dependency between them) race on it.
+static __device__ __align__(256) double g_noalloc_sums[2 * NCONV_B200_NOALLOC_MAX_C];
+
+static int noalloc_sums_ptr(double** out) {
+  static std::mutex mu;
+  static double* ptr[NCONV_MAX_DEVICES] = {};
+  int dev = 0;
+  NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NCONV_MAX_DEVICES) return NCONV_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    double* p = nullptr;
+    NCONV_RETURN_IF_ERR(cudaGetSymbolAddress((void**)&p, g_noalloc_sums));     // the current device's copy of the array
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+extern "C" int nconv_b200_relu_bias_bwd_noalloc(const float* gy, const float* y, float* g, float* gbias, int B, int C, int H,
+                                                int W, int relu, void* stream) {
+  if (!gy || (relu && !y)) return NCONV_ERR_BAD_ARG;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return NCONV_ERR_BAD_ARG;
+  if (C > NCONV_B200_NOALLOC_MAX_C) return NCONV_ERR_STATIC_SCRATCH;           // beyond the static array: use the workspace entry point
+  if ((long long)B > 65535) return NCONV_ERR_UNSUPPORTED;                       // gridDim.z
+  double* sums = nullptr;
+  { const int rc = noalloc_sums_ptr(&sums); if (rc) return rc; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HW = H * W;
+  const long long total = (long long)B * C * HW;
+  NCONV_RETURN_IF_ERR(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * C, st));
+  {
+    LaunchScope ls(st, "relu_bias_bwd (static scratch)", 2.0 * total, 4.0 * total * (g ? 3.0 : (relu ? 2.0 : 1.0)));
+    relu_bias_bwd_kernel<<<dim3(red_chunks(HW, C, B), C, B), RED_THREADS, 0, st>>>(gy, y, g, sums, C, HW, relu);
+  }
+  if (gbias) {
+    LaunchScope ls(st, "channel_sum_out", 0.0, 0.0);
+    double_to_float_kernel<<<(C + 127) / 128, 128, 0, st>>>(sums, gbias, C, 1);
   }
   return (int)cudaGetLastError();
 }

@@ -294,6 +294,7 @@ extern "C" const char* nconv_b200_error_string(int code) {
     case NCONV_ERR_BAD_ARG: return "nconv_b200: bad argument (null pointer or non-positive size)";
     case NCONV_ERR_UNSUPPORTED: return "nconv_b200: unsupported shape/flag combination";
     case NCONV_ERR_WORKSPACE: return "nconv_b200: workspace too small";
+    case NCONV_ERR_STATIC_SCRATCH: return "nconv_b200: size exceeds the static scratch of the no-allocation entry point (see its limit in include/nconv_b200.h); use the entry point that takes a workspace";
     default: return cudaGetErrorString((cudaError_t)code);
   }
 }

@@ -72,6 +72,7 @@ SIGNATURES = {
     "nconv_b200_bn_train_fwd": (c_int, [c_void_p] * 12 + [c_int] * 4 + [c_float, c_float, c_int, c_void_p]),
     "nconv_b200_bn_train_bwd": (c_int, [c_void_p] * 11 + [c_int] * 5 + [c_void_p]),
     "nconv_b200_relu_bias_bwd": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
+    "nconv_b200_relu_bias_bwd_noalloc": (c_int, [c_void_p] * 4 + [c_int] * 5 + [c_void_p]),
     "nconv_b200_conv_wgrad_ws_bytes": (c_size_t, [c_int] * 3),
     "nconv_b200_conv_wgrad": (c_int, [c_void_p] * 4 + [c_size_t] + [c_int] * 8 + [c_void_p]),
     "nconv_b200_conv_dgrad_ws_bytes": (c_size_t, [c_int] * 3),
