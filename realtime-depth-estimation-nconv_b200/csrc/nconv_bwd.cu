@@ -484,6 +484,7 @@ extern "C" size_t nconv_b200_nconv2d_bwd_workspace_bytes(int B, int Ci, int Co, 
   int K = kh > kw ? kh : kw;
   fl += wgrad_partial_floats(Ci, Co, K) + 64;
   if (Co == 2 && Ci <= 2 && K == 3) { size_t bs = (size_t)BS_MAX_UNITS * (Co * Ci * 9 + 2 * Co) + 64; if (bs > fl) fl = bs; }
+  if (Co == 2 && Ci <= 2 && K == 5) { size_t bs = (size_t)BS_MAX_UNITS * (Co * 25 + 2 * Co) + 64; if (bs > fl) fl = bs; }
   return fl * sizeof(float);
 }
 
@@ -557,6 +558,13 @@ extern "C" int nconv_b200_nconv2d_bwd(const float* gy, const float* gcout, const
       a.gy = gy; a.gco = gcout; a.y = y; a.co = cout; a.x = x; a.c = c; a.w = w; a.bias = bias;
       a.gx = gx; a.gc = gc; a.partial = (float*)workspace; a.B = B; a.H = H; a.W = W; a.eps = eps;
       const int rc = (Ci == 1) ? launch_bwd_stream<1, 2>(a, gw, gb, st) : launch_bwd_stream<2, 2>(a, gw, gb, st);
+      if (rc != NCONV_ERR_UNSUPPORTED) return rc;
+    }
+    if (!no_stream && gx && gc && gw && vec && kh == 5 && kw == 5 && ph == 2 && pw == 2 && Co == 2 && (Ci == 1 || Ci == 2)) {
+      BsArgs a = {};
+      a.gy = gy; a.gco = gcout; a.y = y; a.co = cout; a.x = x; a.c = c; a.w = w; a.bias = bias;
+      a.gx = gx; a.gc = gc; a.partial = (float*)workspace; a.B = B; a.H = H; a.W = W; a.eps = eps;
+      const int rc = (Ci == 1) ? launch_bwd_stream5<1>(a, gw, gb, st) : launch_bwd_stream5<2>(a, gw, gb, st);
       if (rc != NCONV_ERR_UNSUPPORTED) return rc;
     }
   }

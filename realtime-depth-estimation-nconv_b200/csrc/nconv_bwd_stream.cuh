@@ -329,4 +329,275 @@ static int launch_bwd_stream(BsArgs a, float* gw, float* gb, cudaStream_t st) {
   return (int)cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The same single pass for K = 5 (pad 2), Co = 2, Ci in {1, 2} (BASELINE config 2's 1->2 / 2->2 k5 rows; before: two
+// passes, nconv_bwd_data + nconv_wgrad, 0.23 / 0.27 ms at 16x480x640).  What changes against the 3x3 kernel:
+//   * a lane owns 2 pixels (64-column strips): five window rows of 2 + 4 columns for both output channels are 120
+//     registers, 4-pixel lanes would not fit;
+//   * a unit handles ONE input channel (50 weight-gradient accumulators); with Ci = 2 the two units of a strip are
+//     adjacent warps of one CTA, so the second one's (gy, gcout, y, cout) loads hit L1 / L2; bias and T sums are taken
+//     by the channel-0 unit;
+//   * two halo columns per side: from the neighbouring lane's two pixels by shuffle, strip-edge lanes load theirs.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int B5_PX = 2, B5_COLS = 32 * B5_PX, B5_K = 5, B5_CO = 2, B5_WIN = B5_PX + 4;
+
+struct B5RawG {
+  float2 gy[B5_CO], gco[B5_CO], y[B5_CO], co[B5_CO];
+  float2 hgy[B5_CO], hgco[B5_CO], hy[B5_CO], hco[B5_CO];      // strip-edge halo columns (lanes 0 and 31 only)
+};
+
+template <bool HAS_GCO>
+__device__ __forceinline__ void b5_load_g(B5RawG& r, const BsArgs& a, long long off, size_t plane, int hoff, bool own, bool h0,
+                                          bool h1) {
+  const float2 z = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int o = 0; o < B5_CO; ++o) {
+    r.gy[o] = z; r.gco[o] = z; r.y[o] = z; r.co[o] = z;
+    r.hgy[o] = z; r.hgco[o] = z; r.hy[o] = z; r.hco[o] = z;
+    if (own) {
+      r.gy[o] = __ldg(reinterpret_cast<const float2*>(a.gy + off + o * plane));
+      if (HAS_GCO) r.gco[o] = __ldg(reinterpret_cast<const float2*>(a.gco + off + o * plane));
+      r.y[o] = __ldg(reinterpret_cast<const float2*>(a.y + off + o * plane));
+      r.co[o] = __ldg(reinterpret_cast<const float2*>(a.co + off + o * plane));
+    }
+    if (h0) {
+      r.hgy[o].x = __ldg(a.gy + off + o * plane + hoff);
+      if (HAS_GCO) r.hgco[o].x = __ldg(a.gco + off + o * plane + hoff);
+      r.hy[o].x = __ldg(a.y + off + o * plane + hoff);
+      r.hco[o].x = __ldg(a.co + off + o * plane + hoff);
+    }
+    if (h1) {
+      r.hgy[o].y = __ldg(a.gy + off + o * plane + hoff + 1);
+      if (HAS_GCO) r.hgco[o].y = __ldg(a.gco + off + o * plane + hoff + 1);
+      r.hy[o].y = __ldg(a.y + off + o * plane + hoff + 1);
+      r.hco[o].y = __ldg(a.co + off + o * plane + hoff + 1);
+    }
+  }
+}
+
+template <int CI, bool HAS_GCO>
+__global__ void __launch_bounds__(BS_WARPS * 32, 1) nconv_bwd_stream5(const BsArgs a) {
+  constexpr int CO = B5_CO, KK = B5_K * B5_K, NW = CO * CI * KK, NPU = CO * KK + 2 * CO;
+  __shared__ float s_w[NW], s_is[CO], s_b[CO];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < NW; i += BS_WARPS * 32) s_w[i] = __ldg(a.w + i);
+  __syncthreads();
+  if (tid < CO) {
+    float s = 0.f;
+    for (int j = 0; j < CI * KK; ++j) s += s_w[tid * CI * KK + j];
+    s_is[tid] = 1.f / s;
+    s_b[tid] = __ldg(a.bias + tid);
+  }
+  __syncthreads();
+
+  const long long unit = (long long)blockIdx.x * BS_WARPS + warp;
+  if (unit >= a.units) return;
+  const int ic = (int)(unit % CI);                           // input channel of this unit (fastest: shares g loads with its twin)
+  const long long u2 = unit / CI;
+  const int strip = (int)(u2 % a.nstrip);
+  const int seg = (int)((u2 / a.nstrip) % a.nseg);
+  const int b = (int)(u2 / ((long long)a.nseg * a.nstrip));
+  const int r0 = seg * a.RS, x0 = strip * B5_COLS, col = x0 + B5_PX * lane;
+  const int rows = min(a.RS, a.H - r0);
+  const int W = a.W, H = a.H;
+  const size_t plane = (size_t)H * W;
+  const bool inb = col < W;
+  const int hcol = (lane == 0) ? x0 - 2 : x0 + B5_COLS;      // first of the two halo columns
+  const bool edge = (lane == 0 || lane == 31);
+  const bool h0 = edge && hcol >= 0 && hcol < W, h1 = edge && hcol + 1 >= 0 && hcol + 1 < W;
+  const int hoff = (lane == 0) ? -2 : B5_PX;
+  float sden[CO], isum[CO], bo[CO];
+#pragma unroll
+  for (int o = 0; o < CO; ++o) { isum[o] = s_is[o]; sden[o] = 1.f / isum[o]; bo[o] = s_b[o]; }
+  const float* wi = s_w + ic * KK;                            // W[o][ic][u][v] = wi[o * CI * KK + u * 5 + v]
+
+  long long goff = ((long long)b * CO * H + (r0 - 2)) * W + col;       // next g row to load
+  long long xoff = (((long long)b * CI + ic) * H + r0) * W + col;      // next x row to load
+  long long ooff = xoff;                                               // next gx/gc row to store
+
+  u64 win[B5_K][CO][B5_WIN];            // (gN, gD) windows of the last five output-space rows
+  float accW[CO][KK], accB[CO], accT[CO];
+#pragma unroll
+  for (int o = 0; o < CO; ++o) {
+    accB[o] = 0.f; accT[o] = 0.f;
+#pragma unroll
+    for (int t = 0; t < KK; ++t) accW[o][t] = 0.f;
+  }
+
+  B5RawG rg;
+  float2 rxx = make_float2(0.f, 0.f), rxc = make_float2(0.f, 0.f);
+  {
+    const bool ok = r0 - 2 >= 0;
+    b5_load_g<HAS_GCO>(rg, a, goff, plane, hoff, ok && inb, ok && h0, ok && h1);
+    goff += W;
+    if (inb) {                                               // row r0: consumed at step 4
+      rxx = __ldg(reinterpret_cast<const float2*>(a.x + xoff));
+      rxc = __ldg(reinterpret_cast<const float2*>(a.c + xoff));
+    }
+    xoff += W;
+  }
+
+  const int nsteps = rows + 4;
+#pragma unroll 1
+  for (int sb = 0; sb < nsteps; sb += B5_K) {
+#pragma unroll
+    for (int sl = 0; sl < B5_K; ++sl) {
+      const int s = sb + sl;
+      if (s < nsteps) {
+        // ---- output-space row gr = r0-2+s -> packed (gN, gD) window with its two-column halos
+        {
+          const int gr = r0 - 2 + s;
+          const bool count = (ic == 0) && (s >= 2) && (s < rows + 2);
+#pragma unroll
+          for (int o = 0; o < CO; ++o) {
+            const float gy2[2] = {rg.gy[o].x, rg.gy[o].y}, gc2[2] = {rg.gco[o].x, rg.gco[o].y};
+            const float y2[2] = {rg.y[o].x, rg.y[o].y}, c2[2] = {rg.co[o].x, rg.co[o].y};
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+              const float gn = gy2[p] * rcp_fast(fmaf(c2[p], sden[o], a.eps));
+              const float gd = fmaf(gc2[p], isum[o], -gn * (y2[p] - bo[o]));
+              win[sl][o][p + 2] = pack2f(gn, gd);
+              if (count) { accB[o] += gy2[p]; accT[o] = fmaf(gc2[p], c2[p], accT[o]); }
+            }
+            const float hg2[2] = {rg.hgy[o].x, rg.hgy[o].y}, hc2[2] = {rg.hgco[o].x, rg.hgco[o].y};
+            const float hy2[2] = {rg.hy[o].x, rg.hy[o].y}, hco2[2] = {rg.hco[o].x, rg.hco[o].y};
+            u64 hp[2];
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+              const float hgn = hg2[p] * rcp_fast(fmaf(hco2[p], sden[o], a.eps));
+              hp[p] = pack2f(hgn, fmaf(hc2[p], isum[o], -hgn * (hy2[p] - bo[o])));
+            }
+            const u64 l0 = shfl_up64(win[sl][o][2]), l1 = shfl_up64(win[sl][o][3]);
+            const u64 q0 = shfl_down64(win[sl][o][2]), q1 = shfl_down64(win[sl][o][3]);
+            win[sl][o][0] = (lane == 0) ? hp[0] : l0;
+            win[sl][o][1] = (lane == 0) ? hp[1] : l1;
+            win[sl][o][4] = (lane == 31) ? hp[0] : q0;
+            win[sl][o][5] = (lane == 31) ? hp[1] : q1;
+          }
+          const int gn_row = gr + 1;
+          const bool ok = (s + 1 < nsteps) && gn_row >= 0 && gn_row < H;
+          b5_load_g<HAS_GCO>(rg, a, goff, plane, hoff, ok && inb, ok && h0, ok && h1);
+          goff += W;
+        }
+        // ---- input row q = r0+s-4: data gradient and weight-gradient accumulation for channel ic
+        if (s >= 4) {
+          const float xo[2] = {rxx.x, rxx.y}, cv[2] = {rxc.x, rxc.y};
+          rxx = make_float2(0.f, 0.f); rxc = make_float2(0.f, 0.f);
+          if (inb && (s + 1 < nsteps)) {
+            rxx = __ldg(reinterpret_cast<const float2*>(a.x + xoff));
+            rxc = __ldg(reinterpret_cast<const float2*>(a.c + xoff));
+          }
+          xoff += W;
+          u64 A[2] = {0ull, 0ull};
+          const float xc[2] = {xo[0] * cv[0], xo[1] * cv[1]};
+#pragma unroll
+          for (int o = 0; o < CO; ++o)
+#pragma unroll
+            for (int u = 0; u < B5_K; ++u) {
+              const int slot = (sl - u + B5_K) % B5_K;               // output-space row q+2-u
+#pragma unroll
+              for (int v = 0; v < B5_K; ++v) {
+                const float wv = wi[o * CI * KK + u * B5_K + v];
+                float acc = accW[o][u * B5_K + v];
+#pragma unroll
+                for (int p = 0; p < 2; ++p) {
+                  const u64 g2 = win[slot][o][p + 4 - v];
+                  ffma2(A[p], g2, wv);
+                  acc = fmaf(lo32f(g2), xc[p], acc);
+                  acc = fmaf(hi32f(g2), cv[p], acc);
+                }
+                accW[o][u * B5_K + v] = acc;
+              }
+            }
+          if (inb) {
+            __stcs(reinterpret_cast<float2*>(a.gx + ooff), make_float2(lo32f(A[0]) * cv[0], lo32f(A[1]) * cv[1]));
+            __stcs(reinterpret_cast<float2*>(a.gc + ooff),
+                   make_float2(fmaf(lo32f(A[0]), xo[0], hi32f(A[0])), fmaf(lo32f(A[1]), xo[1], hi32f(A[1]))));
+          }
+          ooff += W;
+        }
+      }
+    }
+  }
+
+  float* dst = a.partial + (size_t)unit * NPU;              // [o][tap] of channel ic, then gb[o], T[o] (channel-0 units)
+#pragma unroll
+  for (int o = 0; o < CO; ++o) {
+#pragma unroll
+    for (int t = 0; t < KK; ++t) {
+      const float v = warp_sum(accW[o][t]);
+      if (lane == 0) dst[o * KK + t] = v;
+    }
+    const float vb = warp_sum(accB[o]), vt = warp_sum(accT[o]);
+    if (lane == 0) { dst[CO * KK + o] = vb; dst[CO * KK + CO + o] = vt; }
+  }
+}
+
+// gW[o][i][t] = sum over the units of channel i - T[o] / sum(W[o]);  gb[o], T[o] from the channel-0 units.
+template <int CI>
+__global__ void nconv_bwd_stream5_final(const float* __restrict__ partial, const float* __restrict__ w, float* __restrict__ gw,
+                                        float* __restrict__ gb, int units) {
+  constexpr int CO = B5_CO, KK = B5_K * B5_K, NW = CO * CI * KK, NPU = CO * KK + 2 * CO;
+  const int lane = threadIdx.x & 31;
+  const int idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (idx >= NW + CO) return;
+  if (idx < NW) {
+    const int o = idx / (CI * KK), i = (idx / KK) % CI, t = idx % KK;
+    float s = 0.f, T = 0.f, ws = 0.f;
+    for (int u = i + CI * lane; u < units; u += CI * 32) s += __ldg(partial + (size_t)u * NPU + o * KK + t);
+    for (int u = CI * lane; u < units; u += CI * 32) T += __ldg(partial + (size_t)u * NPU + CO * KK + CO + o);
+    for (int j = lane; j < CI * KK; j += 32) ws += __ldg(w + o * CI * KK + j);
+    s = warp_sum(s); T = warp_sum(T); ws = warp_sum(ws);
+    if (lane == 0) gw[idx] = s - T / ws;
+  } else if (gb) {
+    const int o = idx - NW;
+    float s = 0.f;
+    for (int u = CI * lane; u < units; u += CI * 32) s += __ldg(partial + (size_t)u * NPU + CO * KK + o);
+    s = warp_sum(s);
+    if (lane == 0) gb[o] = s;
+  }
+}
+
+template <int CI>
+static int launch_bwd_stream5(BsArgs a, float* gw, float* gb, cudaStream_t st) {
+  constexpr int CO = B5_CO, KK = B5_K * B5_K, NW = CO * CI * KK, NPU = CO * KK + 2 * CO;
+  int dev = 0, sms = 0;
+  NCONV_RETURN_IF_ERR(cudaGetDevice(&dev));
+  static int sm_cache[NCONV_MAX_DEVICES] = {};
+  if (dev < NCONV_MAX_DEVICES) sms = sm_cache[dev];
+  if (sms == 0) {
+    NCONV_RETURN_IF_ERR(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (dev < NCONV_MAX_DEVICES) sm_cache[dev] = sms;
+  }
+  const int nstrip = ceil_div(a.W, B5_COLS);
+  const double cap = (double)sms * BS_WARPS;
+  int best_rs = 0; double best = 1e300;
+  for (int rs = 4; rs <= 160; ++rs) {
+    const double units = (double)a.B * nstrip * ceil_div(a.H, rs) * CI;
+    if (units > BS_MAX_UNITS) continue;
+    const double cost = ceil(units / cap) * (rs + 4);
+    if (cost < best - 1e-9) { best = cost; best_rs = rs; }
+  }
+  if (best_rs == 0) return NCONV_ERR_UNSUPPORTED;
+  if (const char* e = getenv("NCONV_B200_BWD_STREAM_RS")) { int v = atoi(e); if (v > 0) best_rs = v; }
+  a.RS = best_rs; a.nstrip = nstrip; a.nseg = ceil_div(a.H, best_rs);
+  a.units = (long long)a.B * a.nstrip * a.nseg * CI;
+  if (a.units > BS_MAX_UNITS) return NCONV_ERR_UNSUPPORTED;
+  const unsigned blocks = (unsigned)((a.units + BS_WARPS - 1) / BS_WARPS);
+  const double px = (double)a.B * a.H * a.W;
+  char label[64];
+  snprintf(label, sizeof(label), "nconv_bwd_stream %d->%d k5", CI, CO);
+  {
+    LaunchScope ls(st, label, 8.0 * CI * CO * KK * px, 4.0 * (4.0 * CO + 4.0 * CI) * px);
+    if (a.gco) nconv_bwd_stream5<CI, true><<<blocks, BS_WARPS * 32, 0, st>>>(a);
+    else nconv_bwd_stream5<CI, false><<<blocks, BS_WARPS * 32, 0, st>>>(a);
+  }
+  NCONV_RETURN_IF_ERR(cudaGetLastError());
+  {
+    LaunchScope ls(st, "nconv_bwd_stream_final", 0.0, 4.0 * (double)a.units * NPU);
+    nconv_bwd_stream5_final<CI><<<ceil_div((NW + CO) * 32, 128), 128, 0, st>>>(a.partial, a.w, gw, gb, (int)a.units);
+  }
+  return (int)cudaGetLastError();
+}
+
 }  // namespace nconv
