@@ -45,4 +45,33 @@ for depth in (2, 3):
         s.run((host for _ in range(10)), consume=consume)
         torch.cuda.synchronize()
         out["streamed_depth%d_%s_ms" % (depth, name)] = (time.perf_counter() - t0) * 100
+# H2D of one batch WHILE the resident step runs on the compute stream (copy engine vs kernels)
+side = torch.cuda.Stream(dev)
+c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+with torch.no_grad():
+    for _ in range(3):
+        model(*res)
+    with torch.cuda.stream(side):
+        c0.record(side)
+        for d, h in zip([torch.empty_like(r) for r in res], host):
+            d.copy_(h, non_blocking=True)
+        c1.record(side)
+    for _ in range(3):
+        model(*res)
+torch.cuda.synchronize()
+out["h2d_ms_under_compute"] = c0.elapsed_time(c1)
+# host time to ENQUEUE one step (queue drained first; no synchronisation inside)
+torch.cuda.synchronize()
+with torch.no_grad():
+    t0 = time.perf_counter()
+    for _ in range(5):
+        model(*res)
+    out["host_enqueue_ms_per_step"] = (time.perf_counter() - t0) * 200
+torch.cuda.synchronize()
+out["cpus"] = len(os.sched_getaffinity(0))
+try:
+    import subprocess
+    out["topo"] = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout[-700:]
+except Exception as e:       # noqa: BLE001
+    out["topo"] = str(e)
 print(json.dumps(out))
