@@ -552,7 +552,9 @@ using namespace nconv;
 static bool tcx_on(int mode, int CO, int CI) {
   static const bool off = getenv("NCONV_B200_NO_TCX") != nullptr;
   static const bool all = getenv("NCONV_B200_TCX_ALL") != nullptr;
-  return !off && mode == TC_S1 && CO == TCX_CO && (all || CI >= 64);
+  // CI <= 64: the kernel keeps ALL packed weights resident in shared memory (24 KB per 16 input channels); wider Co = 32
+  // layers (none in the reference's stack) take the pixels-on-M kernel, which streams its weights per K-stage
+  return !off && mode == TC_S1 && CO == TCX_CO && CI <= 64 && (all || CI >= 64);
 }
 
 extern "C" size_t nconv_b200_tc_wpack_bytes(int mode, int CO, int CA, int CB, int has_1x1) {

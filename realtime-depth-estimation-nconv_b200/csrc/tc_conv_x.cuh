@@ -349,8 +349,8 @@ static TcxPlan tcx_plan(int AH, int AW, int nk) {
       int rows_alloc = (TCX_N + 2 * P + P - 1) / P;
       while ((rows_alloc * P * 16) % 128) ++rows_alloc;              // tensor copies want 128 B aligned planes
       const size_t stage = (size_t)4 * rows_alloc * P * 16;
+      if (fixed + 2 * stage > (size_t)TC_SMEM_MAX) continue;          // (also keeps the unsigned difference below from wrapping)
       int stages = (int)((TC_SMEM_MAX - fixed) / stage);
-      if (stages < 2) continue;
       if (stages > TCX_MAX_STAGES) stages = TCX_MAX_STAGES;
       const int tx = (AW + Wt - 1) / Wt, ty = (AH + R - 1) / R;
       // every tile costs the same MMA time; loads (halo rows re-read) weigh in lightly
