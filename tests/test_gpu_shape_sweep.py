@@ -241,3 +241,91 @@ def test_setp1_pipeline_random_sizes_tc_vs_fp32(seed):
         worst = max(worst, e)
         assert e <= 1e-4, ("setp1", seed, k, (B, H, W), e)
     report("shape_sweep_setp1_tc_vs_fp32_seed%d" % seed, worst_rel_floor1e3=worst, shapes=4)
+
+
+def _rel_scale(a, ref):
+    ref = ref.detach().double()
+    return float((a.detach().double() - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_training_kernels_random_shapes(seed):
+    """ops.conv_train / convT_train / bn_train (forward, data / weight / bias gradients; fp32 CUDA-core kernels plus the
+    tcgen05 data and weight gradients where the shape allows) through autograd at drawn shapes, against torch autograd in
+    fp64 on the same GPU.  Tolerances of test_gpu_parity.py: forward 1e-5 (2e-5 on tcgen05), gradients 2e-5 (3e-5 for a
+    tcgen05 data gradient) of each tensor's scale."""
+    from nconv_b200 import ops
+    rng = random.Random(6000 + seed)
+    torch.manual_seed(6000 + seed)
+    worst = 0.0
+    for k in range(6):
+        # ---- Conv2d K in {1, 3}, stride in {1, 2}, optional bias / ReLU
+        CI = rng.choice((1, 3, 16, 32, 33, 64, 65, 128))
+        CO = rng.choice((1, 32, 64)) if CI >= 16 else rng.choice((32, 64))
+        K, stride = rng.choice(((3, 1), (3, 1), (3, 2), (1, 1), (1, 2)))
+        if CO == 1:
+            stride = 1           # the stack's single-channel heads are stride 1; stride 2 needs Co % 16 == 0 (UNSUPPORTED otherwise)
+        relu, bias = rng.random() < 0.5, rng.random() < 0.6
+        B = rng.randint(1, 3)
+        H, W = rng.randint(4, 40), rng.randint(4, 90)
+        x = torch.rand(B, CI, H, W, device=dev()) * 4 - 1
+        w = (torch.rand(CO, CI, K, K, device=dev()) - 0.5) * 0.2
+        bb = torch.rand(CO, device=dev()) - 0.5 if bias else None
+        xr, wr = x.double().requires_grad_(True), w.double().requires_grad_(True)
+        br = bb.double().requires_grad_(True) if bias else None
+        yr = F.conv2d(xr, wr, br, stride=stride, padding=K // 2)
+        if relu:
+            yr = F.relu(yr)
+        G = torch.randn(yr.shape, device=dev())
+        (yr * G.double()).sum().backward()
+        xd, wd = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+        bd = bb.clone().requires_grad_(True) if bias else None
+        y = ops.conv_train(xd, wd, bd, None, stride, relu)
+        (y * G).sum().backward()
+        tag = ("conv", seed, k, (CI, CO, K, stride, relu, bias, B, H, W))
+        errs = [_rel_scale(y, yr), _rel_scale(wd.grad, wr.grad), _rel_scale(xd.grad, xr.grad)]
+        assert errs[0] <= 2e-5 and errs[1] <= 2e-5 and errs[2] <= 3e-5, (tag, errs)
+        if bias:
+            assert _rel_scale(bd.grad, br.grad) <= 2e-5, tag
+        worst = max(worst, *errs)
+        # ---- ConvTranspose2d(4, 2, 1)
+        CI, CO = rng.choice(((65, 64), (33, 32), (64, 64), (9, 16), (32, 32)))
+        B = rng.randint(1, 2)
+        H, W = rng.randint(2, 24), rng.randint(2, 40)
+        x = torch.rand(B, CI, H, W, device=dev()) * 2 - 0.5
+        w = (torch.rand(CI, CO, 4, 4, device=dev()) - 0.5) * 0.2
+        xr, wr = x.double().requires_grad_(True), w.double().requires_grad_(True)
+        yr = F.conv_transpose2d(xr, wr, None, stride=2, padding=1)
+        G = torch.randn(yr.shape, device=dev())
+        (yr * G.double()).sum().backward()
+        xd, wd = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+        y = ops.convT_train(xd, wd)
+        (y * G).sum().backward()
+        errs = [_rel_scale(y, yr), _rel_scale(wd.grad, wr.grad), _rel_scale(xd.grad, xr.grad)]
+        assert errs[0] <= 1e-5 and errs[1] <= 2e-5 and errs[2] <= 2e-5, (("convT", seed, k, (CI, CO, B, H, W)), errs)
+        worst = max(worst, *errs)
+        # ---- BatchNorm2d, batch statistics (+ReLU), un-normalised inputs
+        C = rng.choice((8, 32, 64))
+        B = rng.randint(2, 4)
+        H, W = rng.randint(3, 30), rng.randint(3, 50)
+        relu = rng.random() < 0.7
+        z = torch.randn(B, C, H, W, device=dev()) * 3 + 20
+        bn = torch.nn.BatchNorm2d(C).to(dev()).train()
+        with torch.no_grad():
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-1, 1)
+        bn64 = torch.nn.BatchNorm2d(C).to(dev()).double().train()
+        bn64.load_state_dict({k2: (v.double() if v.is_floating_point() else v) for k2, v in bn.state_dict().items()})
+        zr = z.double().requires_grad_(True)
+        yr = bn64(zr)
+        if relu:
+            yr = F.relu(yr)
+        G = torch.randn(yr.shape, device=dev())
+        (yr * G.double()).sum().backward()
+        zd = z.clone().requires_grad_(True)
+        y = ops.bn_train(zd, bn, None, relu)
+        (y * G).sum().backward()
+        errs = [_rel_scale(y, yr), _rel_scale(zd.grad, zr.grad), _rel_scale(bn.weight.grad, bn64.weight.grad),
+                _rel_scale(bn.bias.grad, bn64.bias.grad), _rel_scale(bn.running_var, bn64.running_var)]
+        assert max(errs) <= 2e-5, (("bn", seed, k, (B, C, H, W, relu)), errs)
+        worst = max(worst, *errs)
+    report("shape_sweep_training_kernels_seed%d" % seed, worst_rel=worst, shapes=18)
