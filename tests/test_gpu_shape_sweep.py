@@ -329,3 +329,43 @@ def test_training_kernels_random_shapes(seed):
         assert max(errs) <= 2e-5, (("bn", seed, k, (B, C, H, W, relu)), errs)
         worst = max(worst, *errs)
     report("shape_sweep_training_kernels_seed%d" % seed, worst_rel=worst, shapes=18)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_nconv2d_layer_random_shapes(seed):
+    """torch.ops.nconv_b200.nconv2d forward + backward (the stream / tiled / pipelined / generic fp32 kernels behind one
+    dispatcher, incl. the single-pass k3 and k5 backward) at drawn (Ci, Co, k, B, H, W): widths that are and are not
+    multiples of 4 (vector and scalar paths), frames smaller than a tile, exact-zero confidences.  Checker: the layer's
+    formula (step1.py:116-149) through torch autograd in fp64 on the same GPU.  y / cout max-rel 1e-4 at the 1e-3 floor,
+    gradients 1e-4 of each tensor's scale (the bounds of test_gpu_parity.py)."""
+    from nconv_b200 import ops  # noqa: F401  (registers torch.ops.nconv_b200.*)
+    K = torch.ops.nconv_b200
+    rng = random.Random(7000 + seed)
+    torch.manual_seed(7000 + seed)
+    worst_f = worst_g = 0.0
+    for k_ in range(8):
+        ci, co, k = rng.choice(((1, 2, 3), (2, 2, 3), (4, 4, 3), (16, 16, 3), (1, 2, 5), (2, 2, 5), (4, 4, 5), (16, 16, 5),
+                                (1, 8, 5), (8, 8, 5), (16, 8, 3), (3, 5, 3), (8, 1, 1)))
+        pad = rng.choice((k // 2, k // 2, 0)) if k > 1 else rng.choice((0, 2))
+        B = rng.randint(1, 3)
+        H, W = rng.randint(max(k, 3), 70), rng.choice((rng.randint(max(k, 3), 150), 4 * rng.randint(2, 40)))
+        x = torch.rand(B, ci, H, W, device=dev()) * 10
+        c = torch.rand(B, ci, H, W, device=dev()) * (torch.rand(B, ci, H, W, device=dev()) < 0.5)
+        w = F.softplus(torch.rand(co, ci, k, k, device=dev()), beta=10)
+        b = torch.rand(co, device=dev()) * 0.1
+        xr, cr, wr, br = (t.double().requires_grad_(True) for t in (x, c, w, b))
+        denom = F.conv2d(cr, wr, padding=pad)
+        yr = F.conv2d(xr * cr, wr, padding=pad) / (denom + 1e-7) + br.view(1, -1, 1, 1)
+        cor = denom / wr.sum((1, 2, 3)).view(1, -1, 1, 1)
+        gy, gc = torch.randn(yr.shape, device=dev()), torch.randn(yr.shape, device=dev())
+        ((yr * gy.double()).sum() + (cor * gc.double()).sum()).backward()
+        xg, cg, wg, bg = (t.clone().requires_grad_(True) for t in (x, c, w, b))
+        y, cout = K.nconv2d(xg, cg, wg, bg, pad, pad, 1e-7)
+        ((y * gy).sum() + (cout * gc).sum()).backward()
+        tag = (seed, k_, (ci, co, k, pad, B, H, W))
+        ef = max(_rel_floor(y, yr.detach()), _rel_floor(cout, cor.detach()))
+        assert ef <= 1e-4, ("fwd", tag, ef)
+        eg = max(_rel_scale(xg.grad, xr.grad), _rel_scale(cg.grad, cr.grad), _rel_scale(wg.grad, wr.grad), _rel_scale(bg.grad, br.grad))
+        assert eg <= 1e-4, ("bwd", tag, eg)
+        worst_f, worst_g = max(worst_f, ef), max(worst_g, eg)
+    report("shape_sweep_nconv2d_layer_seed%d" % seed, worst_fwd_rel_floor1e3=worst_f, worst_grad_rel=worst_g, shapes=8)
