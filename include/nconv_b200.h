@@ -299,6 +299,16 @@ int nconv_b200_p8_unpack(const void* p8, float* x, int B, int C, int H, int W, v
  * in blocks of 64 input channels: no concatenation pass afterwards) */
 int nconv_b200_p8_unpack_into(const void* p8, float* x, int B, int C, int H, int W, int Ctot, int c0, void* stream);
 int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream);
+/* pack from a channel sub-range of x [B][Ctot][..][..] (channels c0 .. c0+C), optionally with the 2x2 spatial phases of a
+ * [2H][2W] source moved to channels (phases != 0: the P8 tensor has 4*C channels of H x W, channel (py*2+px)*C + c at (i, j)
+ * = x[c0+c][2i+py][2j+px]; C % 8 == 0).  With the two weight helpers below this turns the backward of Basic2dTrans'
+ * ConvTranspose2d(4, 2, 1) (step2.py:197-214 under train_step2.py:62-64) into 3x3 / stride-1 problems for the tcgen05
+ * kernels: data gradient = conv3x3(phases(gy), w3), weight gradient = wgrad3x3(phases(gy), x) gathered back. */
+int nconv_b200_p8_pack_ex(const float* x, void* p8, int B, int C, int H, int W, int Ctot, int c0, int phases, void* stream);
+/* w [CI][CO][4][4] (ConvTranspose2d layout) -> w3 [CI][4*CO][3][3] */
+int nconv_b200_convT_phase_weights(const float* w, float* w3, int CI, int CO, void* stream);
+/* gw3 [CIF][4*CO][3][3] -> gw [lead + CIF][CO][4][4], rows lead .. lead+CIF (the first `lead` rows are left alone) */
+int nconv_b200_convT_phase_wgrad(const float* gw3, float* gw, int CIF, int CO, int lead, void* stream);
 /* Backward of ReLU(conv + bias) (step2.py:290-297 under train_step2.py:62-64) written straight into P8 for the tcgen05
  * data / weight gradient kernels: p8 = P8(gy * [y > 0]) (y null: no mask), gbias[c] = per-channel sum of the masked
  * gradient (null: not wanted).  ws: C doubles of scratch when gbias is given.  gy, y: fp32 NCHW [B,C,H,W]. */

@@ -70,6 +70,72 @@ __global__ void __launch_bounds__(PK_THREADS) p8_pack_kernel(const float* __rest
   }
 }
 
+// fp32 NCHW -> P8 from a channel sub-range and / or with the 2x2 spatial phases moved to channels (training backward of the
+// transposed convolutions, ops.py::_ConvTTrain.backward):
+//   PHASES = false: p8[n][c][i][j]              = x[n][c0 + c][i][j]                       x: [B][Ctot][H][W]
+//   PHASES = true : p8[n][(py*2+px)*C + c][i][j] = x[n][c0 + c][2i + py][2j + px]           x: [B][Ctot][2H][2W], p8: 4C channels
+// (C a multiple of 8 with PHASES, so a chunk of 8 output channels lies in one phase.)
+template <bool PHASES>
+__global__ void __launch_bounds__(PK_THREADS) p8_pack_ex_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ p8, int B, int C,
+                                                                int H, int W, int Ctot, int c0) {
+  const int CP = PHASES ? 4 * C : C;                             // channels of the P8 tensor
+  const P8Geom g = P8Geom::make(B, CP, H, W);
+  const int xx = blockIdx.x * PK_THREADS + threadIdx.x;          // padded column
+  const int ch = blockIdx.z % g.C8, n = blockIdx.z / g.C8;
+  const int y0 = blockIdx.y * PK_ROWS;
+  if (xx >= g.Wp) return;
+  const int ph = PHASES ? (ch * 8) / C : 0, cb = PHASES ? ch * 8 - ph * C : ch * 8;
+  const int py = ph >> 1, px = ph & 1;
+  const int Hs = PHASES ? 2 * H : H, Ws = PHASES ? 2 * W : W;
+#pragma unroll 2
+  for (int yy = y0; yy < y0 + PK_ROWS && yy < g.Hp; ++yy) {
+    float f[8];
+    const bool inside = yy >= 1 && yy <= H && xx >= 1 && xx <= W;
+    const int sy = PHASES ? 2 * (yy - 1) + py : yy - 1, sx = PHASES ? 2 * (xx - 1) + px : xx - 1;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = cb + e;
+      const bool ok = inside && c < C;
+      f[e] = ok ? __ldg(x + (((size_t)n * Ctot + c0 + c) * Hs + sy) * Ws + sx) : 0.f;
+    }
+    uint4 hi, lo;
+    split8_fast(f, hi, lo);
+    const size_t off = ((size_t)yy * g.Wp + xx) * 8;
+    *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 0) + off) = hi;
+    *reinterpret_cast<uint4*>(p8 + g.plane(n, ch, 1) + off) = lo;
+  }
+}
+
+// ConvTranspose2d(4, 2, 1) as a 3x3 / stride-1 convolution over the phase-split output gradient (see ops.py):
+//   w3[ci][(py*2+px)*CO + co][r][s] = w[ci][co][u][v]  with  py = 1: r = 0 -> u = 0, r = 1 -> u = 2;  py = 0: r = 1 -> u = 1,
+//   r = 2 -> u = 3 (same for px, s, v); every other entry 0.   w: [CI][CO][4][4], w3: [CI][4*CO][3][3]
+__device__ __forceinline__ int ctp_tap(int p, int r) { return p ? (r == 0 ? 0 : (r == 1 ? 2 : -1)) : (r == 1 ? 1 : (r == 2 ? 3 : -1)); }
+
+__global__ void convT_phase_weights_kernel(const float* __restrict__ w, float* __restrict__ w3, int CI, int CO) {
+  const int total = CI * 4 * CO * 9;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int s = idx % 3, r = (idx / 3) % 3;
+    int q = idx / 9;
+    const int co = q % CO; q /= CO;
+    const int ph = q % 4, ci = q / 4;
+    const int u = ctp_tap(ph >> 1, r), v = ctp_tap(ph & 1, s);
+    w3[idx] = (u >= 0 && v >= 0) ? __ldg(w + (((size_t)ci * CO + co) * 4 + u) * 4 + v) : 0.f;
+  }
+}
+
+// the inverse gather for the weight gradient: gw[lead + ci][co][u][v] = gw3[ci][(py*2+px)*CO + co][r][s]
+// gw3: [CIF][4*CO][3][3] (CIF = the CI - lead feature channels), gw: [CIF + lead][CO][4][4]
+__global__ void convT_phase_wgrad_kernel(const float* __restrict__ gw3, float* __restrict__ gw, int CIF, int CO, int lead) {
+  const int total = CIF * CO * 16;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int v = idx & 3, u = (idx >> 2) & 3;
+    const int co = (idx >> 4) % CO, ci = (idx >> 4) / CO;
+    const int py = (u & 1) ? 0 : 1, px = (v & 1) ? 0 : 1;            // u = 0, 2: odd rows (py = 1); u = 1, 3: even rows
+    const int r = py ? (u == 0 ? 0 : 1) : (u == 1 ? 1 : 2), s = px ? (v == 0 ? 0 : 1) : (v == 1 ? 1 : 2);
+    gw[(((size_t)(lead + ci)) * CO + co) * 16 + u * 4 + v] = __ldg(gw3 + (((size_t)ci * 4 * CO + (py * 2 + px) * CO + co) * 3 + r) * 3 + s);
+  }
+}
+
 // P8 -> fp32 NCHW; the C channels land at channel offset c0 of a [B, Ctot, H, W] tensor (Ctot = C, c0 = 0: a plain unpack)
 __global__ void __launch_bounds__(PK_THREADS) p8_unpack_kernel(const __nv_bfloat16* __restrict__ p8, float* __restrict__ x, int B, int C,
                                                                int H, int W, int Ctot, int c0) {
@@ -166,6 +232,41 @@ extern "C" int nconv_b200_p8_unpack_into(const void* p8, float* x, int B, int C,
   {
     LaunchScope ls((cudaStream_t)stream, "p8_unpack", 0.0, 8.0 * B * C * H * W);
     p8_unpack_kernel<<<grid, PK_THREADS, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)p8, x, B, C, H, W, Ctot, c0);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_p8_pack_ex(const float* x, void* p8, int B, int C, int H, int W, int Ctot, int c0, int phases, void* stream) {
+  if (!x || !p8 || B <= 0 || C <= 0 || H <= 0 || W <= 0 || c0 < 0 || c0 + C > Ctot) return NCONV_ERR_BAD_ARG;
+  if (phases && (C % 8)) return NCONV_ERR_UNSUPPORTED;
+  const P8Geom g = P8Geom::make(B, phases ? 4 * C : C, H, W);
+  if ((long long)B * g.C8 > 65535) return NCONV_ERR_UNSUPPORTED;
+  dim3 grid((g.Wp + PK_THREADS - 1) / PK_THREADS, (g.Hp + PK_ROWS - 1) / PK_ROWS, B * g.C8);
+  cudaStream_t st = (cudaStream_t)stream;
+  {
+    LaunchScope ls(st, phases ? "p8_pack_phases" : "p8_pack", 0.0, 8.0 * B * (phases ? 4.0 : 1.0) * C * H * W);
+    if (phases) p8_pack_ex_kernel<true><<<grid, PK_THREADS, 0, st>>>(x, (__nv_bfloat16*)p8, B, C, H, W, Ctot, c0);
+    else p8_pack_ex_kernel<false><<<grid, PK_THREADS, 0, st>>>(x, (__nv_bfloat16*)p8, B, C, H, W, Ctot, c0);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_convT_phase_weights(const float* w, float* w3, int CI, int CO, void* stream) {
+  if (!w || !w3 || CI <= 0 || CO <= 0) return NCONV_ERR_BAD_ARG;
+  const int total = CI * 4 * CO * 9;
+  {
+    LaunchScope ls((cudaStream_t)stream, "convT_phase_weights", 0.0, 4.0 * (total + CI * CO * 16));
+    convT_phase_weights_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, w3, CI, CO);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_convT_phase_wgrad(const float* gw3, float* gw, int CIF, int CO, int lead, void* stream) {
+  if (!gw3 || !gw || CIF <= 0 || CO <= 0 || lead < 0) return NCONV_ERR_BAD_ARG;
+  const int total = CIF * CO * 16;
+  {
+    LaunchScope ls((cudaStream_t)stream, "convT_phase_wgrad", 0.0, 8.0 * total);
+    convT_phase_wgrad_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(gw3, gw, CIF, CO, lead);
   }
   return (int)cudaGetLastError();
 }

@@ -120,6 +120,9 @@ SIGNATURES = {
     "nconv_b200_p8_zero_ring": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p]),
     "nconv_b200_relu_bias_bwd_p8": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "nconv_b200_p8_unpack_into": (c_int, [c_void_p] * 2 + [c_int] * 6 + [c_void_p]),
+    "nconv_b200_p8_pack_ex": (c_int, [c_void_p] * 2 + [c_int] * 7 + [c_void_p]),
+    "nconv_b200_convT_phase_weights": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
+    "nconv_b200_convT_phase_wgrad": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
     "nconv_b200_p8q_bytes": (c_size_t, [c_int] * 4),
     "nconv_b200_p8q_zero_ring": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p]),
     "nconv_b200_p8q_pack": (c_int, [c_void_p, c_void_p] + [c_int] * 4 + [c_void_p]),

@@ -506,6 +506,21 @@ class P8:
                 check(_C.nconv_b200_p8q_pack(_p(x), _p(t.qbuf), B, C, H, W, _stream(x)), "p8q_pack")
         return t
 
+    @staticmethod
+    def pack_ex(x, c0: int = 0, C=None, phases: bool = False):
+        """Pack channels [c0, c0+C) of x; with `phases` the 2x2 spatial phases of x [B, Ctot, 2H, 2W] become channels: a P8
+        tensor of 4*C channels of H x W with channel (py*2+px)*C + c at (i, j) = x[c0+c, 2i+py, 2j+px]."""
+        x = _prep(x, "x")
+        B, Ctot, Hs, Ws = x.shape
+        C = Ctot - c0 if C is None else C
+        if phases and ((Hs | Ws) & 1):
+            raise ValueError("pack_ex: phases need even H and W")
+        H, W = (Hs // 2, Ws // 2) if phases else (Hs, Ws)
+        t = P8.empty(B, 4 * C if phases else C, H, W, x.device, zero_ring=False)
+        with torch.cuda.device(x.device):
+            check(_C.nconv_b200_p8_pack_ex(_p(x), _p(t.buf), B, C, H, W, Ctot, int(c0), int(phases), _stream(x)), "p8_pack_ex")
+        return t
+
     def unpack_into(self, x, c0: int):
         """Write the C channels at channel offset c0 of the contiguous fp32 tensor x [B, Ctot, H, W]."""
         if x.dtype != torch.float32 or not x.is_contiguous() or x.shape[0] != self.B or tuple(x.shape[2:]) != (self.H, self.W):
@@ -831,6 +846,7 @@ import os as _os
 _TRAIN_TC = _os.environ.get("NCONV_B200_TRAIN_NO_TC") is None
 _TRAIN_TC_FWD = _TRAIN_TC and _os.environ.get("NCONV_B200_TRAIN_TC_FWD") is not None
 _TRAIN_TC_WGRAD = _os.environ.get("NCONV_B200_TRAIN_NO_TC_WGRAD") is None      # weight gradients on tcgen05 (csrc/wgrad_tc.cu)
+_TRAIN_TC_CONVT = _os.environ.get("NCONV_B200_TRAIN_NO_TC_CONVT") is None      # transposed-conv gradients on tcgen05 (phase split)
 
 
 def _tc_train_ok(ci: int, co: int, K: int, stride: int) -> bool:
@@ -973,6 +989,51 @@ class _ConvTTrain(torch.autograd.Function):
             g2, gb = _relu_bias_bwd(gy, y, relu, want_g=relu, want_bias=has_bias and ctx.needs_input_grad[2])
             if relu:
                 gy = g2
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        lead = CI % 32                                            # the depth channel of cat[depth, features] (step2.py:174), or 0
+        CF = CI - lead
+        if _TRAIN_TC and _TRAIN_TC_CONVT and (need_x or need_w) and lead in (0, 1) and CF in (32, 64) and CO in (32, 64):
+            # Both gradients as 3x3 / stride-1 problems on tcgen05.  The output gradient gy [B,CO,2H,2W] is packed with its
+            # 2x2 phases as channels, P [B,4CO,H,W]: gy[2i+u-1, 2j+v-1] is phase (u odd ? 0 : 1) at row i + {-1, 0, +1}, so
+            #   gx[ci]          = conv3x3(P, w3)[ci]               w3[ci][(p, co)][r][s] = w[ci][co][u][v] or 0
+            #   gw3[ci][(p,co)] = wgrad3x3(input P, out-grad x)    gathered back to gw[ci][co][u][v]
+            # 16 of the 36 taps are zero (2.25x the needed MMAs), still ~6x faster than the CUDA-core gather / split-K kernels.
+            # The lone depth channel (Ci = 65 / 33) stays on those, restricted to that channel.
+            dev = x.device
+            P = P8.pack_ex(gy, phases=True)
+            if need_x:
+                gx = torch.empty_like(x)
+                w3 = torch.empty((CF, 4 * CO, 3, 3), device=dev, dtype=torch.float32)
+                wf = weight[lead:] if lead == 0 else weight[lead:].contiguous()
+                with torch.cuda.device(dev):
+                    check(_C.nconv_b200_convT_phase_weights(_p(wf), _p(w3), CF, CO, _stream(x)), "convT_phase_weights")
+                wpk = tc_pack_weights(TC_S1, w3, 4 * CO, 0)
+                if not conv_tc_f32(P, wpk, CF, gx, lead):
+                    conv_tc(TC_S1, P, None, wpk, CF, None, None, False).unpack_into(gx, lead)
+                if lead:
+                    g0 = torch.empty((B, lead, H, W), device=dev, dtype=torch.float32)
+                    w0 = weight[:lead].contiguous()
+                    ws = _scratch(dev, int(_C.nconv_b200_conv_dgrad_ws_bytes(lead, CO, 4)))
+                    with torch.cuda.device(dev):
+                        check(_C.nconv_b200_conv_dgrad_gather(_p(gy), _p(w0), _p(g0), _p(ws), B, lead, CO, H, W, 4, 2, 1, 1,
+                                                              _stream(x)), "conv_dgrad_gatherT")
+                    gx[:, :lead].copy_(g0)
+            if need_w:
+                gw = torch.empty_like(weight)
+                gw3 = _conv_wgrad_tc(P, P8.pack_ex(x, c0=lead, C=CF))          # [CF][4CO][3][3]
+                with torch.cuda.device(dev):
+                    check(_C.nconv_b200_convT_phase_wgrad(_p(gw3), _p(gw), CF, CO, lead, _stream(x)), "convT_phase_wgrad")
+                if lead:
+                    # the depth channel's 16*CO weight gradients: the same tensor-core problem with the channel padded to a
+                    # block of 32 (31 zero channels ride along; the split-K CUDA-core kernel took 0.4-1.3 ms per layer here)
+                    xl = torch.zeros((B, 32, H, W), device=dev, dtype=torch.float32)
+                    xl[:, :lead].copy_(x[:, :lead])
+                    gl3 = _conv_wgrad_tc(P, P8.pack(xl))                      # [32][4CO][3][3], rows >= lead are zero
+                    gl = torch.empty((32, CO, 4, 4), device=dev, dtype=torch.float32)
+                    with torch.cuda.device(dev):
+                        check(_C.nconv_b200_convT_phase_wgrad(_p(gl3), _p(gl), 32, CO, 0, _stream(x)), "convT_phase_wgrad")
+                    gw[:lead].copy_(gl[:lead])
+            return gx, gw, gb, None
         if ctx.needs_input_grad[1]:
             # roles swapped: "input" = gy [B,CO,2H,2W], "output gradient" = x [B,CI,H,W]  ->  [CI][CO][4][4]
             gw = _conv_wgrad(x, gy, 4, 2, 1)

@@ -144,7 +144,7 @@ def main():
         for label, kms, fl, by_ in records:
             key = label.split(" @")[0]
             d = by.setdefault(key, [0.0, 0, 0.0]); d[0] += kms; d[1] += 1; d[2] += fl
-        top = sorted(by.items(), key=lambda kv: -kv[1][0])[:32]
+        top = sorted(by.items(), key=lambda kv: -kv[1][0])[:56]
         print(json.dumps({
             "metric": "setp1+setp2_training_frames_per_s_480x640", "value": args.frames * world * args.steps / (ms / 1e3),
             "unit": "frames/s", "n_gpus": world, "steps": args.steps, "ms_per_step": ms / args.steps,
