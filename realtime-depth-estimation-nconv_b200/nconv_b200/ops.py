@@ -1011,13 +1011,18 @@ class _ConvTTrain(torch.autograd.Function):
                 if not conv_tc_f32(P, wpk, CF, gx, lead):
                     conv_tc(TC_S1, P, None, wpk, CF, None, None, False).unpack_into(gx, lead)
                 if lead:
-                    g0 = torch.empty((B, lead, H, W), device=dev, dtype=torch.float32)
-                    w0 = weight[:lead].contiguous()
-                    ws = _scratch(dev, int(_C.nconv_b200_conv_dgrad_ws_bytes(lead, CO, 4)))
+                    # the depth channel: the same conv with its weight row padded to a block of 32 output channels (31 zero
+                    # rows; the one-channel CUDA-core gather took 0.45-0.5 ms per layer)
+                    wl = torch.zeros((32, CO, 4, 4), device=dev, dtype=torch.float32)
+                    wl[:lead].copy_(weight[:lead])
+                    w3l = torch.empty((32, 4 * CO, 3, 3), device=dev, dtype=torch.float32)
                     with torch.cuda.device(dev):
-                        check(_C.nconv_b200_conv_dgrad_gather(_p(gy), _p(w0), _p(g0), _p(ws), B, lead, CO, H, W, 4, 2, 1, 1,
-                                                              _stream(x)), "conv_dgrad_gatherT")
-                    gx[:, :lead].copy_(g0)
+                        check(_C.nconv_b200_convT_phase_weights(_p(wl), _p(w3l), 32, CO, _stream(x)), "convT_phase_weights")
+                    g0 = torch.empty((B, 32, H, W), device=dev, dtype=torch.float32)
+                    wpl = tc_pack_weights(TC_S1, w3l, 4 * CO, 0)
+                    if not conv_tc_f32(P, wpl, 32, g0, 0):
+                        conv_tc(TC_S1, P, None, wpl, 32, None, None, False).unpack_into(g0, 0)
+                    gx[:, :lead].copy_(g0[:, :lead])
             if need_w:
                 gw = torch.empty_like(weight)
                 gw3 = _conv_wgrad_tc(P, P8.pack_ex(x, c0=lead, C=CF))          # [CF][4CO][3][3]
