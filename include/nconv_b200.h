@@ -305,6 +305,12 @@ int nconv_b200_p8_zero_ring(void* p8, int B, int C, int H, int W, void* stream);
  * ConvTranspose2d(4, 2, 1) (step2.py:197-214 under train_step2.py:62-64) into 3x3 / stride-1 problems for the tcgen05
  * kernels: data gradient = conv3x3(phases(gy), w3), weight gradient = wgrad3x3(phases(gy), x) gathered back. */
 int nconv_b200_p8_pack_ex(const float* x, void* p8, int B, int C, int H, int W, int Ctot, int c0, int phases, void* stream);
+/* The same device for the backward of a 3x3 / stride-2 / pad-1 Conv2d (RGBEncoder, step2.py:134-154): x[2i+u-1] is phase
+ * (u odd ? 0 : 1) of x at row i + {-1, 0}, so  weight gradient = wgrad3x3(phases(x), gy) gathered back (convS2_phase_wgrad),
+ * data gradient, phase by phase, = conv3x3(gy, w3d) with w3d from convS2_phase_weights, stored interleaved (y_phase_c).
+ *   w [CO][CI][3][3] -> w3d [4*CI][CO][3][3];   gw3 [CO][4*CI][3][3] -> gw [CO][CI][3][3] */
+int nconv_b200_convS2_phase_weights(const float* w, float* w3d, int CO, int CI, void* stream);
+int nconv_b200_convS2_phase_wgrad(const float* gw3, float* gw, int CO, int CI, void* stream);
 /* w [CI][CO][4][4] (ConvTranspose2d layout) -> w3 [CI][4*CO][3][3] */
 int nconv_b200_convT_phase_weights(const float* w, float* w3, int CI, int CO, void* stream);
 /* gw3 [CIF][4*CO][3][3] -> gw [lead + CIF][CO][4][4], rows lead .. lead+CIF (the first `lead` rows are left alone) */
@@ -349,6 +355,10 @@ typedef struct {
                            contiguous [B][y_ctot][H][W] tensor (the data gradient of train_step2.py:62-64's backward);
                            NCONV_B200_ERR_UNSUPPORTED for CO = 32 with CA+CB >= 64 (that shape's kernel writes P8 only) */
   int y_ctot, y_c0;
+  int y_phase_c;        /* with y_f32, > 0: the CO output channels are phase-major, channel (py*2+px)*y_phase_c + c, and are
+                           written interleaved into y_f32 = [B][y_phase_c][2H][2W] at [c][2y+py][2x+px] (the data gradient of a
+                           3x3 / stride-2 convolution computed as a stride-1 convolution of its output gradient); y_c0 = first
+                           phase-major channel of this launch, y_phase_c % 32 == 0, y_c0 % 32 == 0; y_ctot unused */
 } nconv_b200_tc_desc;
 int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream);
 

@@ -136,6 +136,34 @@ __global__ void convT_phase_wgrad_kernel(const float* __restrict__ gw3, float* _
   }
 }
 
+// 3x3 / stride-2 / pad-1 Conv2d backward through the same phase split (include/nconv_b200.h):
+//   w3d[(a*2+b)*CI + ci][co][r][s] = w[co][ci][u][v]   a = 0: r = 1 -> u = 1;  a = 1: r = 1 -> u = 2, r = 2 -> u = 0
+__device__ __forceinline__ int cs2_dtap(int a, int r) { return a ? (r == 1 ? 2 : (r == 2 ? 0 : -1)) : (r == 1 ? 1 : -1); }
+
+__global__ void convS2_phase_weights_kernel(const float* __restrict__ w, float* __restrict__ w3d, int CO, int CI) {
+  const int total = 4 * CI * CO * 9;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int s = idx % 3, r = (idx / 3) % 3;
+    int q = idx / 9;
+    const int co = q % CO; q /= CO;
+    const int ci = q % CI, ph = q / CI;
+    const int u = cs2_dtap(ph >> 1, r), v = cs2_dtap(ph & 1, s);
+    w3d[idx] = (u >= 0 && v >= 0) ? __ldg(w + (((size_t)co * CI + ci) * 3 + u) * 3 + v) : 0.f;
+  }
+}
+
+//   gw[co][ci][u][v] = gw3[co][(py*2+px)*CI + ci][r][s]   u = 0: py = 1, r = 0;  u = 1: py = 0, r = 1;  u = 2: py = 1, r = 1
+__global__ void convS2_phase_wgrad_kernel(const float* __restrict__ gw3, float* __restrict__ gw, int CO, int CI) {
+  const int total = CO * CI * 9;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int v = idx % 3, u = (idx / 3) % 3;
+    const int ci = (idx / 9) % CI, co = idx / (9 * CI);
+    const int py = (u == 1) ? 0 : 1, px = (v == 1) ? 0 : 1;
+    const int r = (u == 0) ? 0 : 1, s = (v == 0) ? 0 : 1;
+    gw[idx] = __ldg(gw3 + (((size_t)co * 4 * CI + (py * 2 + px) * CI + ci) * 3 + r) * 3 + s);
+  }
+}
+
 // P8 -> fp32 NCHW; the C channels land at channel offset c0 of a [B, Ctot, H, W] tensor (Ctot = C, c0 = 0: a plain unpack)
 __global__ void __launch_bounds__(PK_THREADS) p8_unpack_kernel(const __nv_bfloat16* __restrict__ p8, float* __restrict__ x, int B, int C,
                                                                int H, int W, int Ctot, int c0) {
@@ -247,6 +275,26 @@ extern "C" int nconv_b200_p8_pack_ex(const float* x, void* p8, int B, int C, int
     LaunchScope ls(st, phases ? "p8_pack_phases" : "p8_pack", 0.0, 8.0 * B * (phases ? 4.0 : 1.0) * C * H * W);
     if (phases) p8_pack_ex_kernel<true><<<grid, PK_THREADS, 0, st>>>(x, (__nv_bfloat16*)p8, B, C, H, W, Ctot, c0);
     else p8_pack_ex_kernel<false><<<grid, PK_THREADS, 0, st>>>(x, (__nv_bfloat16*)p8, B, C, H, W, Ctot, c0);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_convS2_phase_weights(const float* w, float* w3d, int CO, int CI, void* stream) {
+  if (!w || !w3d || CI <= 0 || CO <= 0) return NCONV_ERR_BAD_ARG;
+  const int total = 4 * CI * CO * 9;
+  {
+    LaunchScope ls((cudaStream_t)stream, "convS2_phase_weights", 0.0, 4.0 * (total + CI * CO * 9));
+    convS2_phase_weights_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, w3d, CO, CI);
+  }
+  return (int)cudaGetLastError();
+}
+
+extern "C" int nconv_b200_convS2_phase_wgrad(const float* gw3, float* gw, int CO, int CI, void* stream) {
+  if (!gw3 || !gw || CI <= 0 || CO <= 0) return NCONV_ERR_BAD_ARG;
+  const int total = CO * CI * 9;
+  {
+    LaunchScope ls((cudaStream_t)stream, "convS2_phase_wgrad", 0.0, 8.0 * total);
+    convS2_phase_wgrad_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(gw3, gw, CO, CI);
   }
   return (int)cudaGetLastError();
 }

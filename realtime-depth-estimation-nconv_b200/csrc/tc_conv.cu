@@ -115,6 +115,7 @@ struct TcArgs {
   __nv_bfloat16* outq;          // optional P8Q copy of the output
   float* out32;                 // S1 only: fp32 NCHW output instead of `out` (channels [o32_c0, o32_c0+CO) of a [B][o32_ctot][OH][OW] tensor)
   int o32_ctot, o32_c0;
+  int o32_phase_c;              // > 0: out32 is [B][phase_c][2*OH][2*OW] and output channel (py*2+px)*phase_c + c lands at [c][2y+py][2x+px]
   int B, AH, AW, OH, OW;        // anchor grid and output size
   int R, Wt, P, T, rows_alloc, rows_ld, G, ngrp, ntaps, ntaps_w;
   uint32_t P_magic;             // ceil(2^32 / P): m / P == __umulhi(m, P_magic) for m * P < 2^32 (no integer division in the epilogue)
@@ -321,8 +322,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
               // fp32 NCHW epilogue (the training data gradient, ops.py::_ConvTrain.backward): a lane owns one pixel, so every
               // channel's store is a 128-byte run across the warp; no P8 round trip through HBM
               if (valid && !(a.dbg & 1)) {
-                const size_t cs = (size_t)a.OH * a.OW;
+                size_t cs = (size_t)a.OH * a.OW;
                 float* ob = a.out32 + ((size_t)n * a.o32_ctot + a.o32_c0 + cb * 32) * cs + (size_t)oy * a.OW + ox;
+                if (a.o32_phase_c > 0) {
+                  // phase-major output channels -> the interleaved full-resolution tensor (data gradient of a stride-2 conv)
+                  const int chan = a.o32_c0 + cb * 32, ph = chan / a.o32_phase_c, cbase = chan - ph * a.o32_phase_c;
+                  cs *= 4;
+                  ob = a.out32 + ((size_t)n * a.o32_phase_c + cbase) * cs + (size_t)(2 * oy + (ph >> 1)) * (2 * a.OW) + 2 * ox + (ph & 1);
+                }
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
                   const int o = cb * 32 + e;
@@ -592,7 +599,9 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   if (d->B <= 0 || d->H <= 0 || d->W <= 0 || d->CA <= 0 || d->CB < 0) return NCONV_ERR_BAD_ARG;
   if (d->mode < 0 || d->mode > 2) return NCONV_ERR_BAD_ARG;
   if (d->y_f32) {
-    if (d->mode != TC_S1 || d->yq || d->y_c0 < 0 || d->y_c0 + d->CO > d->y_ctot) return NCONV_ERR_BAD_ARG;
+    if (d->mode != TC_S1 || d->yq || d->y_c0 < 0) return NCONV_ERR_BAD_ARG;
+    if (d->y_phase_c > 0 ? ((d->y_phase_c % 32) || (d->y_c0 % 32) || d->y_c0 + d->CO > 4 * d->y_phase_c) : (d->y_c0 + d->CO > d->y_ctot))
+      return NCONV_ERR_BAD_ARG;
     if (tcx_on(d->mode, d->CO, d->CA + d->CB)) return NCONV_ERR_UNSUPPORTED;       // the pixels-on-N kernel writes P8 only
   }
   const int mode = d->mode;
@@ -639,7 +648,7 @@ extern "C" int nconv_b200_conv_tc(const nconv_b200_tc_desc* d, void* stream) {
   }
   a.wpack = (const __nv_bfloat16*)d->wpack; a.scale = d->scale; a.shift = d->shift;
   a.out = (__nv_bfloat16*)d->y; a.outq = (__nv_bfloat16*)d->yq;
-  a.out32 = d->y_f32; a.o32_ctot = d->y_ctot; a.o32_c0 = d->y_c0;
+  a.out32 = d->y_f32; a.o32_ctot = d->y_ctot; a.o32_c0 = d->y_c0; a.o32_phase_c = d->y_f32 ? d->y_phase_c : 0;
   a.B = d->B; a.AH = AH; a.AW = AW;
   a.OH = (mode == TC_T) ? 2 * d->H : AH; a.OW = (mode == TC_T) ? 2 * d->W : AW;
   a.R = p.R; a.Wt = p.Wt; a.P = p.P; a.T = p.T; a.rows_alloc = p.rows_alloc; a.rows_ld = p.rows_ld;

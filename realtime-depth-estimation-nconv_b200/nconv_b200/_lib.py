@@ -45,7 +45,7 @@ class TcDesc(Structure):
         ("y", c_void_p), ("yq", c_void_p),
         ("B", c_int), ("CA", c_int), ("CB", c_int), ("CO", c_int), ("H", c_int), ("W", c_int), ("relu", c_int),
         ("mode", c_int), ("has_1x1", c_int),
-        ("y_f32", c_void_p), ("y_ctot", c_int), ("y_c0", c_int),
+        ("y_f32", c_void_p), ("y_ctot", c_int), ("y_c0", c_int), ("y_phase_c", c_int),
     ]
 
 
@@ -122,6 +122,8 @@ SIGNATURES = {
     "nconv_b200_p8_unpack_into": (c_int, [c_void_p] * 2 + [c_int] * 6 + [c_void_p]),
     "nconv_b200_p8_pack_ex": (c_int, [c_void_p] * 2 + [c_int] * 7 + [c_void_p]),
     "nconv_b200_convT_phase_weights": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
+    "nconv_b200_convS2_phase_weights": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
+    "nconv_b200_convS2_phase_wgrad": (c_int, [c_void_p] * 2 + [c_int] * 2 + [c_void_p]),
     "nconv_b200_convT_phase_wgrad": (c_int, [c_void_p] * 2 + [c_int] * 3 + [c_void_p]),
     "nconv_b200_p8q_bytes": (c_size_t, [c_int] * 4),
     "nconv_b200_p8q_zero_ring": (c_int, [c_void_p] + [c_int] * 4 + [c_void_p]),

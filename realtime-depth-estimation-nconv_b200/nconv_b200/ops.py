@@ -568,21 +568,23 @@ def conv_tc(mode: int, a: "P8", b, wpack, CO: int, scale, shift, relu: bool, has
     else:
         pa, pb = _p(a.buf), None if b is None else _p(b.buf)
     d = TcDesc(pa, pb, _p(wpack), _p(scale), _p(shift), _p(y.buf), _p(y.qbuf), a.B, a.C, CB, CO, a.H, a.W,
-               int(relu), mode, int(has_1x1), None, 0, 0)
+               int(relu), mode, int(has_1x1), None, 0, 0, 0)
     with torch.cuda.device(a.buf.device):
         check(_C.nconv_b200_conv_tc(byref(d), _stream(a.buf)), "conv_tc")
     return y
 
 
-def conv_tc_f32(a: "P8", wpack, CO: int, out, c0: int = 0, shift=None, relu: bool = False):
+def conv_tc_f32(a: "P8", wpack, CO: int, out, c0: int = 0, shift=None, relu: bool = False, phase_c: int = 0):
     """3x3 / stride-1 conv of the P8 tensor `a` on tcgen05, written as fp32 into channels [c0, c0+CO) of the contiguous
     NCHW tensor `out` [B, Ctot, H, W] (no P8 round trip).  Returns False when the shape's kernel cannot (CO = 32 with >= 64
     input channels): the caller takes conv_tc(...).unpack_into(out, c0)."""
-    if out.dtype != torch.float32 or not out.is_contiguous() or out.shape[0] != a.B or tuple(out.shape[2:]) != (a.H, a.W):
-        raise ValueError("conv_tc_f32: out must be contiguous fp32 [B, Ctot, H, W] of the source's B, H, W")
+    want = (a.B, phase_c, 2 * a.H, 2 * a.W) if phase_c else (a.B, out.shape[1], a.H, a.W)
+    if out.dtype != torch.float32 or not out.is_contiguous() or tuple(out.shape) != want:
+        raise ValueError("conv_tc_f32: out must be contiguous fp32 [B, Ctot, H, W] of the source's B, H, W "
+                         "([B, phase_c, 2H, 2W] with phase_c: phase-major output channels stored interleaved)")
     shift = _prep_opt(shift, "shift")
     d = TcDesc(_p(a.buf), None, _p(wpack), None, _p(shift), None, None, a.B, a.C, 0, CO, a.H, a.W, int(relu), TC_S1, 0,
-               _p(out), int(out.shape[1]), int(c0))
+               _p(out), int(out.shape[1]), int(c0), int(phase_c))
     with torch.cuda.device(a.buf.device):
         rc = _C.nconv_b200_conv_tc(byref(d), _stream(a.buf))
     if rc == 100002:          # NCONV_B200_ERR_UNSUPPORTED
@@ -847,6 +849,7 @@ _TRAIN_TC = _os.environ.get("NCONV_B200_TRAIN_NO_TC") is None
 _TRAIN_TC_FWD = _TRAIN_TC and _os.environ.get("NCONV_B200_TRAIN_TC_FWD") is not None
 _TRAIN_TC_WGRAD = _os.environ.get("NCONV_B200_TRAIN_NO_TC_WGRAD") is None      # weight gradients on tcgen05 (csrc/wgrad_tc.cu)
 _TRAIN_TC_CONVT = _os.environ.get("NCONV_B200_TRAIN_NO_TC_CONVT") is None      # transposed-conv gradients on tcgen05 (phase split)
+_TRAIN_TC_S2 = _os.environ.get("NCONV_B200_TRAIN_NO_TC_S2") is None            # stride-2 3x3 gradients on tcgen05 (phase split)
 
 
 def _tc_train_ok(ci: int, co: int, K: int, stride: int) -> bool:
@@ -911,6 +914,31 @@ class _ConvTrain(torch.autograd.Function):
         tc_w = need_w and _tc_wgrad_ok(CI, CO, K, stride)
         tc_x = need_x and stride == 1 and blk != 0 and _tc_train_ok(CO, blk, K, 1)
         g8 = None
+        if (_TRAIN_TC and _TRAIN_TC_S2 and K == 3 and stride == 2 and CI in (32, 64) and CO in (32, 64)
+                and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and (need_x or need_w)):
+            # 3x3 / stride 2 (RGBEncoder): both gradients as stride-1 problems on tcgen05 through the 2x2 phase split
+            # (include/nconv_b200.h, convS2_phase_*): 9 of the 36 taps are non-zero, still ~4x faster than the CUDA-core kernels
+            dev = x.device
+            if relu or (has_bias and need_b):
+                g8, gb = _relu_bias_bwd_p8(gy, y if relu else None, want_bias=has_bias and need_b)
+            else:
+                g8 = P8.pack(gy)
+            gw = gx = None
+            if need_w:
+                gw3 = _conv_wgrad_tc(P8.pack_ex(x, phases=True), g8)                 # [CO][4CI][3][3]
+                gw = torch.empty_like(weight)
+                with torch.cuda.device(dev):
+                    check(_C.nconv_b200_convS2_phase_wgrad(_p(gw3), _p(gw), CO, CI, _stream(x)), "convS2_phase_wgrad")
+            if need_x:
+                w3d = torch.empty((4 * CI, CO, 3, 3), device=dev, dtype=torch.float32)
+                with torch.cuda.device(dev):
+                    check(_C.nconv_b200_convS2_phase_weights(_p(weight), _p(w3d), CO, CI, _stream(x)), "convS2_phase_weights")
+                gx = torch.empty_like(x)
+                for c0 in range(0, 4 * CI, 64):
+                    wpk = tc_pack_weights(TC_S1, w3d[c0:c0 + 64], CO, 0)
+                    if not conv_tc_f32(g8, wpk, 64, gx, c0, phase_c=CI):
+                        raise RuntimeError("conv_train: stride-2 data gradient: no fp32 epilogue for this shape")
+            return gx, gw, gb, (gy if (has_res and need_r) else None), None, None
         if (relu or (has_bias and need_b)) and (tc_w or not need_w) and (tc_x or not need_x) and (tc_w or tc_x):
             # every consumer of the masked gradient runs on tcgen05: mask, bias sum and P8 split in one pass (no fp32 copy)
             g8, gb = _relu_bias_bwd_p8(gy, y if relu else None, want_bias=has_bias and need_b)
