@@ -830,20 +830,20 @@ def _conv_wgrad(g, x, K: int, S: int, P: int):
     return gw
 
 
-# Training convolutions on the tensor cores.  The dense 3x3 / stride-1 layers of the RGB-guided stack (57 of the
-# 145 ms of a config-5 step as fp32 CUDA-core kernels at 40-50 TFLOP/s) run their forward and their data gradient
-# through the inference kernels (conv_tc: tcgen05, split-bf16 operands, fp32 accumulate, <= 2e-5 of the output scale):
-# the fp32 NCHW activation / gradient is packed to P8, convolved, and unpacked (two extra HBM passes per conv, ~10 % of
-# what the conv saves).  The weight gradient stays on the fp32 kernel.
-#   * data gradients: on by default (a gradient error of ~1e-5 per layer propagates linearly);
-#   * forward: OPT-IN with NCONV_B200_TRAIN_TC_FWD=1.  A training step of this stack is chaotic at the 1e-3 level (ReLU /
-#     BatchNorm chains on raw 0..255 RGB: the reference's own fp32 gradients are up to 1e-2 from its fp64 gradients), and a
-#     1e-6 forward perturbation moves one BatchNorm bias gradient to 3.03x the reference's own fp32-vs-fp64 distance,
-#     just outside the 3x bound the training-step parity test holds; with the fp32 forward the activations stay
-#     bit-identical to round 1's.  Measured on the golden training step with the tensor-core forward: gradient distances
-#     to fp64 at a median 2.5x (worst 18.6x) of the reference's own fp32 noise, 4 of 78 tensors closer than the reference
-#     (default: worst 2.57x, 37 of 78).  89.7 ms default / 69.1 ms opt-in per 16-frame step.
-#   * NCONV_B200_TRAIN_NO_TC=1 keeps everything fp32.
+# Training convolutions on the tensor cores.  The dense layers of the RGB-guided stack run their BACKWARD through
+# the tcgen05 kernels (split-bf16 operands, fp32 accumulation: <= 1e-5 of the gradient scale per layer, an error that
+# propagates linearly):
+#   * 3x3 / stride-1 data gradients  = conv_tc of the ReLU-masked output gradient with the flipped weights, fp32 NCHW epilogue;
+#   * 3x3 / stride-1 weight gradients = csrc/wgrad_tc.cu (MN-major operands over P8);
+#   * ConvTranspose2d(4, 2, 1) and 3x3 / stride-2 layers: the same two kernels after a 2x2 phase split of the strided tensor
+#     (P8.pack_ex(phases=True), convT_phase_* / convS2_phase_*);
+#   * the ReLU mask, the bias sum and the P8 split of the output gradient are one pass (relu_bias_bwd_p8).
+# The FORWARD stays on the fp32 CUDA-core kernels unless NCONV_B200_TRAIN_TC_FWD=1: a training step of this stack is chaotic
+# at the 1e-3 level (ReLU / BatchNorm chains on raw 0..255 RGB: the reference's own fp32 gradients are up to 1e-2 from its
+# fp64 gradients), and with the tensor-core forward the gradient distances to fp64 on the golden training step are a median
+# 2.5x (worst 18.6x) the reference's own fp32 noise, 4 of 78 tensors closer than the reference (default: worst 2.57x, 37 of
+# 78) -- outside the 3x bound the training-step parity test holds.  82.0 ms default / 61.2 ms opt-in per 16-frame step.
+# NCONV_B200_TRAIN_NO_TC=1 keeps everything fp32; NCONV_B200_TRAIN_NO_TC_{WGRAD,CONVT,S2}=1 switch single groups off (A/B).
 import os as _os
 _TRAIN_TC = _os.environ.get("NCONV_B200_TRAIN_NO_TC") is None
 _TRAIN_TC_FWD = _TRAIN_TC and _os.environ.get("NCONV_B200_TRAIN_TC_FWD") is not None
@@ -853,7 +853,7 @@ _TRAIN_TC_S2 = _os.environ.get("NCONV_B200_TRAIN_NO_TC_S2") is None            #
 
 
 def _tc_train_ok(ci: int, co: int, K: int, stride: int) -> bool:
-    # Co = 32 keeps its packed weights resident in shared memory (24 KB per 16 input channels): Ci <= 64
+    # (Co = 32 is limited to the reference's own widths; wider Co = 32 layers would run too, on the pixels-on-M kernel)
     return _TRAIN_TC and K == 3 and stride == 1 and ci % 16 == 0 and ((co == 64 and ci <= 256) or (co == 32 and ci <= 64))
 
 
