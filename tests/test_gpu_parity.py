@@ -942,3 +942,69 @@ def test_conv3x3_tc_fp32_output(cfg):
     assert bool((out[:, :8] == -3).all()) and bool((out[:, 8 + CO:] == -3).all())
     via_p8 = ops.conv_tc(TC_S1, x8, None, wp, CO, None, shift.to(dev()), False).unpack()
     assert O.max_rel_err(via_p8, got, floor=1e-6) <= 2.0 ** -16
+
+
+@pytest.mark.parametrize("cfg", [(2, 32, 8, 8, 12, 0, 1), (1, 65, 64, 6, 10, 1, 1), (2, 33, 32, 9, 7, 1, 0), (1, 16, 5, 4, 4, 3, 0), (1, 16, 8, 4, 4, 3, 1)])
+def test_p8_pack_ex_subrange_and_phases(cfg):
+    """P8.pack_ex: a channel sub-range of a wider tensor, and the 2x2 spatial phases moved to channels (the device behind
+    the transposed / stride-2 gradients on tcgen05): against plain indexing."""
+    from nconv_b200.ops import P8
+    B, Ctot, C, H, W, c0, phases = cfg
+    torch.manual_seed(sum(cfg))
+    if phases:
+        x = torch.randn(B, Ctot, 2 * H, 2 * W, device=dev())
+        ref = torch.cat([x[:, c0:c0 + C, py::2, px::2] for py in (0, 1) for px in (0, 1)], 1)
+    else:
+        x = torch.randn(B, Ctot, H, W, device=dev())
+        ref = x[:, c0:c0 + C]
+    t = P8.pack_ex(x, c0=c0, C=C, phases=bool(phases))
+    assert (t.B, t.C, t.H, t.W) == tuple(ref.shape)
+    assert O.max_rel_err(t.unpack(), ref, floor=1e-6) <= 2.0 ** -16
+    assert _ring_intact(t)
+
+
+@pytest.mark.parametrize("cfg", [(65, 64), (33, 32), (8, 16)])
+def test_phase_weight_maps_reproduce_the_strided_layers(cfg):
+    """convT_phase_weights / convS2_phase_weights and their inverse gathers, checked through the identities they encode, in
+    fp64 torch arithmetic on the mapped weights (no tensor-core kernel involved):
+      ConvTranspose2d(4,2,1): dL/dx = conv3x3(phases(gy), w3);   dL/dw = gather(wgrad3x3(phases(gy), x))
+      Conv2d(3, s2, p1)     : dL/dx (phase-major) = conv3x3(gy, w3d);   dL/dw = gather(wgrad3x3(phases(x), gy))"""
+    from nconv_b200 import _lib
+    from nconv_b200.ops import _p, _stream
+    C = _lib.load()
+    CI, CO = cfg
+    B, H, W = 2, 5, 6
+    torch.manual_seed(CI + CO)
+    def phases(t):
+        return torch.cat([t[:, :, py::2, px::2] for py in (0, 1) for px in (0, 1)], 1)
+    # ---- transposed conv
+    w = torch.randn(CI, CO, 4, 4, device=dev())
+    x = torch.randn(B, CI, H, W, device=dev(), dtype=torch.float64, requires_grad=True)
+    wd = w.double().requires_grad_(True)
+    gy = torch.randn(B, CO, 2 * H, 2 * W, device=dev(), dtype=torch.float64)
+    (F.conv_transpose2d(x, wd, stride=2, padding=1) * gy).sum().backward()
+    w3 = torch.empty(CI, 4 * CO, 3, 3, device=dev())
+    _lib.check(C.nconv_b200_convT_phase_weights(_p(w), _p(w3), CI, CO, _stream(w)), "convT_phase_weights")
+    gx = F.conv2d(phases(gy), w3.double(), padding=1)
+    assert float((gx - x.grad).abs().max()) <= 1e-5 * float(x.grad.abs().max())
+    w3g = torch.zeros(CI, 4 * CO, 3, 3, device=dev(), dtype=torch.float64, requires_grad=True)
+    (F.conv2d(phases(gy), w3g, padding=1) * x.detach()).sum().backward()
+    gw = torch.full((CI + 2, CO, 4, 4), 7.0, device=dev())
+    _lib.check(C.nconv_b200_convT_phase_wgrad(_p(w3g.grad.float().contiguous()), _p(gw), CI, CO, 2, _stream(w)), "convT_phase_wgrad")
+    assert float((gw[2:].double() - wd.grad).abs().max()) <= 1e-5 * float(wd.grad.abs().max())
+    assert bool((gw[:2] == 7).all())                                    # the `lead` rows are left alone
+    # ---- 3x3 / stride-2 conv (CO output channels from CI input channels)
+    w = torch.randn(CO, CI, 3, 3, device=dev())
+    x = torch.randn(B, CI, 2 * H, 2 * W, device=dev(), dtype=torch.float64, requires_grad=True)
+    wd = w.double().requires_grad_(True)
+    gy = torch.randn(B, CO, H, W, device=dev(), dtype=torch.float64)
+    (F.conv2d(x, wd, stride=2, padding=1) * gy).sum().backward()
+    w3d = torch.empty(4 * CI, CO, 3, 3, device=dev())
+    _lib.check(C.nconv_b200_convS2_phase_weights(_p(w), _p(w3d), CO, CI, _stream(w)), "convS2_phase_weights")
+    gxp = F.conv2d(gy, w3d.double(), padding=1)                            # [B, 4CI, H, W], phase-major
+    assert float((gxp - phases(x.grad)).abs().max()) <= 1e-5 * float(x.grad.abs().max())
+    w3g = torch.zeros(CO, 4 * CI, 3, 3, device=dev(), dtype=torch.float64, requires_grad=True)
+    (F.conv2d(phases(x.detach()), w3g, padding=1) * gy).sum().backward()
+    gw = torch.empty(CO, CI, 3, 3, device=dev())
+    _lib.check(C.nconv_b200_convS2_phase_wgrad(_p(w3g.grad.float().contiguous()), _p(gw), CO, CI, _stream(w)), "convS2_phase_wgrad")
+    assert float((gw.double() - wd.grad).abs().max()) <= 1e-5 * float(wd.grad.abs().max())
